@@ -1,0 +1,299 @@
+"""ctypes binding of include/gfalign_b200.h (the drop-in C ABI).
+
+Mirrors the three reference entry points the ABI replaces — evaluatePath / evalPath scoring /
+InAlignments::buildEdgeGraph and the dijkstra() driver (reference src/eval.cpp:34-242) — with the
+same argument meaning; errors raise GfeError carrying the library's message.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+from typing import Callable, List, Optional, Sequence
+
+import numpy as np
+
+_u32p = C.POINTER(C.c_uint32)
+_i32p = C.POINTER(C.c_int32)
+_u8p = C.POINTER(C.c_uint8)
+
+GFE_SCORE_FILTERED = -(2 ** 31)
+GFE_MAX_STEPS = 1000
+
+
+class GfeError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"gfalign_b200 error {status}: {message}")
+        self.status = status
+
+
+def lib_path() -> str:
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "libgfalign_b200.so")
+
+
+class _SearchRow(C.Structure):
+    _fields_ = [("path_counter", C.c_uint64), ("bad", C.c_uint32), ("good", C.c_uint32),
+                ("alt", C.c_int32), ("size", C.c_uint32), ("uniques", C.c_uint32),
+                ("hamiltonian", C.c_int), ("steps", _u32p)]
+
+
+class _Graph(C.Structure):
+    _fields_ = [("n_nodes", C.c_uint32), ("adj_offsets", _u32p), ("adj_target", _u32p),
+                ("adj_or0", _u8p), ("adj_or1", _u8p)]
+
+
+class _SearchParams(C.Structure):
+    _fields_ = [("source", C.c_uint32), ("destination", C.c_uint32), ("budget_nodes", _u32p),
+                ("budget_counts", _u32p), ("n_budget", C.c_uint32), ("node_count", C.c_uint32),
+                ("max_steps", C.c_uint32), ("min_nodes", C.c_uint32),
+                ("return_all_paths", C.c_int), ("speculate", C.c_uint32)]
+
+
+class _SearchStats(C.Structure):
+    _fields_ = [("extractions", C.c_uint64), ("evaluations", C.c_uint64),
+                ("kernel_batches", C.c_uint64), ("paths_scored", C.c_uint64), ("rows", C.c_uint64),
+                ("reached_max_steps", C.c_int), ("seconds_scoring", C.c_double),
+                ("seconds_total", C.c_double)]
+
+
+class _Counters(C.Structure):
+    _fields_ = [("kernel_launches", C.c_uint64), ("exact_pairs", C.c_uint64),
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+
+
+_ROW_FN = C.CFUNCTYPE(None, C.POINTER(_SearchRow), C.c_void_p)
+
+# every symbol include/gfalign_b200.h declares (checked by tests/test_abi.py)
+EXPORTS = [
+    "gfe_create", "gfe_destroy", "gfe_last_error", "gfe_version", "gfe_set_alignments",
+    "gfe_set_alignments_device", "gfe_set_universe", "gfe_score_paths", "gfe_score_paths_device",
+    "gfe_score_pairs", "gfe_edge_support", "gfe_edge_traversals_device",
+    "gfe_edge_weights_from_counts", "gfe_search", "gfe_get_counters", "gfe_set_timing",
+    "gfe_last_kernel_ms",
+]
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """Load libgfalign_b200.so (built in-tree by __graft_entry__.build()). Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = lib_path()
+    if not os.path.exists(path):
+        raise ImportError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; "
+                          f"g.build()'` (nvcc, sm_100a). gfalign_b200 has no CPU fallback.")
+    lib = C.CDLL(path)
+    lib.gfe_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    lib.gfe_destroy.argtypes = [C.c_void_p]
+    lib.gfe_destroy.restype = None
+    lib.gfe_last_error.argtypes = [C.c_void_p]
+    lib.gfe_last_error.restype = C.c_char_p
+    lib.gfe_version.restype = C.c_char_p
+    lib.gfe_set_alignments.argtypes = [C.c_void_p, _u32p, _u32p, C.c_uint64, C.c_uint32]
+    lib.gfe_set_alignments_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64,
+                                              C.c_uint64, C.c_uint32]
+    lib.gfe_set_universe.argtypes = [C.c_void_p, _u32p, C.c_uint32]
+    lib.gfe_score_paths.argtypes = [C.c_void_p, _u32p, _u32p, C.c_uint32, C.c_int, _u32p]
+    lib.gfe_score_paths_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
+                                           C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]
+    lib.gfe_score_pairs.argtypes = [C.c_void_p, _u32p, C.c_uint32, C.c_int, _i32p, _i32p, _u32p,
+                                    _u32p]
+    lib.gfe_edge_support.argtypes = [C.c_void_p, _u32p, _u32p, C.c_uint32, _u32p]
+    lib.gfe_edge_traversals_device.argtypes = [C.c_void_p, _u32p, _u32p, C.c_uint32, C.c_void_p,
+                                               C.c_void_p]
+    lib.gfe_edge_weights_from_counts.argtypes = [_u32p, _u32p, C.c_uint32, _u32p, _u32p]
+    lib.gfe_search.argtypes = [C.c_void_p, C.POINTER(_Graph), C.POINTER(_SearchParams), _ROW_FN,
+                               C.c_void_p, C.POINTER(_SearchStats)]
+    lib.gfe_get_counters.argtypes = [C.c_void_p, C.POINTER(_Counters)]
+    lib.gfe_set_timing.argtypes = [C.c_void_p, C.c_int]
+    lib.gfe_last_kernel_ms.argtypes = [C.c_void_p]
+    lib.gfe_last_kernel_ms.restype = C.c_float
+    _lib = lib
+    return lib
+
+
+def _u32(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.uint32)
+
+
+def _ptr(a: np.ndarray, typ=_u32p):
+    return a.ctypes.data_as(typ)
+
+
+@dataclass
+class SearchRow:
+    """One emitted row of `gfalign search` (reference src/eval.cpp:183)."""
+    path_counter: int
+    bad: int
+    good: int
+    alt: int
+    size: int
+    uniques: int
+    hamiltonian: bool
+    steps: List[int]
+
+    def columns(self, names: Sequence[str]) -> str:
+        path = ",".join(f"{names[s >> 1]}{'-' if s & 1 else '+'}" for s in self.steps)
+        return "\t".join([str(self.path_counter), str(self.bad), str(self.good), str(self.alt),
+                          str(self.size), str(self.uniques), "T" if self.hamiltonian else "F", path])
+
+
+class Engine:
+    """One engine = one CUDA device.  Thin, typed wrapper over the gfe_* C ABI."""
+
+    def __init__(self, device: int = 0):
+        self._lib = load_library()
+        h = C.c_void_p()
+        rc = self._lib.gfe_create(device, C.byref(h))
+        if rc != 0:
+            raise GfeError(rc, self._lib.gfe_last_error(None).decode())
+        self._h = h
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.gfe_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise GfeError(rc, self._lib.gfe_last_error(self._h).decode())
+
+    # -- alignment table ---------------------------------------------------------------------
+    def set_alignments(self, offsets, steps, n_nodes: int):
+        offsets, steps = _u32(offsets), _u32(steps)
+        if offsets.size < 1:
+            raise ValueError("offsets must have A+1 entries")
+        self._check(self._lib.gfe_set_alignments(self._h, _ptr(offsets), _ptr(steps),
+                                                 offsets.size - 1, n_nodes))
+
+    def set_alignments_device(self, d_offsets_ptr: int, d_steps_ptr: int, A: int, total_steps: int,
+                              n_nodes: int):
+        self._check(self._lib.gfe_set_alignments_device(self._h, d_offsets_ptr, d_steps_ptr, A,
+                                                        total_steps, n_nodes))
+
+    def set_universe(self, nodes):
+        nodes = _u32(nodes)
+        self._check(self._lib.gfe_set_universe(self._h, _ptr(nodes), nodes.size))
+
+    # -- scoring -----------------------------------------------------------------------------
+    def score_paths(self, path_offsets, path_steps, filter: bool = True) -> np.ndarray:
+        """evaluatePath for P candidate paths -> uint32 array (P, 2) of (bad, good)."""
+        po, ps = _u32(path_offsets), _u32(path_steps)
+        P = po.size - 1
+        counts = np.zeros((max(P, 0), 2), dtype=np.uint32)
+        self._check(self._lib.gfe_score_paths(self._h, _ptr(po), _ptr(ps), P, int(filter),
+                                              _ptr(counts)))
+        return counts
+
+    def score_paths_device(self, d_path_offsets: int, d_path_steps: int, P: int, total: int,
+                           d_counts: int, filter: bool = True, stream: int = 0):
+        self._check(self._lib.gfe_score_paths_device(self._h, d_path_offsets, d_path_steps, P,
+                                                     total, int(filter), d_counts, stream))
+
+    def score_pairs(self, path_steps, filter: bool = False, want_scores: bool = True):
+        """evalPath scoring: (t_fw, t_rc, bad, good) of one path against every alignment."""
+        ps = _u32(path_steps)
+        A = self._A_hint
+        bad, good = C.c_uint32(), C.c_uint32()
+        if want_scores:
+            tf = np.empty(A, dtype=np.int32)
+            tr = np.empty(A, dtype=np.int32)
+            self._check(self._lib.gfe_score_pairs(self._h, _ptr(ps), ps.size, int(filter),
+                                                  _ptr(tf, _i32p), _ptr(tr, _i32p),
+                                                  C.byref(bad), C.byref(good)))
+            return tf, tr, bad.value, good.value
+        self._check(self._lib.gfe_score_pairs(self._h, _ptr(ps), ps.size, int(filter), None, None,
+                                              C.byref(bad), C.byref(good)))
+        return None, None, bad.value, good.value
+
+    # -- edge support ------------------------------------------------------------------------
+    def edge_support(self, edge_from, edge_to) -> np.ndarray:
+        ef, et = _u32(edge_from), _u32(edge_to)
+        w = np.zeros(ef.size, dtype=np.uint32)
+        self._check(self._lib.gfe_edge_support(self._h, _ptr(ef), _ptr(et), ef.size, _ptr(w)))
+        return w
+
+    def edge_traversals_device(self, edge_from, edge_to, d_counts: int, stream: int = 0):
+        ef, et = _u32(edge_from), _u32(edge_to)
+        self._check(self._lib.gfe_edge_traversals_device(self._h, _ptr(ef), _ptr(et), ef.size,
+                                                         d_counts, stream))
+
+    @staticmethod
+    def edge_weights_from_counts(edge_from, edge_to, counts) -> np.ndarray:
+        lib = load_library()
+        ef, et, cn = _u32(edge_from), _u32(edge_to), _u32(counts)
+        w = np.zeros(ef.size, dtype=np.uint32)
+        rc = lib.gfe_edge_weights_from_counts(_ptr(ef), _ptr(et), ef.size, _ptr(cn), _ptr(w))
+        if rc != 0:
+            raise GfeError(rc, "gfe_edge_weights_from_counts: bad arguments")
+        return w
+
+    # -- search ------------------------------------------------------------------------------
+    def search(self, adj_offsets, adj_target, adj_or0, adj_or1, source: int, destination: int,
+               budget_nodes, budget_counts, node_count: int, max_steps: int = 100000,
+               min_nodes: int = 0, return_all_paths: bool = False, speculate: int = 0,
+               on_row: Optional[Callable[[SearchRow], None]] = None):
+        """dijkstra() of the reference on packed inputs -> (rows, stats dict)."""
+        ao, at = _u32(adj_offsets), _u32(adj_target)
+        o0 = np.ascontiguousarray(adj_or0, dtype=np.uint8)
+        o1 = np.ascontiguousarray(adj_or1, dtype=np.uint8)
+        bn, bc = _u32(budget_nodes), _u32(budget_counts)
+        g = _Graph(ao.size - 1, _ptr(ao), _ptr(at), _ptr(o0, _u8p), _ptr(o1, _u8p))
+        p = _SearchParams(source, destination, _ptr(bn), _ptr(bc), bn.size, node_count, max_steps,
+                          min_nodes, int(return_all_paths), speculate)
+        rows: List[SearchRow] = []
+
+        def _cb(rp, _user):
+            r = rp.contents
+            row = SearchRow(r.path_counter, r.bad, r.good, r.alt, r.size, r.uniques,
+                            bool(r.hamiltonian), [r.steps[i] for i in range(r.size)])
+            rows.append(row)
+            if on_row:
+                on_row(row)
+
+        cb = _ROW_FN(_cb)
+        st = _SearchStats()
+        self._check(self._lib.gfe_search(self._h, C.byref(g), C.byref(p), cb, None, C.byref(st)))
+        stats = {f: getattr(st, f) for f, _ in _SearchStats._fields_}
+        return rows, stats
+
+    # -- introspection -----------------------------------------------------------------------
+    def counters(self) -> dict:
+        c = _Counters()
+        self._check(self._lib.gfe_get_counters(self._h, C.byref(c)))
+        return {f: getattr(c, f) for f, _ in _Counters._fields_}
+
+    def set_timing(self, on: bool):
+        self._check(self._lib.gfe_set_timing(self._h, int(on)))
+
+    def last_kernel_ms(self) -> float:
+        return float(self._lib.gfe_last_kernel_ms(self._h))
+
+    # set_alignments records A so score_pairs can size its outputs
+    _A_hint = 0
+
+
+_orig_set = Engine.set_alignments
+
+
+def _set_alignments(self, offsets, steps, n_nodes):
+    _orig_set(self, offsets, steps, n_nodes)
+    self._A_hint = int(np.asarray(offsets).size - 1)
+
+
+Engine.set_alignments = _set_alignments

@@ -1,0 +1,624 @@
+// gfalign_b200/csrc/engine.cu — C ABI (include/gfalign_b200.h) over the sm_100a kernels.
+// Owns the device copies of the alignment table, the universe-local view, staging buffers and
+// one CUDA stream.  There is no CPU scoring path in this library: every entry point either runs
+// the kernels or fails with an error status.
+#include "engine.h"
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <unordered_map>
+
+using namespace gfe;
+
+static thread_local char g_create_error[512] = "";
+
+static void set_error(gfe_engine *e, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    if (e) vsnprintf(e->error, sizeof(e->error), fmt, ap);
+    else vsnprintf(g_create_error, sizeof(g_create_error), fmt, ap);
+    va_end(ap);
+}
+
+#define CUDA_TRY(e, call)                                                                   \
+    do {                                                                                    \
+        cudaError_t err__ = (call);                                                         \
+        if (err__ != cudaSuccess) {                                                         \
+            set_error((e), "%s failed: %s (%s:%d)", #call, cudaGetErrorString(err__),       \
+                      __FILE__, __LINE__);                                                  \
+            return GFE_ERR_CUDA;                                                            \
+        }                                                                                   \
+    } while (0)
+
+template <typename T>
+static int ensure_dev(gfe_engine *e, DevBuf<T> &b, size_t n) {
+    if (n <= b.cap) return GFE_OK;
+    size_t want = std::max(n, b.cap + b.cap / 2);
+    if (b.ptr) CUDA_TRY(e, cudaFree(b.ptr));
+    b.ptr = nullptr;
+    b.cap = 0;
+    CUDA_TRY(e, cudaMalloc(&b.ptr, want * sizeof(T)));
+    b.cap = want;
+    return GFE_OK;
+}
+
+template <typename T>
+static int ensure_pinned(gfe_engine *e, PinBuf<T> &b, size_t n) {
+    if (n <= b.cap) return GFE_OK;
+    size_t want = std::max(n, b.cap + b.cap / 2);
+    if (b.ptr) CUDA_TRY(e, cudaFreeHost(b.ptr));
+    b.ptr = nullptr;
+    b.cap = 0;
+    CUDA_TRY(e, cudaMallocHost(&b.ptr, want * sizeof(T)));
+    b.cap = want;
+    return GFE_OK;
+}
+
+#define TRY(x)                      \
+    do {                            \
+        int rc__ = (x);             \
+        if (rc__ != GFE_OK) return rc__; \
+    } while (0)
+
+extern "C" {
+
+const char *gfe_version(void) { return "gfalign_b200 0.1 (sm_100a)"; }
+
+const char *gfe_last_error(const gfe_engine *e) { return e ? e->error : g_create_error; }
+
+int gfe_create(int cuda_device, gfe_engine **out) {
+    if (!out) return GFE_ERR_ARG;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t err = cudaGetDeviceCount(&count);
+    if (err != cudaSuccess || count == 0) {
+        set_error(nullptr, "no CUDA device available (%s); gfalign_b200 has no CPU fallback",
+                  err != cudaSuccess ? cudaGetErrorString(err) : "device count is 0");
+        return GFE_ERR_CUDA;
+    }
+    if (cuda_device < 0 || cuda_device >= count) {
+        set_error(nullptr, "CUDA device %d out of range (0..%d)", cuda_device, count - 1);
+        return GFE_ERR_ARG;
+    }
+    gfe_engine *e = new (std::nothrow) gfe_engine();
+    if (!e) return GFE_ERR_NOMEM;
+    e->device = cuda_device;
+    err = cudaSetDevice(cuda_device);
+    if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    if (err == cudaSuccess) err = cudaEventCreate(&e->ev0);
+    if (err == cudaSuccess) err = cudaEventCreate(&e->ev1);
+    cudaDeviceProp prop;
+    if (err == cudaSuccess) err = cudaGetDeviceProperties(&prop, cuda_device);
+    if (err == cudaSuccess) {
+        e->sm_count = prop.multiProcessorCount;
+        int rc = configure_kernels();
+        if (rc != 0) err = (cudaError_t)rc;
+    }
+    if (err != cudaSuccess) {
+        set_error(nullptr, "CUDA initialisation failed on device %d: %s", cuda_device,
+                  cudaGetErrorString(err));
+        delete e;
+        return GFE_ERR_CUDA;
+    }
+    *out = e;
+    return GFE_OK;
+}
+
+void gfe_destroy(gfe_engine *e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    e->free_all();
+    if (e->ev0) cudaEventDestroy(e->ev0);
+    if (e->ev1) cudaEventDestroy(e->ev1);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+int gfe_set_timing(gfe_engine *e, int enabled) {
+    if (!e) return GFE_ERR_ARG;
+    e->timing = enabled != 0;
+    return GFE_OK;
+}
+
+float gfe_last_kernel_ms(const gfe_engine *e) { return e ? e->last_kernel_ms : 0.f; }
+
+int gfe_get_counters(const gfe_engine *e, gfe_counters *out) {
+    if (!e || !out) return GFE_ERR_ARG;
+    out->kernel_launches = e->kernel_launches;
+    out->exact_pairs = e->exact_pairs;
+    out->h2d_bytes = e->h2d_bytes;
+    out->d2h_bytes = e->d2h_bytes;
+    return GFE_OK;
+}
+
+// ---- alignment table ----------------------------------------------------------------------------
+
+static int validate_csr_host(gfe_engine *e, const uint32_t *offsets, const uint32_t *steps,
+                             uint64_t A, uint32_t n_nodes, uint32_t *max_m) {
+    if (!offsets || (A && !steps && offsets[A] != 0)) {
+        set_error(e, "alignment CSR: NULL buffer");
+        return GFE_ERR_ARG;
+    }
+    if (offsets[0] != 0) {
+        set_error(e, "alignment CSR: offsets[0] must be 0");
+        return GFE_ERR_ARG;
+    }
+    uint32_t mx = 0;
+    for (uint64_t a = 0; a < A; ++a) {
+        if (offsets[a + 1] < offsets[a]) {
+            set_error(e, "alignment CSR: offsets not monotone at %llu", (unsigned long long)a);
+            return GFE_ERR_ARG;
+        }
+        uint32_t m = offsets[a + 1] - offsets[a];
+        if (m > GFE_MAX_STEPS) {
+            set_error(e, "alignment %llu has %u steps; the reference's MAX_N allows %u",
+                      (unsigned long long)a, m, GFE_MAX_STEPS);
+            return GFE_ERR_LIMIT;
+        }
+        mx = std::max(mx, m);
+    }
+    const uint64_t S = offsets[A];
+    for (uint64_t i = 0; i < S; ++i)
+        if ((steps[i] >> 1) >= n_nodes) {
+            set_error(e, "alignment step %llu names node %u >= n_nodes %u", (unsigned long long)i,
+                      steps[i] >> 1, n_nodes);
+            return GFE_ERR_ARG;
+        }
+    *max_m = mx;
+    return GFE_OK;
+}
+
+int gfe_set_alignments(gfe_engine *e, const uint32_t *offsets, const uint32_t *steps, uint64_t A,
+                       uint32_t n_nodes) {
+    if (!e) return GFE_ERR_ARG;
+    if (A >= 0xFFFFFFFFull) {
+        set_error(e, "more than 2^32-2 alignments per engine are not supported; shard them");
+        return GFE_ERR_LIMIT;
+    }
+    uint32_t mx = 0;
+    TRY(validate_csr_host(e, offsets, steps, A, n_nodes, &mx));
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const uint64_t S = offsets[A];
+    TRY(ensure_dev(e, e->own_off, A + 1));
+    TRY(ensure_dev(e, e->own_steps, std::max<uint64_t>(S, 1) + 4));
+    CUDA_TRY(e, cudaMemcpyAsync(e->own_off.ptr, offsets, (A + 1) * sizeof(uint32_t),
+                                cudaMemcpyHostToDevice, e->stream));
+    if (S)
+        CUDA_TRY(e, cudaMemcpyAsync(e->own_steps.ptr, steps, S * sizeof(uint32_t),
+                                    cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    e->h2d_bytes += (A + 1 + S) * sizeof(uint32_t);
+    e->d_off = e->own_off.ptr;
+    e->d_steps = e->own_steps.ptr;
+    e->A = A;
+    e->S = S;
+    e->n_nodes = n_nodes;
+    e->max_m = mx;
+    e->have_alignments = true;
+    e->have_universe = false;
+    return GFE_OK;
+}
+
+int gfe_set_alignments_device(gfe_engine *e, const uint32_t *d_offsets, const uint32_t *d_steps,
+                              uint64_t A, uint64_t total_steps, uint32_t n_nodes) {
+    if (!e || !d_offsets || (total_steps && !d_steps)) return GFE_ERR_ARG;
+    if (A >= 0xFFFFFFFFull || total_steps >= 0xFFFFFFFFull) {
+        set_error(e, "shard too large for 32-bit CSR offsets");
+        return GFE_ERR_LIMIT;
+    }
+    e->d_off = d_offsets;
+    e->d_steps = d_steps;
+    e->A = A;
+    e->S = total_steps;
+    e->n_nodes = n_nodes;
+    e->max_m = GFE_MAX_STEPS;   // unknown: keep the long-alignment kernels armed
+    e->have_alignments = true;
+    e->have_universe = false;
+    return GFE_OK;
+}
+
+int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) {
+    if (!e || (n_universe && !nodes)) return GFE_ERR_ARG;
+    if (!e->have_alignments) {
+        set_error(e, "gfe_set_universe: call gfe_set_alignments first");
+        return GFE_ERR_STATE;
+    }
+    if (n_universe > GFE_MAX_UNIVERSE) {
+        set_error(e, "universe of %u nodes exceeds the %u the 16-bit local ids can name", n_universe,
+                  GFE_MAX_UNIVERSE);
+        return GFE_ERR_LIMIT;
+    }
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    e->node2local.assign(e->n_nodes, n_universe);
+    uint32_t L = 0;
+    for (uint32_t i = 0; i < n_universe; ++i) {
+        if (nodes[i] >= e->n_nodes) {
+            set_error(e, "universe node %u >= n_nodes %u", nodes[i], e->n_nodes);
+            return GFE_ERR_ARG;
+        }
+        if (e->node2local[nodes[i]] == n_universe) e->node2local[nodes[i]] = L++;
+    }
+    // duplicates in `nodes` leave local ids [L, n_universe) unused; the outside id stays n_universe
+    e->L = n_universe;
+    TRY(ensure_dev(e, e->d_node2local, std::max<uint32_t>(e->n_nodes, 1)));
+    if (e->n_nodes)
+        CUDA_TRY(e, cudaMemcpyAsync(e->d_node2local.ptr, e->node2local.data(),
+                                    (size_t)e->n_nodes * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                                    e->stream));
+    TRY(ensure_dev(e, e->d_lstep, e->S + 8));
+    launch_localize_steps(e->d_steps, e->d_node2local.ptr, e->d_lstep.ptr, e->S, e->stream);
+    e->kernel_launches += e->S ? 1 : 0;
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    e->h2d_bytes += (size_t)e->n_nodes * sizeof(uint32_t);
+    e->tab_stride = ((e->L + 1 + 7) / 8) * 8;
+    e->have_universe = true;
+    return GFE_OK;
+}
+
+// ---- search scoring -----------------------------------------------------------------------------
+
+static uint32_t pick_chunk(const gfe_engine *e, uint32_t P) {
+    const size_t row = (size_t)e->tab_stride * 2 + 12;
+    size_t budget = 48 * 1024;               // keeps several CTAs per SM for small tables
+    uint32_t c = (uint32_t)std::max<size_t>(1, budget / row);
+    c = std::min<uint32_t>(c, 64);
+    return std::min<uint32_t>(c, std::max<uint32_t>(P, 1));
+}
+
+// Enqueue table build + scoring (+ exact fallbacks) for paths already on the device in local ids.
+static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *d_pstep, uint32_t P,
+                         int filter, uint32_t *d_counts, cudaStream_t st) {
+    TRY(ensure_dev(e, e->d_ptab, (size_t)P * e->tab_stride));
+    if (!e->d_work.ptr) {
+        TRY(ensure_dev(e, e->d_work, e->work_cap));
+        TRY(ensure_dev(e, e->d_work_count, 4));
+    }
+    CUDA_TRY(e, cudaMemsetAsync(d_counts, 0, (size_t)P * 2 * sizeof(uint32_t), st));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_work_count.ptr, 0, 4 * sizeof(uint32_t), st));
+    launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, st);
+    ScoreArgs a;
+    a.off = e->d_off;
+    a.lstep = e->d_lstep.ptr;
+    a.A = e->A;
+    a.poff = d_poff;
+    a.pstep = d_pstep;
+    a.ptab = e->d_ptab.ptr;
+    a.tab_stride = e->tab_stride;
+    a.P = P;
+    a.chunk = pick_chunk(e, P);
+    a.filter = filter;
+    a.counts = d_counts;
+    a.work = e->d_work.ptr;
+    a.work_count = e->d_work_count.ptr;
+    a.work_cap = (uint32_t)e->work_cap;
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    launch_score_paths(a, e->sm_count, st);
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
+    e->kernel_launches += 1 + (e->A ? 1 : 0);
+    if (e->A) {
+        launch_exact_worklist(a, st);
+        e->kernel_launches += 1;
+        if (e->max_m > (uint32_t)kExactRegSteps) {
+            launch_exact_worklist_long(a, e->max_m, st);
+            e->kernel_launches += 1;
+        }
+    }
+    CUDA_TRY(e, cudaGetLastError());
+    return GFE_OK;
+}
+
+int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t *path_steps,
+                    uint32_t P, int filter, uint32_t *counts) {
+    if (!e || !path_offsets || !counts) return GFE_ERR_ARG;
+    if (!e->have_alignments || !e->have_universe) {
+        set_error(e, "gfe_score_paths: alignments and universe must be set first");
+        return GFE_ERR_STATE;
+    }
+    if (P == 0) return GFE_OK;
+    if (!path_steps || path_offsets[0] != 0) {
+        set_error(e, "gfe_score_paths: malformed path CSR");
+        return GFE_ERR_ARG;
+    }
+    const uint32_t total = path_offsets[P];
+    for (uint32_t p = 0; p < P; ++p) {
+        if (path_offsets[p + 1] <= path_offsets[p]) {
+            set_error(e, "gfe_score_paths: path %u is empty or offsets not monotone", p);
+            return GFE_ERR_ARG;
+        }
+        if (path_offsets[p + 1] - path_offsets[p] > GFE_MAX_STEPS) {
+            set_error(e, "gfe_score_paths: path %u has %u steps; the reference's MAX_N allows %u",
+                      p, path_offsets[p + 1] - path_offsets[p], GFE_MAX_STEPS);
+            return GFE_ERR_LIMIT;
+        }
+    }
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    // staging: [P+1 offsets u32][total local steps u16]
+    const size_t off_bytes = ((size_t)(P + 1) * 4 + 15) & ~(size_t)15;
+    const size_t bytes = off_bytes + (size_t)total * 2;
+    TRY(ensure_pinned(e, e->h_stage, bytes));
+    TRY(ensure_dev(e, e->d_stage, bytes));
+    TRY(ensure_pinned(e, e->h_counts, (size_t)P * 2));
+    TRY(ensure_dev(e, e->d_counts, (size_t)P * 2));
+    memcpy(e->h_stage.ptr, path_offsets, (size_t)(P + 1) * 4);
+    uint16_t *ls = reinterpret_cast<uint16_t *>(e->h_stage.ptr + off_bytes);
+    for (uint32_t i = 0; i < total; ++i) {
+        const uint32_t node = path_steps[i] >> 1;
+        const uint32_t l = node < e->n_nodes ? e->node2local[node] : e->L;
+        if (l >= e->L) {
+            set_error(e, "gfe_score_paths: step %u names node %u outside the universe", i, node);
+            return GFE_ERR_ARG;
+        }
+        ls[i] = (uint16_t)((l << 1) | (path_steps[i] & 1u));
+    }
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_stage.ptr, e->h_stage.ptr, bytes, cudaMemcpyHostToDevice,
+                                e->stream));
+    const uint32_t *d_poff = reinterpret_cast<const uint32_t *>(e->d_stage.ptr);
+    const uint16_t *d_pstep = reinterpret_cast<const uint16_t *>(e->d_stage.ptr + off_bytes);
+    TRY(enqueue_score(e, d_poff, d_pstep, P, filter, e->d_counts.ptr, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, (size_t)P * 2 * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, e->stream));
+    uint32_t wc[2] = {0, 0};
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_wc, e->d_work_count.ptr, 2 * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    wc[0] = e->h_wc[0];
+    wc[1] = e->h_wc[1];
+    if (e->timing) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
+    e->h2d_bytes += bytes;
+    e->d2h_bytes += (size_t)P * 2 * sizeof(uint32_t) + 8;
+    if (wc[1]) {
+        // the exact-DP worklist overflowed: grow it and redo the batch (never silently wrong)
+        e->work_cap = std::max<size_t>(e->work_cap * 4, (size_t)wc[0] + 1024);
+        CUDA_TRY(e, cudaFree(e->d_work.ptr));
+        e->d_work.ptr = nullptr;
+        e->d_work.cap = 0;
+        TRY(ensure_dev(e, e->d_work, e->work_cap));
+        return gfe_score_paths(e, path_offsets, path_steps, P, filter, counts);
+    }
+    e->exact_pairs += wc[0];
+    memcpy(counts, e->h_counts.ptr, (size_t)P * 2 * sizeof(uint32_t));
+    return GFE_OK;
+}
+
+int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
+                           const uint32_t *d_path_steps, uint32_t P, uint32_t total_path_steps,
+                           int filter, uint32_t *d_counts, void *cuda_stream) {
+    if (!e || !d_path_offsets || !d_path_steps || !d_counts) return GFE_ERR_ARG;
+    if (!e->have_alignments || !e->have_universe) {
+        set_error(e, "gfe_score_paths_device: alignments and universe must be set first");
+        return GFE_ERR_STATE;
+    }
+    if (P == 0) return GFE_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : e->stream;
+    TRY(ensure_dev(e, e->d_plocal, (size_t)total_path_steps + 8));
+    if (!e->d_err.ptr) {
+        TRY(ensure_dev(e, e->d_err, 4));
+        CUDA_TRY(e, cudaMemsetAsync(e->d_err.ptr, 0, 4 * sizeof(uint32_t), st));
+    }
+    launch_localize_paths(d_path_steps, e->d_node2local.ptr, e->n_nodes, e->L, e->d_plocal.ptr,
+                          total_path_steps, e->d_err.ptr, st);
+    e->kernel_launches += 1;
+    return enqueue_score(e, d_path_offsets, e->d_plocal.ptr, P, filter, d_counts, st);
+}
+
+// ---- evalPath scoring ---------------------------------------------------------------------------
+
+int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int filter,
+                    int32_t *t_fw, int32_t *t_rc, uint32_t *bad, uint32_t *good) {
+    if (!e || !path_steps || !bad || !good) return GFE_ERR_ARG;
+    if (!e->have_alignments) {
+        set_error(e, "gfe_score_pairs: call gfe_set_alignments first");
+        return GFE_ERR_STATE;
+    }
+    if (n == 0 || n > GFE_MAX_STEPS) {
+        set_error(e, "gfe_score_pairs: path has %u steps; allowed 1..%u", n, GFE_MAX_STEPS);
+        return n == 0 ? GFE_ERR_ARG : GFE_ERR_LIMIT;
+    }
+    // universe = the distinct nodes of the path, in first-visit order
+    std::vector<uint32_t> uni;
+    uni.reserve(n);
+    {
+        std::unordered_map<uint32_t, uint32_t> seen;
+        for (uint32_t i = 0; i < n; ++i) {
+            const uint32_t node = path_steps[i] >> 1;
+            if (node >= e->n_nodes) {
+                set_error(e, "gfe_score_pairs: step %u names node %u >= n_nodes %u", i, node,
+                          e->n_nodes);
+                return GFE_ERR_ARG;
+            }
+            if (seen.emplace(node, (uint32_t)uni.size()).second) uni.push_back(node);
+        }
+    }
+    TRY(gfe_set_universe(e, uni.data(), (uint32_t)uni.size()));
+    const size_t off_bytes = 16;
+    const size_t bytes = off_bytes + (size_t)n * 2;
+    TRY(ensure_pinned(e, e->h_stage, bytes));
+    TRY(ensure_dev(e, e->d_stage, bytes));
+    uint32_t *po = reinterpret_cast<uint32_t *>(e->h_stage.ptr);
+    po[0] = 0;
+    po[1] = n;
+    uint16_t *ls = reinterpret_cast<uint16_t *>(e->h_stage.ptr + off_bytes);
+    for (uint32_t i = 0; i < n; ++i)
+        ls[i] = (uint16_t)((e->node2local[path_steps[i] >> 1] << 1) | (path_steps[i] & 1u));
+    cudaStream_t st = e->stream;
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_stage.ptr, e->h_stage.ptr, bytes, cudaMemcpyHostToDevice, st));
+    const uint32_t *d_poff = reinterpret_cast<const uint32_t *>(e->d_stage.ptr);
+    const uint16_t *d_pstep = reinterpret_cast<const uint16_t *>(e->d_stage.ptr + off_bytes);
+    TRY(ensure_dev(e, e->d_ptab, (size_t)e->tab_stride));
+    TRY(ensure_dev(e, e->d_counts, 2));
+    TRY(ensure_pinned(e, e->h_counts, 2));
+    TRY(ensure_dev(e, e->d_pair_work, std::max<uint64_t>(e->A, 1)));
+    TRY(ensure_dev(e, e->d_work_count, 4));
+    const bool want_scores = t_fw || t_rc;
+    if (want_scores) {
+        TRY(ensure_dev(e, e->d_tfw, std::max<uint64_t>(e->A, 1)));
+        TRY(ensure_dev(e, e->d_trc, std::max<uint64_t>(e->A, 1)));
+    }
+    CUDA_TRY(e, cudaMemsetAsync(e->d_counts.ptr, 0, 2 * sizeof(uint32_t), st));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_work_count.ptr, 0, 4 * sizeof(uint32_t), st));
+    launch_build_tables(d_poff, d_pstep, 1, e->L, e->tab_stride, e->d_ptab.ptr, st);
+    PairArgs a;
+    a.off = e->d_off;
+    a.lstep = e->d_lstep.ptr;
+    a.A = e->A;
+    a.pstep = d_pstep;
+    a.n = n;
+    a.ptab = e->d_ptab.ptr;
+    a.tab_entries = e->tab_stride;
+    a.filter = filter;
+    a.t_fw = want_scores ? e->d_tfw.ptr : nullptr;
+    a.t_rc = want_scores ? e->d_trc.ptr : nullptr;
+    a.counts = e->d_counts.ptr;
+    a.work = e->d_pair_work.ptr;
+    a.work_count = e->d_work_count.ptr;
+    a.work_cap = (uint32_t)std::min<uint64_t>(e->d_pair_work.cap, 0xFFFFFFFFu);
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    launch_pair_classify(a, e->sm_count, st);
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
+    e->kernel_launches += 1 + (e->A ? 1 : 0);
+    if (e->A) {
+        launch_pair_exact(a, st);
+        e->kernel_launches += 1;
+        if (e->max_m > (uint32_t)kExactRegSteps) {
+            launch_pair_exact_long(a, e->max_m, st);
+            e->kernel_launches += 1;
+        }
+    }
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, 2 * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_wc, e->d_work_count.ptr, 2 * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, st));
+    if (t_fw && e->A)
+        CUDA_TRY(e, cudaMemcpyAsync(t_fw, e->d_tfw.ptr, e->A * sizeof(int32_t),
+                                    cudaMemcpyDeviceToHost, st));
+    if (t_rc && e->A)
+        CUDA_TRY(e, cudaMemcpyAsync(t_rc, e->d_trc.ptr, e->A * sizeof(int32_t),
+                                    cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(e, cudaStreamSynchronize(st));
+    if (e->timing) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
+    e->exact_pairs += e->h_wc[0];
+    e->h2d_bytes += bytes;
+    e->d2h_bytes += 16 + ((t_fw ? 1 : 0) + (t_rc ? 1 : 0)) * e->A * sizeof(int32_t);
+    *bad = e->h_counts.ptr[0];
+    *good = e->h_counts.ptr[1];
+    return GFE_OK;
+}
+
+// ---- edge support -------------------------------------------------------------------------------
+
+namespace {
+struct PairKeyHash {
+    size_t operator()(uint64_t k) const { return (size_t)(k * 0x9E3779B97F4A7C15ull >> 16); }
+};
+inline uint64_t pair_key(uint32_t from, uint32_t to) { return ((uint64_t)from << 32) | to; }
+
+// representative slot of every directed pair: the first slot (2i = edge i, 2i+1 = its reverse
+// complement) that carries the pair.
+void build_rep(const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
+               std::unordered_map<uint64_t, uint32_t, PairKeyHash> &rep) {
+    rep.reserve((size_t)E * 2 + 1);
+    for (uint32_t i = 0; i < E; ++i) {
+        rep.emplace(pair_key(edge_from[i], edge_to[i]), 2 * i);
+        rep.emplace(pair_key(edge_to[i] ^ 1u, edge_from[i] ^ 1u), 2 * i + 1);
+    }
+}
+}  // namespace
+
+int gfe_edge_traversals_device(gfe_engine *e, const uint32_t *edge_from, const uint32_t *edge_to,
+                               uint32_t E, uint32_t *d_counts, void *cuda_stream) {
+    if (!e || (E && (!edge_from || !edge_to)) || !d_counts) return GFE_ERR_ARG;
+    if (!e->have_alignments) {
+        set_error(e, "gfe_edge_support: call gfe_set_alignments first");
+        return GFE_ERR_STATE;
+    }
+    if (E >= 0x7FFFFFFFu) return GFE_ERR_LIMIT;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : e->stream;
+    const uint32_t space = 2 * e->n_nodes;
+    for (uint32_t i = 0; i < E; ++i)
+        if (edge_from[i] >= space || edge_to[i] >= space) {
+            set_error(e, "edge %u names a node >= n_nodes %u", i, e->n_nodes);
+            return GFE_ERR_ARG;
+        }
+    // adjacency rows by oriented from-step, entries (to, representative slot), deduplicated
+    std::unordered_map<uint64_t, uint32_t, PairKeyHash> rep;
+    build_rep(edge_from, edge_to, E, rep);
+    std::vector<uint32_t> row_off((size_t)space + 1, 0);
+    for (auto &kv : rep) row_off[(kv.first >> 32) + 1]++;
+    for (uint32_t i = 0; i < space; ++i) row_off[i + 1] += row_off[i];
+    std::vector<uint2> ent(rep.size());
+    {
+        std::vector<uint32_t> fill(row_off.begin(), row_off.end() - 1);
+        for (auto &kv : rep) {
+            const uint32_t from = (uint32_t)(kv.first >> 32);
+            ent[fill[from]++] = make_uint2((uint32_t)kv.first, kv.second);
+        }
+    }
+    TRY(ensure_dev(e, e->d_row_off, row_off.size()));
+    TRY(ensure_dev(e, e->d_row_ent, std::max<size_t>(ent.size(), 1)));
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_row_off.ptr, row_off.data(), row_off.size() * 4,
+                                cudaMemcpyHostToDevice, st));
+    if (!ent.empty())
+        CUDA_TRY(e, cudaMemcpyAsync(e->d_row_ent.ptr, ent.data(), ent.size() * sizeof(uint2),
+                                    cudaMemcpyHostToDevice, st));
+    CUDA_TRY(e, cudaMemsetAsync(d_counts, 0, (size_t)E * 2 * sizeof(uint32_t), st));
+    EdgeArgs a;
+    a.off = e->d_off;
+    a.steps = e->d_steps;
+    a.A = e->A;
+    a.row_off = e->d_row_off.ptr;
+    a.row_ent = e->d_row_ent.ptr;
+    a.n_steps_space = space;
+    a.counts = d_counts;
+    a.n_slots = 2 * E;
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    if (E) launch_edge_support(a, e->sm_count, st);
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
+    e->kernel_launches += (E && e->A) ? 1 : 0;
+    CUDA_TRY(e, cudaGetLastError());
+    // the host vectors above must outlive the async copies
+    CUDA_TRY(e, cudaStreamSynchronize(st));
+    e->h2d_bytes += row_off.size() * 4 + ent.size() * sizeof(uint2);
+    return GFE_OK;
+}
+
+int gfe_edge_weights_from_counts(const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
+                                 const uint32_t *counts, uint32_t *weights) {
+    if (E && (!edge_from || !edge_to || !counts || !weights)) return GFE_ERR_ARG;
+    std::unordered_map<uint64_t, uint32_t, PairKeyHash> rep;
+    build_rep(edge_from, edge_to, E, rep);
+    for (uint32_t i = 0; i < E; ++i) {
+        const uint32_t x = edge_from[i], y = edge_to[i];
+        const bool hairpin = (y == (x ^ 1u));   // its reverse complement is itself
+        uint64_t k = counts[rep[pair_key(x, y)]];
+        if (!hairpin) k += counts[rep[pair_key(y ^ 1u, x ^ 1u)]];
+        // reference src/alignments.cpp:371-396: the twin entries are incremented together; a
+        // self-twin edge is inserted with weight 1 and then incremented twice per traversal.
+        weights[i] = (uint32_t)(hairpin ? (k ? 2 * k - 1 : 0) : k);
+    }
+    return GFE_OK;
+}
+
+int gfe_edge_support(gfe_engine *e, const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
+                     uint32_t *weights) {
+    if (!e || (E && !weights)) return GFE_ERR_ARG;
+    TRY(ensure_dev(e, e->d_edge_counts, std::max<size_t>((size_t)E * 2, 1)));
+    TRY(gfe_edge_traversals_device(e, edge_from, edge_to, E, e->d_edge_counts.ptr, nullptr));
+    std::vector<uint32_t> counts((size_t)E * 2);
+    if (E) {
+        CUDA_TRY(e, cudaMemcpyAsync(counts.data(), e->d_edge_counts.ptr, counts.size() * 4,
+                                    cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    }
+    if (e->timing) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
+    e->d2h_bytes += counts.size() * 4;
+    return gfe_edge_weights_from_counts(edge_from, edge_to, E, counts.data(), weights);
+}
+
+}  // extern "C"

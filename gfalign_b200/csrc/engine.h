@@ -1,0 +1,79 @@
+// gfalign_b200/csrc/engine.h — engine state shared by engine.cu (C ABI) and search.cpp (driver).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+
+#include "../../include/gfalign_b200.h"
+#include "kernels.cuh"
+
+template <typename T>
+struct DevBuf {
+    T *ptr = nullptr;
+    size_t cap = 0;   // elements
+};
+template <typename T>
+struct PinBuf {
+    T *ptr = nullptr;
+    size_t cap = 0;
+};
+
+struct gfe_engine {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timing = false;
+    float last_kernel_ms = 0.f;
+    char error[512] = "";
+
+    // alignment table (owned copies, or adopted device pointers)
+    DevBuf<uint32_t> own_off, own_steps;
+    const uint32_t *d_off = nullptr, *d_steps = nullptr;
+    uint64_t A = 0, S = 0;
+    uint32_t n_nodes = 0, max_m = 0;
+    bool have_alignments = false;
+
+    // universe-local view
+    std::vector<uint32_t> node2local;
+    DevBuf<uint32_t> d_node2local;
+    DevBuf<uint16_t> d_lstep;
+    uint32_t L = 0, tab_stride = 8;
+    bool have_universe = false;
+
+    // candidate-path staging and results
+    PinBuf<unsigned char> h_stage;
+    DevBuf<unsigned char> d_stage;
+    DevBuf<uint16_t> d_ptab, d_plocal;
+    DevBuf<uint32_t> d_counts, d_err;
+    PinBuf<uint32_t> h_counts;
+    uint32_t h_wc_storage[4] = {0, 0, 0, 0};
+    uint32_t *h_wc = h_wc_storage;
+
+    // exact-DP worklists
+    DevBuf<uint2> d_work;
+    DevBuf<uint32_t> d_work_count, d_pair_work;
+    size_t work_cap = 1u << 20;
+
+    // evalPath outputs
+    DevBuf<int32_t> d_tfw, d_trc;
+
+    // edge support
+    DevBuf<uint32_t> d_row_off, d_edge_counts;
+    DevBuf<uint2> d_row_ent;
+
+    // counters
+    uint64_t kernel_launches = 0, exact_pairs = 0, h2d_bytes = 0, d2h_bytes = 0;
+
+    void free_all() {
+        auto fd = [](void *p) { if (p) cudaFree(p); };
+        auto fh = [](void *p) { if (p) cudaFreeHost(p); };
+        fd(own_off.ptr); fd(own_steps.ptr); fd(d_node2local.ptr); fd(d_lstep.ptr);
+        fd(d_stage.ptr); fd(d_ptab.ptr); fd(d_plocal.ptr); fd(d_counts.ptr); fd(d_err.ptr);
+        fd(d_work.ptr); fd(d_work_count.ptr); fd(d_pair_work.ptr); fd(d_tfw.ptr); fd(d_trc.ptr);
+        fd(d_row_off.ptr); fd(d_edge_counts.ptr); fd(d_row_ent.ptr);
+        fh(h_stage.ptr); fh(h_counts.ptr);
+    }
+};

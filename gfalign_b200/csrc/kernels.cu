@@ -1,0 +1,660 @@
+// gfalign_b200/csrc/kernels.cu — hand-written sm_100a kernels (integer, HBM/L2/shared-memory bound;
+// no tensor cores: the path has no dense contraction).  See kernels.cuh for the data layout and
+// DESIGN.md for the per-kernel roofline.
+#include "kernels.cuh"
+
+namespace gfe {
+
+namespace {
+
+constexpr unsigned kFull = 0xFFFFFFFFu;
+enum Verdict : int { kNone = 0, kBad = 1, kGood = 2, kExact = 3 };
+
+__device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }
+
+// ------------------------------------------------------------------------------------------------
+// K0a: global-id steps -> universe-local 16-bit steps.  One pass, 16 B in / 8 B out per thread
+// iteration; the node->local map (4 B/node) is gathered through L2.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock)
+localize_steps_kernel(const uint32_t *__restrict__ steps, const uint32_t *__restrict__ map,
+                      uint16_t *__restrict__ out, uint64_t S) {
+    const uint64_t nvec = S >> 2;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t v = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += stride) {
+        uint4 s = __ldg(reinterpret_cast<const uint4 *>(steps) + v);
+        uint32_t a = (__ldg(map + (s.x >> 1)) << 1) | (s.x & 1u);
+        uint32_t b = (__ldg(map + (s.y >> 1)) << 1) | (s.y & 1u);
+        uint32_t c = (__ldg(map + (s.z >> 1)) << 1) | (s.z & 1u);
+        uint32_t d = (__ldg(map + (s.w >> 1)) << 1) | (s.w & 1u);
+        uint2 o = make_uint2(a | (b << 16), c | (d << 16));
+        reinterpret_cast<uint2 *>(out)[v] = o;
+    }
+    const uint64_t tail = nvec << 2;
+    uint64_t t = tail + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < S) {
+        uint32_t s = steps[t];
+        out[t] = (uint16_t)((map[s >> 1] << 1) | (s & 1u));
+    }
+}
+
+// K0b: candidate paths (global ids) -> local ids; a node outside the universe raises *err.
+__global__ void localize_paths_kernel(const uint32_t *__restrict__ psteps,
+                                      const uint32_t *__restrict__ map, uint32_t n_nodes,
+                                      uint32_t L, uint16_t *__restrict__ out, uint32_t total,
+                                      uint32_t *err) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    uint32_t s = psteps[i], node = s >> 1;
+    uint32_t l = node < n_nodes ? map[node] : L;
+    if (l >= L) { atomicOr(err, 1u); l = L; }
+    out[i] = (uint16_t)((l << 1) | (s & 1u));
+}
+
+// ------------------------------------------------------------------------------------------------
+// K0c: node -> first-position table of each candidate path.  One CTA per path; the 32-bit working
+// row lives in shared memory ((L+1)*4 B <= 128 KB).  atomicMin on (pos<<1|minus) keeps the first
+// visit, a second pass flags nodes visited more than once (NodeTable counts > 1, reference
+// include/nodetable.h:4-7).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock)
+build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restrict__ pstep,
+                    uint32_t L, uint32_t stride, uint16_t *__restrict__ ptab) {
+    extern __shared__ uint32_t row[];
+    const uint32_t p = blockIdx.x;
+    const uint32_t o0 = poff[p], n = poff[p + 1] - o0;
+    const uint16_t *s = pstep + o0;
+    for (uint32_t i = threadIdx.x; i <= L; i += blockDim.x) row[i] = 0xFFFFFFFFu;
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        uint32_t st = s[i], node = st >> 1;
+        if (node < L) atomicMin(&row[node], (i << 1) | (st & 1u));
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        uint32_t node = s[i] >> 1;
+        if (node < L && ((row[node] & 0x7FFFFFFFu) >> 1) != i) atomicOr(&row[node], 0x80000000u);
+    }
+    __syncthreads();
+    uint16_t *dst = ptab + (size_t)p * stride;
+    for (uint32_t i = threadIdx.x; i < stride; i += blockDim.x) {
+        uint32_t v = i <= L ? row[i] : 0xFFFFFFFFu;
+        uint32_t e = 0;
+        if (v != 0xFFFFFFFFu)
+            e = ((((v & 0x7FFFFFFFu) >> 1) + 1u) << 2) | ((v & 1u) << 1) | (v >> 31);
+        dst[i] = (uint16_t)e;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Exact traceback score T of one (path A, alignment B) direction, forward-only.
+//
+// The reference fills dp[n+1][m+1] (src/alignments.cpp:499-509) and then walks back from (n,m)
+// (:511-554).  The walk is deterministic given dp, so its accumulated score can be carried
+// FORWARD with the DP row:  F[i][j]  = score of the walk from (i,j) once a B step was consumed
+// (SBlen > 0), F0[i][j] = score of the walk from (i,j) while SBlen == 0 (up-moves free).
+//   diag (dp[i][j] == dp[i-1][j-1]+S):   F = F0 = F[i-1][j-1] + S
+//   up   (dp[i-1][j] >= dp[i][j-1]):     F = F[i-1][j] - 1,  F0 = F0[i-1][j]
+//   left:                                F = F0 = F[i][j-1] - 1
+// borders F = F0 = 0 (ii == 0 / jj == 0 moves are free, :517-524); T = F0[n][m].
+// Row 0 of dp is -j for j <= n and 0 beyond (loop bound n at :500), column 0 is 0.
+// One row of (dp, F, F0) lives in registers: MCAP+1 values each, fully unrolled.
+// ------------------------------------------------------------------------------------------------
+template <int MCAP>
+__device__ __forceinline__ int exact_T_regs(const uint16_t *__restrict__ A, int n,
+                                            const uint32_t (&B)[MCAP], int m) {
+    int dp[MCAP + 1], F[MCAP + 1], F0[MCAP + 1];
+#pragma unroll
+    for (int j = 0; j <= MCAP; ++j) {
+        dp[j] = (j <= n) ? -j : 0;
+        F[j] = 0;
+        F0[j] = 0;
+    }
+    int res = 0;
+    for (int i = 1; i <= n; ++i) {
+        const uint32_t a = A[i - 1];
+        int diag_dp = 0, diag_F = 0;     // column 0 of row i-1
+        int left_dp = 0, left_F = 0;     // column 0 of row i
+#pragma unroll
+        for (int j = 1; j <= MCAP; ++j) {
+            if (j > m) break;
+            const int S = (a == B[j - 1]) ? 0 : -1;
+            const int up_dp = dp[j], up_F = F[j], up_F0 = F0[j];
+            const int d = diag_dp + S;
+            const int u = up_dp + (j < m ? -1 : 0);
+            const int l = left_dp - 1;
+            const int v = imax(d, imax(u, l));
+            int nF, nF0;
+            if (v == d) {
+                nF = diag_F + S;
+                nF0 = nF;
+            } else if (up_dp >= left_dp) {
+                nF = up_F - 1;
+                nF0 = up_F0;
+            } else {
+                nF = left_F - 1;
+                nF0 = nF;
+            }
+            diag_dp = up_dp;
+            diag_F = up_F;
+            dp[j] = v;
+            F[j] = nF;
+            F0[j] = nF0;
+            left_dp = v;
+            left_F = nF;
+            if (j == m) res = nF0;
+        }
+    }
+    return res;   // m == 0: 0 (the walk only consumes A, free)
+}
+
+// Load an alignment (local ids) into registers, forward and reverse-complemented
+// (Path::reverseComplement, reference include/alignments.h:64-70).
+template <int MCAP>
+__device__ __forceinline__ void load_fw_rc(const uint16_t *__restrict__ b, int m,
+                                           uint32_t (&Bf)[MCAP], uint32_t (&Br)[MCAP]) {
+#pragma unroll
+    for (int j = 0; j < MCAP; ++j) {
+        Bf[j] = (j < m) ? (uint32_t)b[j] : 0xFFFFFFFFu;
+        Br[j] = (j < m) ? ((uint32_t)b[m - 1 - j] ^ 1u) : 0xFFFFFFFFu;
+    }
+}
+
+template <int MCAP>
+__device__ __noinline__ void exact_both_regs(const uint16_t *__restrict__ A, int n,
+                                             const uint16_t *__restrict__ b, int m, bool need_both,
+                                             int *tf, int *tr) {
+    uint32_t Bf[MCAP], Br[MCAP];
+    load_fw_rc<MCAP>(b, m, Bf, Br);
+    int f = exact_T_regs<MCAP>(A, n, Bf, m);
+    int r = -1;
+    if (need_both || f != 0) r = exact_T_regs<MCAP>(A, n, Br, m);
+    *tf = f;
+    *tr = r;
+}
+
+__device__ __forceinline__ void exact_both(const uint16_t *__restrict__ A, int n,
+                                           const uint16_t *__restrict__ b, int m, bool need_both,
+                                           int *tf, int *tr) {
+    if (m <= 8) exact_both_regs<8>(A, n, b, m, need_both, tf, tr);
+    else exact_both_regs<kExactRegSteps>(A, n, b, m, need_both, tf, tr);
+}
+
+// Exact T for alignments longer than kExactRegSteps: one warp per direction, anti-diagonal
+// wavefront.  Diagonal d holds the cells (i = d - j, j); three diagonals of dp and F and two of
+// F0 live in shared memory (8 arrays of m+1 ints, indexed by j).  Border cells (i == 0 or
+// j == 0) are produced on the fly, so the loop starts at d = 0 with nothing to initialise.
+__device__ int warp_exact_T(const uint16_t *__restrict__ A, int n, const uint16_t *__restrict__ b,
+                            int m, bool rc, int *scratch) {
+    const int lane = threadIdx.x & 31;
+    const int w = m + 1;
+    int *dpA = scratch, *dpB = scratch + w, *dpC = scratch + 2 * w;          // d-2, d-1, d
+    int *fA = scratch + 3 * w, *fB = scratch + 4 * w, *fC = scratch + 5 * w;  // F: d-2, d-1, d
+    int *zB = scratch + 6 * w, *zC = scratch + 7 * w;                         // F0: d-1, d
+    int result = 0;
+    for (int d = 0; d <= n + m; ++d) {
+        const int jlo = d > n ? d - n : 0;
+        const int jhi = d < m ? d : m;
+        for (int j = jlo + lane; j <= jhi; j += 32) {
+            const int i = d - j;
+            int v, f, z;
+            if (i == 0) {
+                v = (j <= n) ? -j : 0;   // row 0 is written for columns 0..n only (:500)
+                f = 0;
+                z = 0;
+            } else if (j == 0) {
+                v = 0;
+                f = 0;
+                z = 0;
+            } else {
+                const uint32_t bj = rc ? ((uint32_t)b[m - j] ^ 1u) : (uint32_t)b[j - 1];
+                const int S = ((uint32_t)A[i - 1] == bj) ? 0 : -1;
+                const int diag_dp = dpA[j - 1], diag_F = fA[j - 1];
+                const int up_dp = dpB[j], up_F = fB[j], up_Z = zB[j];
+                const int left_dp = dpB[j - 1], left_F = fB[j - 1];
+                const int dd = diag_dp + S, u = up_dp + (j < m ? -1 : 0), l = left_dp - 1;
+                v = imax(dd, imax(u, l));
+                if (v == dd) { f = diag_F + S; z = f; }
+                else if (up_dp >= left_dp) { f = up_F - 1; z = up_Z; }
+                else { f = left_F - 1; z = f; }
+            }
+            dpC[j] = v; fC[j] = f; zC[j] = z;
+            if (i == n && j == m) result = z;   // last diagonal: its single cell is lane 0's
+        }
+        __syncwarp();
+        int *t = dpA; dpA = dpB; dpB = dpC; dpC = t;
+        t = fA; fA = fB; fB = fC; fC = t;
+        t = zB; zB = zC; zC = t;
+    }
+    return __shfl_sync(kFull, result, 0);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: score_paths — evaluatePath(filter) for a chunk of candidate paths x a stream of alignments.
+// grid = (alignment-tile workers, path chunks).  The chunk's node->position tables sit in shared
+// memory; one thread owns one alignment (steps in registers when m <= kRegSteps) and tests it
+// against every table of the chunk: one shared-memory lookup per step answers the id filter, the
+// forward occurrence and the reverse-complement occurrence at once.  Per path the warp's verdicts
+// are combined with two ballots and one shared-memory atomic per warp; the CTA flushes its
+// chunk x {bad, good} counters with global atomics at the end.
+// Verdict rule (proved + fuzzed against the reference, SURVEY.md Appendix A.3, tests/):
+//   filtered out -> nothing;  m > n -> good;  B or rc(B) occurs contiguously -> good;
+//   otherwise bad unless B touches the path's first node or a node visited twice -> exact DP.
+// ------------------------------------------------------------------------------------------------
+template <bool kFilter, bool kRegs>
+__device__ __forceinline__ int test_alignment(const uint16_t *__restrict__ tab, int n,
+                                              const uint32_t (&B)[kRegSteps],
+                                              const uint16_t *__restrict__ bglob, int m) {
+    bool pass = true, fw = true, rc = true;
+    uint32_t special = 0;    // bit0: node visited twice, bit1: node of path[0]
+    int p0 = 0;
+    if (kRegs) {
+#pragma unroll
+        for (int j = 0; j < kRegSteps; ++j) {
+            if (j >= m) break;
+            const uint32_t st = B[j];
+            const uint32_t e = tab[st >> 1];
+            if (e == kTabAbsent) {
+                pass = false;
+                if (kFilter) break;
+                fw = rc = false;
+                continue;
+            }
+            const int pos = (int)(e >> 2) - 1;
+            const uint32_t o = (e >> 1) & 1u, bo = st & 1u;
+            special |= (e & 1u) | ((pos == 0) ? 2u : 0u);
+            if (j == 0) p0 = pos;
+            fw = fw && (pos == p0 + j) && (o == bo);
+            rc = rc && (pos == p0 - j) && (o != bo);
+        }
+    } else {
+        for (int j = 0; j < m; ++j) {
+            const uint32_t st = bglob[j];
+            const uint32_t e = tab[st >> 1];
+            if (e == kTabAbsent) {
+                pass = false;
+                if (kFilter) break;
+                fw = rc = false;
+                continue;
+            }
+            const int pos = (int)(e >> 2) - 1;
+            const uint32_t o = (e >> 1) & 1u, bo = st & 1u;
+            special |= (e & 1u) | ((pos == 0) ? 2u : 0u);
+            if (j == 0) p0 = pos;
+            fw = fw && (pos == p0 + j) && (o == bo);
+            rc = rc && (pos == p0 - j) && (o != bo);
+        }
+    }
+    if (kFilter && !pass) return kNone;
+    if (m > n) return kGood;
+    if (fw || rc) return kGood;
+    if (special) return kExact;
+    return kBad;
+}
+
+template <bool kFilter>
+__global__ void __launch_bounds__(kBlock)
+score_paths_kernel(const ScoreArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    uint16_t *s_tab = reinterpret_cast<uint16_t *>(smem);
+    uint32_t *s_cnt = reinterpret_cast<uint32_t *>(smem + (size_t)a.chunk * a.tab_stride * 2);
+    uint32_t *s_n = s_cnt + 2 * a.chunk;
+
+    const uint32_t p_base = blockIdx.y * a.chunk;
+    const uint32_t pc = min(a.chunk, a.P - p_base);
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(a.ptab + (size_t)p_base * a.tab_stride);
+        uint4 *dst = reinterpret_cast<uint4 *>(s_tab);
+        const uint32_t nvec = pc * (a.tab_stride >> 3);
+        for (uint32_t i = threadIdx.x; i < nvec; i += blockDim.x) dst[i] = __ldg(src + i);
+        for (uint32_t i = threadIdx.x; i < 2 * pc; i += blockDim.x) s_cnt[i] = 0;
+        for (uint32_t i = threadIdx.x; i < pc; i += blockDim.x)
+            s_n[i] = a.poff[p_base + i + 1] - a.poff[p_base + i];
+    }
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    const uint64_t n_tiles = (a.A + kBlock - 1) / kBlock;
+    for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint64_t ai = tile * kBlock + threadIdx.x;
+        const bool valid = ai < a.A;
+        uint32_t o0 = 0, o1 = 0;
+        if (valid) {
+            o0 = __ldg(a.off + ai);
+            o1 = __ldg(a.off + ai + 1);
+        }
+        const int m = (int)(o1 - o0);
+        const uint16_t *bglob = a.lstep + o0;
+        uint32_t B[kRegSteps];
+        const bool regs = m <= kRegSteps;
+        if (regs) {
+#pragma unroll
+            for (int j = 0; j < kRegSteps; ++j) B[j] = (j < m) ? (uint32_t)__ldg(bglob + j) : 0u;
+        }
+        for (uint32_t p = 0; p < pc; ++p) {
+            const uint16_t *tab = s_tab + (size_t)p * a.tab_stride;
+            const int n = (int)s_n[p];
+            int v = kNone;
+            if (valid) {
+                v = regs ? test_alignment<kFilter, true>(tab, n, B, bglob, m)
+                         : test_alignment<kFilter, false>(tab, n, B, bglob, m);
+            }
+            const unsigned gm = __ballot_sync(kFull, v == kGood);
+            const unsigned bm = __ballot_sync(kFull, v == kBad);
+            if (lane == 0) {
+                if (bm) atomicAdd(&s_cnt[2 * p], (uint32_t)__popc(bm));
+                if (gm) atomicAdd(&s_cnt[2 * p + 1], (uint32_t)__popc(gm));
+            }
+            if (v == kExact) {
+                const uint32_t idx = atomicAdd(a.work_count, 1u);
+                if (idx < a.work_cap) a.work[idx] = make_uint2(p_base + p, (uint32_t)ai);
+                else atomicOr(a.work_count + 1, 1u);
+            }
+        }
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < 2 * pc; i += blockDim.x)
+        if (s_cnt[i]) atomicAdd(&a.counts[2 * (size_t)p_base + i], s_cnt[i]);
+}
+
+// K1b: exact verdict for the worklist of ambiguous (path, alignment) pairs.
+__global__ void __launch_bounds__(128)
+exact_worklist_kernel(const ScoreArgs a) {
+    const uint32_t cnt = min(a.work_count[0], a.work_cap);
+    for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < cnt;
+         idx += gridDim.x * blockDim.x) {
+        const uint2 w = a.work[idx];
+        const uint32_t o0 = a.off[w.y];
+        const int m = (int)(a.off[w.y + 1] - o0);
+        if (m > kExactRegSteps) continue;   // long alignments: exact_worklist_long_kernel
+        const uint32_t po = a.poff[w.x];
+        const int n = (int)(a.poff[w.x + 1] - po);
+        int tf, tr;
+        exact_both(a.pstep + po, n, a.lstep + o0, m, false, &tf, &tr);
+        const bool good = (tf == 0) || (tr == 0);
+        atomicAdd(&a.counts[2 * (size_t)w.x + (good ? 1 : 0)], 1u);
+    }
+}
+
+__global__ void __launch_bounds__(32)
+exact_worklist_long_kernel(const ScoreArgs a) {
+    extern __shared__ int scratch[];
+    const uint32_t cnt = min(a.work_count[0], a.work_cap);
+    for (uint32_t idx = blockIdx.x; idx < cnt; idx += gridDim.x) {
+        const uint2 w = a.work[idx];
+        const uint32_t o0 = a.off[w.y];
+        const int m = (int)(a.off[w.y + 1] - o0);
+        if (m <= kExactRegSteps) continue;
+        const uint32_t po = a.poff[w.x];
+        const int n = (int)(a.poff[w.x + 1] - po);
+        int tf = warp_exact_T(a.pstep + po, n, a.lstep + o0, m, false, scratch);
+        __syncwarp();
+        int tr = -1;
+        if (tf != 0) tr = warp_exact_T(a.pstep + po, n, a.lstep + o0, m, true, scratch);
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) {
+            const bool good = (tf == 0) || (tr == 0);
+            atomicAdd(&a.counts[2 * (size_t)w.x + (good ? 1 : 0)], 1u);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: evalPath — T_fw / T_rc of ONE path against every alignment (reference src/eval.cpp:92-93).
+// Pass 1 (pair_classify) streams the table: an alignment none of whose nodes lies on the path has
+// an all-mismatch DP matrix, for which the walk is m diagonal moves: T = -m (m <= n); m > n gives
+// T = 0; m == 0 gives T = 0.  Everything else is queued and scored exactly by pass 2 (pair_exact),
+// dense, one thread per alignment with the path in shared memory.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlock)
+pair_classify_kernel(const PairArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    uint16_t *s_tab = reinterpret_cast<uint16_t *>(smem);
+    __shared__ uint32_t s_cnt[2];
+    for (uint32_t i = threadIdx.x; i < a.tab_entries; i += blockDim.x) s_tab[i] = a.ptab[i];
+    if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int n = (int)a.n;
+    const uint64_t n_tiles = (a.A + kBlock - 1) / kBlock;
+    for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint64_t ai = tile * kBlock + threadIdx.x;
+        const bool valid = ai < a.A;
+        int v = kNone;
+        if (valid) {
+            const uint32_t o0 = __ldg(a.off + ai);
+            const int m = (int)(__ldg(a.off + ai + 1) - o0);
+            const uint16_t *b = a.lstep + o0;
+            bool touch = false, pass = true;
+            for (int j = 0; j < m; ++j) {
+                const uint32_t e = s_tab[__ldg(b + j) >> 1];
+                if (e == kTabAbsent) pass = false; else touch = true;
+            }
+            int t = 0;
+            bool queued = false;
+            if (a.filter && !pass) {
+                t = INT32_MIN;
+            } else if (m > n || m == 0) {
+                t = 0; v = kGood;
+            } else if (!touch) {
+                t = -m; v = kBad;
+            } else {
+                queued = true;
+                const uint32_t idx = atomicAdd(a.work_count, 1u);
+                if (idx < a.work_cap) a.work[idx] = (uint32_t)ai;
+                else atomicOr(a.work_count + 1, 1u);
+            }
+            if (!queued) {
+                if (a.t_fw) a.t_fw[ai] = t;
+                if (a.t_rc) a.t_rc[ai] = t;
+            }
+        }
+        const unsigned gm = __ballot_sync(kFull, v == kGood);
+        const unsigned bm = __ballot_sync(kFull, v == kBad);
+        if (lane == 0) {
+            if (bm) atomicAdd(&s_cnt[0], (uint32_t)__popc(bm));
+            if (gm) atomicAdd(&s_cnt[1], (uint32_t)__popc(gm));
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < 2 && s_cnt[threadIdx.x]) atomicAdd(&a.counts[threadIdx.x], s_cnt[threadIdx.x]);
+}
+
+__global__ void __launch_bounds__(128)
+pair_exact_kernel(const PairArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    uint16_t *s_path = reinterpret_cast<uint16_t *>(smem);
+    for (uint32_t i = threadIdx.x; i < a.n; i += blockDim.x) s_path[i] = a.pstep[i];
+    __syncthreads();
+    const uint32_t cnt = min(a.work_count[0], a.work_cap);
+    for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < cnt;
+         idx += gridDim.x * blockDim.x) {
+        const uint32_t ai = a.work[idx];
+        const uint32_t o0 = a.off[ai];
+        const int m = (int)(a.off[ai + 1] - o0);
+        if (m > kExactRegSteps) continue;
+        int tf, tr;
+        exact_both(s_path, (int)a.n, a.lstep + o0, m, true, &tf, &tr);
+        if (a.t_fw) a.t_fw[ai] = tf;
+        if (a.t_rc) a.t_rc[ai] = tr;
+        const int best = tf > tr ? tf : tr;
+        atomicAdd(&a.counts[best < 0 ? 0 : 1], 1u);
+    }
+}
+
+__global__ void __launch_bounds__(32)
+pair_exact_long_kernel(const PairArgs a) {
+    extern __shared__ int scratch[];
+    const uint32_t cnt = min(a.work_count[0], a.work_cap);
+    for (uint32_t idx = blockIdx.x; idx < cnt; idx += gridDim.x) {
+        const uint32_t ai = a.work[idx];
+        const uint32_t o0 = a.off[ai];
+        const int m = (int)(a.off[ai + 1] - o0);
+        if (m <= kExactRegSteps) continue;
+        int tf = warp_exact_T(a.pstep, (int)a.n, a.lstep + o0, m, false, scratch);
+        __syncwarp();
+        int tr = warp_exact_T(a.pstep, (int)a.n, a.lstep + o0, m, true, scratch);
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) {
+            if (a.t_fw) a.t_fw[ai] = tf;
+            if (a.t_rc) a.t_rc[ai] = tr;
+            const int best = tf > tr ? tf : tr;
+            atomicAdd(&a.counts[best < 0 ? 0 : 1], 1u);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: edge_support — scatter-add of every consecutive oriented step pair of every alignment into
+// the counter of the matching adjacency entry (reference src/alignments.cpp:371-396).  Adjacency
+// rows are keyed by the oriented from-step.  When the counter array fits (kSmem) it is privatised
+// in shared memory per CTA and flushed once with global atomics.
+// ------------------------------------------------------------------------------------------------
+template <bool kSmem>
+__global__ void __launch_bounds__(kBlock)
+edge_support_kernel(const EdgeArgs a) {
+    extern __shared__ uint32_t s_counts[];
+    if (kSmem) {
+        for (uint32_t i = threadIdx.x; i < a.n_slots; i += blockDim.x) s_counts[i] = 0;
+        __syncthreads();
+    }
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t ai = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; ai < a.A; ai += stride) {
+        const uint32_t o0 = __ldg(a.off + ai), o1 = __ldg(a.off + ai + 1);
+        if (o1 - o0 < 2) continue;
+        uint32_t x = __ldg(a.steps + o0);
+        for (uint32_t k = o0 + 1; k < o1; ++k) {
+            const uint32_t y = __ldg(a.steps + k);
+            if (x < a.n_steps_space) {
+                const uint32_t r0 = __ldg(a.row_off + x), r1 = __ldg(a.row_off + x + 1);
+                for (uint32_t r = r0; r < r1; ++r) {
+                    const uint2 ent = __ldg(a.row_ent + r);
+                    if (ent.x == y) {
+                        if (kSmem) atomicAdd(&s_counts[ent.y], 1u);
+                        else atomicAdd(&a.counts[ent.y], 1u);
+                        break;
+                    }
+                }
+            }
+            x = y;
+        }
+    }
+    if (kSmem) {
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < a.n_slots; i += blockDim.x)
+            if (s_counts[i]) atomicAdd(&a.counts[i], s_counts[i]);
+    }
+}
+
+constexpr size_t kMaxDynSmem = 200 * 1024;
+constexpr uint32_t kEdgeSmemSlots = 40 * 1024;   // 160 KB of privatised counters
+
+size_t score_smem_bytes(const ScoreArgs &a) {
+    return (size_t)a.chunk * a.tab_stride * 2 + (size_t)a.chunk * 3 * sizeof(uint32_t);
+}
+
+}  // namespace
+
+int configure_kernels() {
+    cudaError_t e;
+    e = cudaFuncSetAttribute(build_tables_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)kMaxDynSmem);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(score_paths_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)kMaxDynSmem);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(score_paths_kernel<false>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(pair_classify_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)kMaxDynSmem);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(edge_support_kernel<true>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+    if (e != cudaSuccess) return (int)e;
+    return 0;
+}
+
+void launch_localize_steps(const uint32_t *steps, const uint32_t *node2local, uint16_t *lstep,
+                           uint64_t S, cudaStream_t st) {
+    if (S == 0) return;
+    uint64_t blocks = ((S >> 2) + kBlock - 1) / kBlock;
+    if (blocks < 1) blocks = 1;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    localize_steps_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(steps, node2local, lstep, S);
+}
+
+void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, uint32_t n_nodes,
+                           uint32_t L, uint16_t *out, uint32_t total, uint32_t *err,
+                           cudaStream_t st) {
+    if (total == 0) return;
+    localize_paths_kernel<<<(total + 255) / 256, 256, 0, st>>>(psteps, node2local, n_nodes, L, out,
+                                                                total, err);
+}
+
+void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
+                         uint32_t tab_stride, uint16_t *ptab, cudaStream_t st) {
+    if (P == 0) return;
+    build_tables_kernel<<<P, kBlock, (size_t)(L + 1) * sizeof(uint32_t), st>>>(poff, pstep, L,
+                                                                                tab_stride, ptab);
+}
+
+void launch_score_paths(const ScoreArgs &a, int sm_count, cudaStream_t st) {
+    if (a.P == 0 || a.A == 0) return;
+    const size_t smem = score_smem_bytes(a);
+    const uint32_t chunks = (a.P + a.chunk - 1) / a.chunk;
+    int per_sm = 1;
+    if (a.filter)
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, score_paths_kernel<true>, kBlock, smem);
+    else
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, score_paths_kernel<false>, kBlock, smem);
+    if (per_sm < 1) per_sm = 1;
+    const uint64_t n_tiles = (a.A + kBlock - 1) / kBlock;
+    // resident CTAs = a multiple of the SM count; split between tile workers (x) and chunks (y)
+    uint64_t gx = ((uint64_t)sm_count * per_sm + chunks - 1) / chunks;
+    if (gx > n_tiles) gx = n_tiles;
+    if (gx < 1) gx = 1;
+    dim3 grid((unsigned)gx, chunks);
+    if (a.filter) score_paths_kernel<true><<<grid, kBlock, smem, st>>>(a);
+    else score_paths_kernel<false><<<grid, kBlock, smem, st>>>(a);
+}
+
+void launch_exact_worklist(const ScoreArgs &a, cudaStream_t st) {
+    exact_worklist_kernel<<<148 * 4, 128, 0, st>>>(a);
+}
+
+void launch_exact_worklist_long(const ScoreArgs &a, uint32_t max_m, cudaStream_t st) {
+    exact_worklist_long_kernel<<<148 * 8, 32, (size_t)(max_m + 1) * 8 * sizeof(int), st>>>(a);
+}
+
+void launch_pair_classify(const PairArgs &a, int sm_count, cudaStream_t st) {
+    if (a.A == 0) return;
+    const uint64_t n_tiles = (a.A + kBlock - 1) / kBlock;
+    uint64_t gx = (uint64_t)sm_count * 8;
+    if (gx > n_tiles) gx = n_tiles;
+    pair_classify_kernel<<<(unsigned)gx, kBlock, (size_t)a.tab_entries * 2, st>>>(a);
+}
+
+void launch_pair_exact(const PairArgs &a, cudaStream_t st) {
+    pair_exact_kernel<<<148 * 4, 128, ((size_t)a.n * 2 + 15) & ~(size_t)15, st>>>(a);
+}
+
+void launch_pair_exact_long(const PairArgs &a, uint32_t max_m, cudaStream_t st) {
+    pair_exact_long_kernel<<<148 * 8, 32, (size_t)(max_m + 1) * 8 * sizeof(int), st>>>(a);
+}
+
+void launch_edge_support(const EdgeArgs &a, int sm_count, cudaStream_t st) {
+    if (a.A == 0) return;
+    uint64_t blocks = (a.A + kBlock - 1) / kBlock;
+    if (a.n_slots <= kEdgeSmemSlots) {
+        const uint64_t cap = (uint64_t)sm_count * 2;
+        if (blocks > cap) blocks = cap;
+        edge_support_kernel<true><<<(unsigned)blocks, kBlock, (size_t)a.n_slots * 4, st>>>(a);
+    } else {
+        const uint64_t cap = (uint64_t)sm_count * 8;
+        if (blocks > cap) blocks = cap;
+        edge_support_kernel<false><<<(unsigned)blocks, kBlock, 0, st>>>(a);
+    }
+}
+
+}  // namespace gfe

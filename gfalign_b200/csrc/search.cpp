@@ -1,0 +1,435 @@
+// gfalign_b200/csrc/search.cpp — gfe_search: the best-first path search of `gfalign search`
+// (reference dijkstra(), src/eval.cpp:110-193) replayed on the host with every evaluatePath call
+// (src/eval.cpp:162) answered by the CUDA kernels.
+//
+// What must match the reference exactly, and how it is kept:
+//   * extraction order — the reference's priority queue is a Fibonacci heap whose tie-breaks are
+//     structural (gfalibs/include/fibonacci-heap.h:55-126, :219-271).  OrderHeap below performs
+//     the same sequence of structural operations on index-linked nodes.
+//   * successor admission — orientation continuity (src/eval.cpp:137) and the remaining-visit
+//     budget of the EXTRACTED path's own NodeTable (:142-143); budgets drop only for
+//     non-destination pushes (:165-167); the source placed at start is not a push.
+//   * key — alt = bad - good - uniques (:163); "better" rule and row emission (:176-183);
+//     hamiltonian flag (include/nodetable.h:56-67).
+// What is free: evaluatePath(path) is a pure function of the path, so the driver may score paths
+// it has not been asked about yet.  On a miss it sends the children of the extracted path plus a
+// breadth-first subtree below them in ONE kernel batch and caches the counts on the path tree.
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <vector>
+
+#include "../../include/gfalign_b200.h"
+
+namespace {
+
+// ---- Fibonacci heap with the reference's structural behaviour ----------------------------------
+class OrderHeap {
+    struct Node {
+        int key, degree;
+        int parent, child, left, right;
+        uint32_t value;
+    };
+    std::vector<Node> N;
+    std::vector<int> freelist, table;
+    int min_ = -1;
+    uint32_t num_ = 0;
+
+    int alloc() {
+        if (!freelist.empty()) {
+            int i = freelist.back();
+            freelist.pop_back();
+            return i;
+        }
+        N.push_back(Node());
+        return (int)N.size() - 1;
+    }
+    // fibonacci-heap.h:145-165 (_existingToRoot): left of the current minimum, strict-less update
+    void to_root(int x) {
+        N[x].parent = -1;
+        if (min_ != -1) {
+            const int ml = N[min_].left;
+            N[min_].left = x;
+            N[x].right = min_;
+            N[x].left = ml;
+            N[ml].right = x;
+            if (N[min_].key > N[x].key) min_ = x;
+        } else {
+            min_ = x;
+            N[x].left = N[x].right = x;
+        }
+    }
+    // :166-180 (_removeNodeFromRoot)
+    void unlink(int x) {
+        if (N[x].right != x) {
+            N[N[x].right].left = N[x].left;
+            N[N[x].left].right = N[x].right;
+        }
+        const int p = N[x].parent;
+        if (p != -1) {
+            N[p].child = (N[p].degree == 1) ? -1 : N[x].right;
+            N[p].degree--;
+        }
+    }
+    // :184-201 (_addChild): appended left of the first child
+    void add_child(int parent, int c) {
+        if (N[parent].degree == 0) {
+            N[parent].child = c;
+            N[c].left = N[c].right = c;
+        } else {
+            const int first = N[parent].child, last = N[first].left;
+            N[first].left = c;
+            N[c].right = first;
+            N[c].left = last;
+            N[last].right = c;
+        }
+        N[c].parent = parent;
+        N[parent].degree++;
+    }
+    // :219-271 (_consolidate)
+    void consolidate() {
+        if (num_ <= 1) return;
+        table.clear();
+        int roots = 0, it = min_;
+        do {
+            ++roots;
+            it = N[it].right;
+        } while (it != min_);
+        int curr = min_;
+        for (int c = 0; c < roots; ++c) {
+            int x = curr;
+            curr = N[curr].right;
+            int deg = N[x].degree;
+            for (;;) {
+                while (deg >= (int)table.size()) table.push_back(-1);
+                if (table[deg] == -1) {
+                    table[deg] = x;
+                    break;
+                }
+                int y = table[deg];
+                if (N[x].key > N[y].key) std::swap(x, y);   // ties: the root in hand stays parent
+                if (y == x) break;
+                unlink(y);
+                add_child(x, y);
+                table[deg] = -1;
+                ++deg;
+            }
+        }
+        min_ = -1;
+        for (size_t i = 0; i < table.size(); ++i)
+            if (table[i] != -1) to_root(table[i]);
+    }
+
+public:
+    uint32_t size() const { return num_; }
+    // :55-86
+    void insert(uint32_t value, int key) {
+        const int x = alloc();
+        N[x].key = key;
+        N[x].degree = 0;
+        N[x].parent = N[x].child = -1;
+        N[x].left = N[x].right = x;
+        N[x].value = value;
+        if (min_ != -1) {
+            const int ml = N[min_].left;
+            N[min_].left = x;
+            N[x].right = min_;
+            N[x].left = ml;
+            N[ml].right = x;
+        }
+        if (min_ == -1 || N[min_].key > key) min_ = x;
+        ++num_;
+    }
+    // :87-126
+    uint32_t extract_min() {
+        const int m = min_;
+        const int deg = N[m].degree;
+        int c = N[m].child;
+        for (int i = 0; i < deg; ++i) {
+            const int r = c;
+            c = N[c].right;
+            to_root(r);
+        }
+        unlink(m);
+        --num_;
+        if (num_ == 0) {
+            min_ = -1;
+        } else {
+            min_ = N[m].right;
+            const int ml = N[m].left;
+            N[min_].left = ml;
+            N[ml].right = min_;
+            consolidate();
+        }
+        const uint32_t v = N[m].value;
+        freelist.push_back(m);
+        return v;
+    }
+};
+
+constexpr uint32_t kNoParent = 0xFFFFFFFFu;
+constexpr uint32_t kHeapCap = 10000000u;   // fibonacci-heap.h:27; past it the reference misbehaves
+
+struct PathNode {
+    uint32_t parent;
+    uint32_t step;         // oriented step (root: node<<1, orientation decided by the first edge)
+    uint32_t depth;        // number of steps of the path ending here
+    uint32_t uniques;
+    uint32_t bad = 0, good = 0;
+    uint32_t child_begin = 0, child_count = 0;
+    uint8_t root_or = 0;   // depth-2 nodes: orientation the source is left in (src/eval.cpp:148-149)
+    bool scored = false, expanded = false;
+};
+
+struct Driver {
+    gfe_engine *eng;
+    const gfe_graph *g;
+    const gfe_search_params *prm;
+    std::vector<PathNode> T;
+    std::vector<uint32_t> budget;     // initial NodeTable counts by node (0 = no record)
+    std::vector<uint32_t> occ;        // scratch: visits of each node along the current path
+    std::vector<uint32_t> base_path;  // materialised path of the node being expanded
+    std::vector<uint32_t> suffix;
+    // batch
+    std::vector<uint32_t> b_nodes, b_off, b_steps, b_counts;
+    gfe_search_stats st{};
+
+    // path of node x into `out` (root orientation resolved)
+    void materialise(uint32_t x, std::vector<uint32_t> &out) {
+        out.resize(T[x].depth);
+        uint32_t i = T[x].depth, cur = x, second = kNoParent;
+        while (cur != kNoParent) {
+            out[--i] = T[cur].step;
+            if (T[cur].depth == 2) second = cur;
+            cur = T[cur].parent;
+        }
+        if (second != kNoParent) out[0] = (out[0] & ~1u) | T[second].root_or;
+    }
+
+    // children of x per src/eval.cpp:136-151; `path` is x's materialised path and occ[] its visits
+    void expand(uint32_t x, const std::vector<uint32_t> &path) {
+        PathNode &nx = T[x];
+        nx.expanded = true;
+        const uint32_t begin = (uint32_t)T.size();
+        const uint32_t last = path.back(), node = last >> 1;
+        const bool is_root = path.size() == 1;
+        const uint32_t root_node = path[0] >> 1;
+        uint32_t count = 0;
+        for (uint32_t k = g->adj_offsets[node]; k < g->adj_offsets[node + 1]; ++k) {
+            if (!is_root && (last & 1u) != g->adj_or0[k]) continue;
+            const uint32_t v = g->adj_target[k];
+            const uint32_t pushes = occ[v] - (v == root_node ? 1u : 0u);
+            if (budget[v] <= pushes) continue;   // no record, or no visits left
+            PathNode c;
+            c.parent = x;
+            c.step = (v << 1) | g->adj_or1[k];
+            c.depth = T[x].depth + 1;
+            c.uniques = T[x].uniques + (occ[v] == 0 ? 1u : 0u);
+            c.root_or = g->adj_or0[k];
+            T.push_back(c);
+            ++count;
+        }
+        T[x].child_begin = begin;
+        T[x].child_count = count;
+    }
+
+    void add_to_batch(uint32_t node_id, const std::vector<uint32_t> &prefix,
+                      const std::vector<uint32_t> &suf) {
+        b_nodes.push_back(node_id);
+        b_steps.insert(b_steps.end(), prefix.begin(), prefix.end());
+        b_steps.insert(b_steps.end(), suf.begin(), suf.end());
+        b_off.push_back((uint32_t)b_steps.size());
+    }
+
+    // Make sure every child of x carries its (bad, good); speculate below them while at it.
+    int score_children(uint32_t x) {
+        materialise(x, base_path);
+        for (uint32_t s : base_path) occ[s >> 1]++;
+        if (!T[x].expanded) expand(x, base_path);
+        bool missing = false;
+        for (uint32_t c = 0; c < T[x].child_count; ++c)
+            if (!T[T[x].child_begin + c].scored) missing = true;
+        int rc = GFE_OK;
+        if (missing) {
+            b_nodes.clear(); b_steps.clear(); b_off.assign(1, 0);
+            const uint32_t limit = prm->speculate ? prm->speculate : 256u;
+            // breadth-first below x: (tree node, suffix of steps below x)
+            std::deque<uint32_t> frontier;
+            frontier.push_back(x);
+            const uint32_t base_depth = T[x].depth;
+            bool base_fixed = base_path.size() > 1;
+            while (!frontier.empty() && b_nodes.size() < limit) {
+                const uint32_t y = frontier.front();
+                frontier.pop_front();
+                // suffix of y below x
+                suffix.resize(T[y].depth - base_depth);
+                for (uint32_t cur = y, i = (uint32_t)suffix.size(); cur != x; cur = T[cur].parent)
+                    suffix[--i] = T[cur].step;
+                if (y != x) {
+                    if (T[y].depth > GFE_MAX_STEPS - 1) continue;   // children would exceed MAX_N
+                    if (!T[y].expanded) {
+                        for (uint32_t s : suffix) occ[s >> 1]++;
+                        // expand() wants the full path only for its ends and length
+                        std::vector<uint32_t> full(base_path);
+                        full.insert(full.end(), suffix.begin(), suffix.end());
+                        if (!base_fixed) full[0] = (full[0] & ~1u) | T[first_below(y, x)].root_or;
+                        expand(y, full);
+                        for (uint32_t s : suffix) occ[s >> 1]--;
+                    }
+                }
+                for (uint32_t c = 0; c < T[y].child_count; ++c) {
+                    // the children of x itself are required; everything deeper is speculation
+                    if (y != x && b_nodes.size() >= limit) break;
+                    const uint32_t ci = T[y].child_begin + c;
+                    if (!T[ci].scored) {
+                        suffix.push_back(T[ci].step);
+                        if (!base_fixed) {
+                            // x is the root: its orientation comes from the first edge of this child
+                            std::vector<uint32_t> pre(base_path);
+                            const uint32_t fb = first_below(ci, x);
+                            pre[0] = (pre[0] & ~1u) | T[fb].root_or;
+                            add_to_batch(ci, pre, suffix);
+                        } else {
+                            add_to_batch(ci, base_path, suffix);
+                        }
+                        suffix.pop_back();
+                    }
+                    if ((T[ci].step >> 1) != prm->destination) frontier.push_back(ci);
+                }
+            }
+            const uint32_t P = (uint32_t)b_nodes.size();
+            b_counts.resize((size_t)P * 2);
+            auto t0 = std::chrono::steady_clock::now();
+            rc = gfe_score_paths(eng, b_off.data(), b_steps.data(), P, 1, b_counts.data());
+            st.seconds_scoring +=
+                std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            st.kernel_batches++;
+            st.paths_scored += P;
+            if (rc == GFE_OK)
+                for (uint32_t i = 0; i < P; ++i) {
+                    PathNode &n = T[b_nodes[i]];
+                    n.bad = b_counts[2 * i];
+                    n.good = b_counts[2 * i + 1];
+                    n.scored = true;
+                }
+        }
+        for (uint32_t s : base_path) occ[s >> 1]--;
+        return rc;
+    }
+
+    // the ancestor of y (or y itself) that is a direct child of x
+    uint32_t first_below(uint32_t y, uint32_t x) const {
+        uint32_t cur = y;
+        while (T[cur].parent != x) cur = T[cur].parent;
+        return cur;
+    }
+};
+
+}  // namespace
+
+extern "C" int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_params *p,
+                          gfe_row_fn emit, void *user, gfe_search_stats *stats) {
+    if (!e || !g || !p || !g->adj_offsets) return GFE_ERR_ARG;
+    if (p->source >= g->n_nodes || p->destination >= g->n_nodes) return GFE_ERR_ARG;
+    const auto t_begin = std::chrono::steady_clock::now();
+    Driver d;
+    d.eng = e;
+    d.g = g;
+    d.prm = p;
+    d.budget.assign(g->n_nodes, 0);
+    d.occ.assign(g->n_nodes, 0);
+    for (uint32_t i = 0; i < p->n_budget; ++i) {
+        if (p->budget_nodes[i] >= g->n_nodes) return GFE_ERR_ARG;
+        d.budget[p->budget_nodes[i]] = p->budget_counts[i];
+    }
+    // universe = every node that owns a NodeTable record (nodelist + source + destination)
+    {
+        std::vector<uint32_t> uni;
+        for (uint32_t v = 0; v < g->n_nodes; ++v)
+            if (d.budget[v] || v == p->source || v == p->destination) uni.push_back(v);
+        int rc = gfe_set_universe(e, uni.data(), (uint32_t)uni.size());
+        if (rc != GFE_OK) return rc;
+    }
+
+    OrderHeap Q;
+    PathNode root;
+    root.parent = kNoParent;
+    root.step = p->source << 1;
+    root.depth = 1;
+    root.uniques = 1;
+    root.scored = true;
+    d.T.push_back(root);
+    Q.insert(0, 0);
+
+    uint64_t path_counter = 0;
+    uint32_t steps = 0, best_uniques = 0;
+    int32_t best_alt = INT32_MAX;
+    std::vector<uint32_t> row_path;
+    std::vector<uint32_t> visits(g->n_nodes, 0);
+    int rc = GFE_OK;
+
+    while (Q.size() > 0 && steps < p->max_steps) {
+        const uint32_t x = Q.extract_min();
+        if (d.T[x].depth < GFE_MAX_STEPS) {
+            rc = d.score_children(x);
+            if (rc != GFE_OK) break;
+        } else {
+            // the reference's dp[MAX_N][MAX_N] cannot hold a longer path (include/alignments.h:246)
+            d.T[x].expanded = true;
+            d.T[x].child_count = 0;
+        }
+        for (uint32_t c = 0; c < d.T[x].child_count; ++c) {
+            const uint32_t ci = d.T[x].child_begin + c;
+            const PathNode &n = d.T[ci];
+            const int32_t alt = (int32_t)n.bad - (int32_t)n.good - (int32_t)n.uniques;
+            d.st.evaluations++;
+            if ((n.step >> 1) != p->destination) {
+                if (Q.size() >= kHeapCap) {
+                    rc = GFE_ERR_LIMIT;   // reference: "reached limit of the Fibonacci heap"
+                    break;
+                }
+                Q.insert(ci, alt);
+            } else {
+                ++path_counter;
+                d.materialise(ci, row_path);
+                // NodeTable::checkHamiltonian, include/nodetable.h:56-67
+                bool ham = (uint64_t)row_path.size() + 2 == p->node_count;
+                if (ham) {
+                    for (uint32_t s : row_path) visits[s >> 1]++;
+                    for (uint32_t i = 0; i < p->n_budget && ham; ++i)
+                        if (visits[p->budget_nodes[i]] != p->budget_counts[i]) ham = false;
+                    for (uint32_t s : row_path) visits[s >> 1]--;
+                }
+                bool print = false;
+                if (n.uniques >= p->min_nodes &&
+                    (best_uniques < n.uniques || (best_uniques == n.uniques && best_alt > alt))) {
+                    best_alt = alt;
+                    best_uniques = n.uniques;
+                    print = true;
+                }
+                if ((p->return_all_paths || print) && emit) {
+                    gfe_search_row row;
+                    row.path_counter = path_counter;
+                    row.bad = n.bad;
+                    row.good = n.good;
+                    row.alt = alt;
+                    row.size = (uint32_t)row_path.size();
+                    row.uniques = n.uniques;
+                    row.hamiltonian = ham ? 1 : 0;
+                    row.steps = row_path.data();
+                    emit(&row, user);
+                    d.st.rows++;
+                }
+            }
+        }
+        if (rc != GFE_OK) break;
+        ++steps;
+    }
+    d.st.extractions = steps;
+    d.st.reached_max_steps = steps >= p->max_steps ? 1 : 0;
+    d.st.seconds_total =
+        std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
+    if (stats) *stats = d.st;
+    return rc;
+}

@@ -1,0 +1,178 @@
+/*
+ * gfalign_b200.h — C ABI of the B200-native scoring engine for gfalign's hot path.
+ *
+ * The reference (vgl-hub/gfalign) has no plugin/FFI layer: its seam is three free functions,
+ *     evalGFA / evalPath / dijkstra                         (reference include/eval.h:4,6,8)
+ * called from Input::read()                                  (reference src/input-gfalign.cpp:94,110,121)
+ * plus the two pure inner functions they spend their time in,
+ *     evaluatePath(path, graph, alignmentPaths, filter, print)   (reference src/eval.cpp:67-108)
+ *     InAlignments::buildEdgeGraph(hash1, hash2, uId)            (reference src/alignments.cpp:353-403)
+ * Each entry point below names the reference interface it replaces.  INTEGRATION.md shows the
+ * few lines a gfalign maintainer adds to call them.
+ *
+ * Conventions
+ *   - plain C, plain pointers and sizes; the caller owns every host buffer, the engine owns all
+ *     device memory; one engine = one CUDA device; a handle is not re-entrant.
+ *   - every function returns GFE_OK (0) or a negative gfe_status; gfe_last_error() gives the text.
+ *     There is NO CPU fallback: without a usable CUDA device gfe_create fails with GFE_ERR_CUDA.
+ *   - oriented step (uint32): node << 1 | (orientation == '-'), node = dense id in [0, n_nodes).
+ *     This replaces reference `struct Step {int32 id; char orientation;}` (include/alignments.h:11-21).
+ *   - alignments are CSR: offsets[A+1] (offsets[0] == 0) into steps[offsets[A]]; this replaces
+ *     `std::vector<Path> alignmentPaths` (reference src/eval.cpp:121, src/alignments.cpp:451-457).
+ *   - reference limits are kept: a candidate path and an alignment have at most GFE_MAX_STEPS steps
+ *     (reference MAX_N = 1001, include/alignments.h:246: longer inputs are undefined there; here
+ *     they are rejected with GFE_ERR_LIMIT).
+ */
+#ifndef GFALIGN_B200_H
+#define GFALIGN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GFE_MAX_STEPS 1000u        /* MAX_N - 1, reference include/alignments.h:246            */
+#define GFE_MAX_UNIVERSE 32766u    /* nodes a candidate path may draw from (u16 local steps)   */
+#define GFE_SCORE_FILTERED INT32_MIN
+
+typedef enum gfe_status {
+    GFE_OK = 0,
+    GFE_ERR_CUDA = -1,     /* no device / CUDA runtime error (text in gfe_last_error)          */
+    GFE_ERR_ARG = -2,      /* NULL pointer, malformed CSR, step out of range                    */
+    GFE_ERR_LIMIT = -3,    /* path or alignment longer than GFE_MAX_STEPS, universe too large   */
+    GFE_ERR_STATE = -4,    /* call order: alignments / universe not set                         */
+    GFE_ERR_NOMEM = -5
+} gfe_status;
+
+typedef struct gfe_engine gfe_engine;
+
+/* ---- lifetime --------------------------------------------------------------------------------- */
+int gfe_create(int cuda_device, gfe_engine **out);
+void gfe_destroy(gfe_engine *e);
+const char *gfe_last_error(const gfe_engine *e);   /* e may be NULL: error of a failed gfe_create */
+const char *gfe_version(void);
+
+/* ---- alignment table ---------------------------------------------------------------------------
+ * Replaces InAlignments::getPaths() (reference src/alignments.cpp:451-457) as the table every
+ * scoring call reads.  Uploads the CSR to HBM (host pointers), or adopts device pointers the
+ * caller keeps alive (gfe_set_alignments_device; e.g. tensors of a torch.distributed rank).
+ * A == 0 is legal.  n_nodes is the size of the dense node-id space. */
+int gfe_set_alignments(gfe_engine *e, const uint32_t *offsets, const uint32_t *steps, uint64_t A,
+                       uint32_t n_nodes);
+int gfe_set_alignments_device(gfe_engine *e, const uint32_t *d_offsets, const uint32_t *d_steps,
+                              uint64_t A, uint64_t total_steps, uint32_t n_nodes);
+
+/* The universe = the nodes candidate paths may contain (search: nodelist + source + destination,
+ * reference src/eval.cpp:125-128; evalPath: the nodes of the path).  The engine keeps a second,
+ * 16-bit "local" copy of the steps in which every node outside the universe is one shared id that
+ * no path contains, so the scoring kernels index a small shared-memory table.  Must be called
+ * after gfe_set_alignments and before the scoring calls; may be called again. */
+int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe);
+
+/* ---- search scoring: evaluatePath x P -----------------------------------------------------------
+ * Replaces `evaluatePath(newPath, inSequences, alignmentPaths, true)` (reference
+ * src/eval.cpp:162, body :67-108) for P candidate paths at once.  paths are CSR over oriented
+ * steps (global dense ids, all inside the universe).  filter != 0 applies the id-set filter of
+ * src/eval.cpp:81-91.  counts[2p] = badAlignments, counts[2p+1] = goodAlignments of path p —
+ * bit-exact with the reference's Needleman-Wunsch + traceback verdict. */
+int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t *path_steps,
+                    uint32_t P, int filter, uint32_t *counts);
+
+/* Same with every buffer already on the device and no host synchronisation: work is enqueued on
+ * `cuda_stream` (a cudaStream_t; NULL = the engine's stream).  d_counts (P x 2, uint32) is zeroed
+ * and filled by the enqueued work, so a collective (NCCL all-reduce over alignment shards) can
+ * be enqueued right behind it on the same stream. */
+int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
+                           const uint32_t *d_path_steps, uint32_t P, uint32_t total_path_steps,
+                           int filter, uint32_t *d_counts, void *cuda_stream);
+
+/* ---- evalPath scoring: per-alignment traceback scores -------------------------------------------
+ * Replaces the unfiltered `evaluatePath(path, ..., false, true)` of evalPath (reference
+ * src/eval.cpp:238): for ONE path, T_fw and T_rc (alignPaths(0,-1,-1,...).alignmentScore,
+ * src/eval.cpp:92-93) of every alignment, and the bad/good totals of src/eval.cpp:94-98.
+ * The universe is set internally to the path's nodes.  t_fw / t_rc (A entries each) may be NULL
+ * when only the totals are wanted.  With filter != 0 filtered alignments get GFE_SCORE_FILTERED. */
+int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int filter,
+                    int32_t *t_fw, int32_t *t_rc, uint32_t *bad, uint32_t *good);
+
+/* ---- evalGFA: per-edge read support -------------------------------------------------------------
+ * Replaces InAlignments::buildEdgeGraph (reference src/alignments.cpp:353-403) + the per-edge
+ * lookup of evalGFA (src/eval.cpp:42-60).  edges are the graph's L lines in file order as
+ * (from, to) oriented steps; weights[i] is the value the reference writes as `RC:i:<w>`
+ * (including its 2k-1 rule for self-reverse-complement edges). */
+int gfe_edge_support(gfe_engine *e, const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
+                     uint32_t *weights);
+
+/* Device-side half of the above for sharded alignments: raw traversal counters per DIRECTED
+ * adjacency entry, to be summed across shards (all-reduce) before gfe_edge_weights_from_counts.
+ * d_counts has 2*E uint32 slots (slot 2i = events equal to edge i, 2i+1 = events equal to its
+ * reverse complement). */
+int gfe_edge_traversals_device(gfe_engine *e, const uint32_t *edge_from, const uint32_t *edge_to,
+                               uint32_t E, uint32_t *d_counts, void *cuda_stream);
+int gfe_edge_weights_from_counts(const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
+                                 const uint32_t *counts /* 2*E, host */, uint32_t *weights);
+
+/* ---- best-first search driver -------------------------------------------------------------------
+ * Replaces dijkstra() (reference src/eval.cpp:110-193) on packed inputs: the bidirected adjacency
+ * of InSequences::buildEdgeGraph (reference gfalibs/src/gfa.cpp:1076-1097) as CSR over nodes
+ * (adj_offsets[n_nodes+1]; per entry orientation0 / target node / orientation1, in L-line order),
+ * the NodeTable budgets (reference include/nodetable.h), source, destination, and the
+ * -m / --min-nodes / --return-all-paths options.  Rows are delivered in emission order through
+ * `emit`; the search itself (Fibonacci-heap order, `alt` keys, hamiltonian flag) follows the
+ * reference exactly, and every evaluatePath call is answered by the CUDA kernels. */
+typedef struct gfe_search_row {
+    uint64_t path_counter;
+    uint32_t bad, good;
+    int32_t alt;
+    uint32_t size, uniques;
+    int hamiltonian;
+    const uint32_t *steps;      /* `size` oriented steps, valid during the callback only */
+} gfe_search_row;
+typedef void (*gfe_row_fn)(const gfe_search_row *row, void *user);
+
+typedef struct gfe_graph {
+    uint32_t n_nodes;
+    const uint32_t *adj_offsets;   /* n_nodes + 1 */
+    const uint32_t *adj_target;    /* target node of each adjacency entry */
+    const uint8_t *adj_or0;        /* 0 '+', 1 '-' : orientation the source node is left in */
+    const uint8_t *adj_or1;        /* orientation the target node is entered in */
+} gfe_graph;
+
+typedef struct gfe_search_params {
+    uint32_t source, destination;      /* dense node ids */
+    const uint32_t *budget_nodes;      /* NodeTable records: node, count (count >= 1) */
+    const uint32_t *budget_counts;
+    uint32_t n_budget;
+    uint32_t node_count;               /* NodeTable::nodeCount incl. the two add() calls */
+    uint32_t max_steps, min_nodes;
+    int return_all_paths;
+    uint32_t speculate;                /* max candidate paths per kernel batch (0 = default) */
+} gfe_search_params;
+
+typedef struct gfe_search_stats {
+    uint64_t extractions, evaluations, kernel_batches, paths_scored, rows;
+    int reached_max_steps;
+    double seconds_scoring, seconds_total;
+} gfe_search_stats;
+
+int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_params *p, gfe_row_fn emit,
+               void *user, gfe_search_stats *stats);
+
+/* ---- introspection (bench / tests) --------------------------------------------------------------*/
+typedef struct gfe_counters {
+    uint64_t kernel_launches;     /* kernels of this library launched since gfe_create */
+    uint64_t exact_pairs;         /* pairs that needed the exact DP (ambiguous class) */
+    uint64_t h2d_bytes, d2h_bytes;
+} gfe_counters;
+int gfe_get_counters(const gfe_engine *e, gfe_counters *out);
+/* Milliseconds the last scoring / edge-support call spent in its dominant kernel (CUDA events on
+ * the engine's stream); 0 if timing was not enabled with gfe_set_timing(e, 1). */
+int gfe_set_timing(gfe_engine *e, int enabled);
+float gfe_last_kernel_ms(const gfe_engine *e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GFALIGN_B200_H */
