@@ -69,7 +69,7 @@ EXPORTS = [
     "gfe_set_alignments_device", "gfe_set_universe", "gfe_score_paths", "gfe_score_paths_device",
     "gfe_score_pairs", "gfe_edge_support", "gfe_edge_traversals_device",
     "gfe_edge_weights_from_counts", "gfe_search", "gfe_get_counters", "gfe_set_timing",
-    "gfe_last_kernel_ms",
+    "gfe_last_kernel_ms", "gfe_kernel_time_stats", "gfe_device_status",
 ]
 
 _lib = None
@@ -110,6 +110,8 @@ def load_library() -> C.CDLL:
     lib.gfe_set_timing.argtypes = [C.c_void_p, C.c_int]
     lib.gfe_last_kernel_ms.argtypes = [C.c_void_p]
     lib.gfe_last_kernel_ms.restype = C.c_float
+    lib.gfe_device_status.argtypes = [C.c_void_p, _u32p]
+    lib.gfe_kernel_time_stats.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_uint32)]
     _lib = lib
     return lib
 
@@ -283,6 +285,18 @@ class Engine:
 
     def last_kernel_ms(self) -> float:
         return float(self._lib.gfe_last_kernel_ms(self._h))
+
+    def device_status(self) -> int:
+        """Sticky flags of the *_device calls (bit0 path outside universe, bit1 worklist overflow)."""
+        f = C.c_uint32()
+        self._check(self._lib.gfe_device_status(self._h, C.byref(f)))
+        return f.value
+
+    def kernel_time_stats(self):
+        """(total ms, launches) of the dominant kernel since the previous call; synchronises."""
+        ms, n = C.c_double(), C.c_uint32()
+        self._check(self._lib.gfe_kernel_time_stats(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
 
     # set_alignments records A so score_pairs can size its outputs
     _A_hint = 0

@@ -62,6 +62,21 @@ static int ensure_pinned(gfe_engine *e, PinBuf<T> &b, size_t n) {
         if (rc__ != GFE_OK) return rc__; \
     } while (0)
 
+// next (start, stop) event pair of the timing ring; also becomes ev0/ev1 ("last launch")
+static int next_event_pair(gfe_engine *e) {
+    if (e->ev_used + 2 > e->ev_ring.size()) {
+        for (int i = 0; i < 2; ++i) {
+            cudaEvent_t ev;
+            CUDA_TRY(e, cudaEventCreate(&ev));
+            e->ev_ring.push_back(ev);
+        }
+    }
+    e->ev0 = e->ev_ring[e->ev_used];
+    e->ev1 = e->ev_ring[e->ev_used + 1];
+    e->ev_used += 2;
+    return GFE_OK;
+}
+
 extern "C" {
 
 const char *gfe_version(void) { return "gfalign_b200 0.1 (sm_100a)"; }
@@ -87,8 +102,6 @@ int gfe_create(int cuda_device, gfe_engine **out) {
     e->device = cuda_device;
     err = cudaSetDevice(cuda_device);
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
-    if (err == cudaSuccess) err = cudaEventCreate(&e->ev0);
-    if (err == cudaSuccess) err = cudaEventCreate(&e->ev1);
     cudaDeviceProp prop;
     if (err == cudaSuccess) err = cudaGetDeviceProperties(&prop, cuda_device);
     if (err == cudaSuccess) {
@@ -111,8 +124,7 @@ void gfe_destroy(gfe_engine *e) {
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     e->free_all();
-    if (e->ev0) cudaEventDestroy(e->ev0);
-    if (e->ev1) cudaEventDestroy(e->ev1);
+    for (cudaEvent_t ev : e->ev_ring) cudaEventDestroy(ev);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -124,6 +136,35 @@ int gfe_set_timing(gfe_engine *e, int enabled) {
 }
 
 float gfe_last_kernel_ms(const gfe_engine *e) { return e ? e->last_kernel_ms : 0.f; }
+
+int gfe_kernel_time_stats(gfe_engine *e, double *total_ms, uint32_t *launches) {
+    if (!e || !total_ms || !launches) return GFE_ERR_ARG;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    CUDA_TRY(e, cudaDeviceSynchronize());
+    double tot = 0;
+    for (size_t i = 0; i + 1 < e->ev_used; i += 2) {
+        float ms = 0.f;
+        CUDA_TRY(e, cudaEventElapsedTime(&ms, e->ev_ring[i], e->ev_ring[i + 1]));
+        tot += ms;
+    }
+    *total_ms = tot;
+    *launches = (uint32_t)(e->ev_used / 2);
+    e->ev_used = 0;
+    return GFE_OK;
+}
+
+int gfe_device_status(gfe_engine *e, uint32_t *flags) {
+    if (!e || !flags) return GFE_ERR_ARG;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    CUDA_TRY(e, cudaDeviceSynchronize());
+    uint32_t err = 0, wc[2] = {0, 0};
+    if (e->d_err.ptr)
+        CUDA_TRY(e, cudaMemcpy(&err, e->d_err.ptr, sizeof(err), cudaMemcpyDeviceToHost));
+    if (e->d_work_count.ptr)
+        CUDA_TRY(e, cudaMemcpy(wc, e->d_work_count.ptr, sizeof(wc), cudaMemcpyDeviceToHost));
+    *flags = (err ? 1u : 0u) | (wc[1] ? 2u : 0u);
+    return GFE_OK;
+}
 
 int gfe_get_counters(const gfe_engine *e, gfe_counters *out) {
     if (!e || !out) return GFE_ERR_ARG;
@@ -171,6 +212,43 @@ static int validate_csr_host(gfe_engine *e, const uint32_t *offsets, const uint3
     return GFE_OK;
 }
 
+// Length histogram of the alignment table on the device -> bucket geometry (host copy in e->bk).
+static int build_bucket_geometry(gfe_engine *e) {
+    TRY(ensure_dev(e, e->d_hist, kNumBuckets + 2));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_hist.ptr, 0, (kNumBuckets + 2) * sizeof(uint32_t), e->stream));
+    launch_length_histogram(e->d_off, e->A, e->d_hist.ptr, e->stream);
+    e->kernel_launches += e->A ? 1 : 0;
+    uint32_t hist[kNumBuckets + 2];
+    CUDA_TRY(e, cudaMemcpyAsync(hist, e->d_hist.ptr, sizeof(hist), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    Buckets &bk = e->bk;
+    uint64_t row = 0, tile = 0, base = 0;
+    for (int b = 0; b < kNumBuckets; ++b) {
+        bk.count[b] = hist[b];
+        bk.row_start[b] = (uint32_t)row;
+        bk.tile_start[b] = (uint32_t)tile;
+        base = (base + 7) & ~7ull;            // 16-byte aligned matrices
+        bk.step_base[b] = (uint32_t)base;
+        row += hist[b];
+        if (b >= 1) tile += (hist[b] + kBlock - 1) / kBlock;
+        base += b == kLongBucket ? (uint64_t)hist[kNumBuckets + 1] : (uint64_t)hist[b] * b;
+    }
+    bk.row_start[kNumBuckets] = (uint32_t)row;
+    bk.tile_start[kNumBuckets] = (uint32_t)tile;
+    if (base + 8 >= 0xFFFFFFFFull) {
+        set_error(e, "alignment shard has too many steps for 32-bit element offsets; shard it");
+        return GFE_ERR_LIMIT;
+    }
+    e->bstep_elems = base + 8;
+    e->max_m = hist[kNumBuckets];
+    if (e->max_m > GFE_MAX_STEPS) {
+        set_error(e, "an alignment has %u steps; the reference's MAX_N allows %u", e->max_m,
+                  GFE_MAX_STEPS);
+        return GFE_ERR_LIMIT;
+    }
+    return GFE_OK;
+}
+
 int gfe_set_alignments(gfe_engine *e, const uint32_t *offsets, const uint32_t *steps, uint64_t A,
                        uint32_t n_nodes) {
     if (!e) return GFE_ERR_ARG;
@@ -199,7 +277,7 @@ int gfe_set_alignments(gfe_engine *e, const uint32_t *offsets, const uint32_t *s
     e->max_m = mx;
     e->have_alignments = true;
     e->have_universe = false;
-    return GFE_OK;
+    return build_bucket_geometry(e);
 }
 
 int gfe_set_alignments_device(gfe_engine *e, const uint32_t *d_offsets, const uint32_t *d_steps,
@@ -214,10 +292,10 @@ int gfe_set_alignments_device(gfe_engine *e, const uint32_t *d_offsets, const ui
     e->A = A;
     e->S = total_steps;
     e->n_nodes = n_nodes;
-    e->max_m = GFE_MAX_STEPS;   // unknown: keep the long-alignment kernels armed
     e->have_alignments = true;
     e->have_universe = false;
-    return GFE_OK;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    return build_bucket_geometry(e);   // also finds the longest alignment
 }
 
 int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) {
@@ -248,9 +326,17 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) 
         CUDA_TRY(e, cudaMemcpyAsync(e->d_node2local.ptr, e->node2local.data(),
                                     (size_t)e->n_nodes * sizeof(uint32_t), cudaMemcpyHostToDevice,
                                     e->stream));
-    TRY(ensure_dev(e, e->d_lstep, e->S + 8));
-    launch_localize_steps(e->d_steps, e->d_node2local.ptr, e->d_lstep.ptr, e->S, e->stream);
-    e->kernel_launches += e->S ? 1 : 0;
+    TRY(ensure_dev(e, e->d_bstep, e->bstep_elems));
+    TRY(ensure_dev(e, e->d_ldesc, std::max<uint32_t>(e->bk.count[kLongBucket], 1)));
+    TRY(ensure_dev(e, e->d_perm, std::max<uint64_t>(e->A, 1)));
+    TRY(ensure_dev(e, e->d_cursors, kNumBuckets + 1));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_cursors.ptr, 0, (kNumBuckets + 1) * sizeof(uint32_t), e->stream));
+    e->bk.bstep = e->d_bstep.ptr;
+    e->bk.ldesc = e->d_ldesc.ptr;
+    e->bk.perm = e->d_perm.ptr;
+    launch_bucket_scatter(e->d_off, e->d_steps, e->d_node2local.ptr, e->A, e->bk, e->d_bstep.ptr,
+                          e->d_ldesc.ptr, e->d_perm.ptr, e->d_cursors.ptr, e->stream);
+    e->kernel_launches += e->A ? 1 : 0;
     CUDA_TRY(e, cudaGetLastError());
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     e->h2d_bytes += (size_t)e->n_nodes * sizeof(uint32_t);
@@ -271,22 +357,29 @@ static uint32_t pick_chunk(const gfe_engine *e, uint32_t P) {
 
 // Enqueue table build + scoring (+ exact fallbacks) for paths already on the device in local ids.
 static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *d_pstep, uint32_t P,
-                         int filter, uint32_t *d_counts, cudaStream_t st) {
+                         uint32_t total_steps, int filter, uint32_t *d_counts, cudaStream_t st) {
     TRY(ensure_dev(e, e->d_ptab, (size_t)P * e->tab_stride));
-    if (!e->d_work.ptr) {
-        TRY(ensure_dev(e, e->d_work, e->work_cap));
+    TRY(ensure_dev(e, e->d_pnext, (size_t)total_steps + 8));
+    // exact-DP worklist: sized for 1 ambiguous pair in 128 checks (cfg3 measures ~1 in 2500)
+    {
+        const uint64_t want = std::min<uint64_t>(std::max<uint64_t>((uint64_t)P * e->A / 128, 1u << 20),
+                                                 1ull << 27);
+        if (want > e->work_cap) e->work_cap = (size_t)want;
+        if (e->d_work.cap < e->work_cap) {
+            CUDA_TRY(e, cudaStreamSynchronize(st));
+            TRY(ensure_dev(e, e->d_work, e->work_cap));
+        }
         TRY(ensure_dev(e, e->d_work_count, 4));
     }
     CUDA_TRY(e, cudaMemsetAsync(d_counts, 0, (size_t)P * 2 * sizeof(uint32_t), st));
     CUDA_TRY(e, cudaMemsetAsync(e->d_work_count.ptr, 0, 4 * sizeof(uint32_t), st));
-    launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, st);
+    launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr, st);
     ScoreArgs a;
-    a.off = e->d_off;
-    a.lstep = e->d_lstep.ptr;
-    a.A = e->A;
+    a.bk = e->bk;
     a.poff = d_poff;
     a.pstep = d_pstep;
     a.ptab = e->d_ptab.ptr;
+    a.pnext = e->d_pnext.ptr;
     a.tab_stride = e->tab_stride;
     a.P = P;
     a.chunk = pick_chunk(e, P);
@@ -294,11 +387,14 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     a.counts = d_counts;
     a.work = e->d_work.ptr;
     a.work_count = e->d_work_count.ptr;
-    a.work_cap = (uint32_t)e->work_cap;
-    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    a.work_cap = (uint32_t)std::min<size_t>(e->d_work.cap, 0xFFFFFFFFu);
+    if (e->timing) {
+        TRY(next_event_pair(e));
+        CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    }
     launch_score_paths(a, e->sm_count, st);
     if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
-    e->kernel_launches += 1 + (e->A ? 1 : 0);
+    e->kernel_launches += 2;
     if (e->A) {
         launch_exact_worklist(a, st);
         e->kernel_launches += 1;
@@ -358,7 +454,7 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
                                 e->stream));
     const uint32_t *d_poff = reinterpret_cast<const uint32_t *>(e->d_stage.ptr);
     const uint16_t *d_pstep = reinterpret_cast<const uint16_t *>(e->d_stage.ptr + off_bytes);
-    TRY(enqueue_score(e, d_poff, d_pstep, P, filter, e->d_counts.ptr, e->stream));
+    TRY(enqueue_score(e, d_poff, d_pstep, P, total, filter, e->d_counts.ptr, e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, (size_t)P * 2 * sizeof(uint32_t),
                                 cudaMemcpyDeviceToHost, e->stream));
     uint32_t wc[2] = {0, 0};
@@ -367,15 +463,12 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     wc[0] = e->h_wc[0];
     wc[1] = e->h_wc[1];
-    if (e->timing) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
+    if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
     e->h2d_bytes += bytes;
     e->d2h_bytes += (size_t)P * 2 * sizeof(uint32_t) + 8;
     if (wc[1]) {
         // the exact-DP worklist overflowed: grow it and redo the batch (never silently wrong)
-        e->work_cap = std::max<size_t>(e->work_cap * 4, (size_t)wc[0] + 1024);
-        CUDA_TRY(e, cudaFree(e->d_work.ptr));
-        e->d_work.ptr = nullptr;
-        e->d_work.cap = 0;
+        e->work_cap = std::max<size_t>(e->d_work.cap * 2, (size_t)wc[0] + 1024);
         TRY(ensure_dev(e, e->d_work, e->work_cap));
         return gfe_score_paths(e, path_offsets, path_steps, P, filter, counts);
     }
@@ -394,7 +487,7 @@ int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
     }
     if (P == 0) return GFE_OK;
     CUDA_TRY(e, cudaSetDevice(e->device));
-    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : e->stream;
+    cudaStream_t st = (cudaStream_t)cuda_stream;   // NULL = the CUDA default stream
     TRY(ensure_dev(e, e->d_plocal, (size_t)total_path_steps + 8));
     if (!e->d_err.ptr) {
         TRY(ensure_dev(e, e->d_err, 4));
@@ -403,7 +496,7 @@ int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
     launch_localize_paths(d_path_steps, e->d_node2local.ptr, e->n_nodes, e->L, e->d_plocal.ptr,
                           total_path_steps, e->d_err.ptr, st);
     e->kernel_launches += 1;
-    return enqueue_score(e, d_path_offsets, e->d_plocal.ptr, P, filter, d_counts, st);
+    return enqueue_score(e, d_path_offsets, e->d_plocal.ptr, P, total_path_steps, filter, d_counts, st);
 }
 
 // ---- evalPath scoring ---------------------------------------------------------------------------
@@ -461,11 +554,10 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
     }
     CUDA_TRY(e, cudaMemsetAsync(e->d_counts.ptr, 0, 2 * sizeof(uint32_t), st));
     CUDA_TRY(e, cudaMemsetAsync(e->d_work_count.ptr, 0, 4 * sizeof(uint32_t), st));
-    launch_build_tables(d_poff, d_pstep, 1, e->L, e->tab_stride, e->d_ptab.ptr, st);
+    TRY(ensure_dev(e, e->d_pnext, (size_t)n + 8));
+    launch_build_tables(d_poff, d_pstep, 1, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr, st);
     PairArgs a;
-    a.off = e->d_off;
-    a.lstep = e->d_lstep.ptr;
-    a.A = e->A;
+    a.bk = e->bk;
     a.pstep = d_pstep;
     a.n = n;
     a.ptab = e->d_ptab.ptr;
@@ -477,10 +569,13 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
     a.work = e->d_pair_work.ptr;
     a.work_count = e->d_work_count.ptr;
     a.work_cap = (uint32_t)std::min<uint64_t>(e->d_pair_work.cap, 0xFFFFFFFFu);
-    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    if (e->timing) {
+        TRY(next_event_pair(e));
+        CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    }
     launch_pair_classify(a, e->sm_count, st);
     if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
-    e->kernel_launches += 1 + (e->A ? 1 : 0);
+    e->kernel_launches += 2;
     if (e->A) {
         launch_pair_exact(a, st);
         e->kernel_launches += 1;
@@ -501,7 +596,7 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
         CUDA_TRY(e, cudaMemcpyAsync(t_rc, e->d_trc.ptr, e->A * sizeof(int32_t),
                                     cudaMemcpyDeviceToHost, st));
     CUDA_TRY(e, cudaStreamSynchronize(st));
-    if (e->timing) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
+    if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
     e->exact_pairs += e->h_wc[0];
     e->h2d_bytes += bytes;
     e->d2h_bytes += 16 + ((t_fw ? 1 : 0) + (t_rc ? 1 : 0)) * e->A * sizeof(int32_t);
@@ -539,7 +634,7 @@ int gfe_edge_traversals_device(gfe_engine *e, const uint32_t *edge_from, const u
     }
     if (E >= 0x7FFFFFFFu) return GFE_ERR_LIMIT;
     CUDA_TRY(e, cudaSetDevice(e->device));
-    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : e->stream;
+    cudaStream_t st = (cudaStream_t)cuda_stream;   // NULL = the CUDA default stream
     const uint32_t space = 2 * e->n_nodes;
     for (uint32_t i = 0; i < E; ++i)
         if (edge_from[i] >= space || edge_to[i] >= space) {
@@ -577,7 +672,10 @@ int gfe_edge_traversals_device(gfe_engine *e, const uint32_t *edge_from, const u
     a.n_steps_space = space;
     a.counts = d_counts;
     a.n_slots = 2 * E;
-    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    if (e->timing) {
+        TRY(next_event_pair(e));
+        CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    }
     if (E) launch_edge_support(a, e->sm_count, st);
     if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
     e->kernel_launches += (E && e->A) ? 1 : 0;
@@ -609,14 +707,14 @@ int gfe_edge_support(gfe_engine *e, const uint32_t *edge_from, const uint32_t *e
                      uint32_t *weights) {
     if (!e || (E && !weights)) return GFE_ERR_ARG;
     TRY(ensure_dev(e, e->d_edge_counts, std::max<size_t>((size_t)E * 2, 1)));
-    TRY(gfe_edge_traversals_device(e, edge_from, edge_to, E, e->d_edge_counts.ptr, nullptr));
+    TRY(gfe_edge_traversals_device(e, edge_from, edge_to, E, e->d_edge_counts.ptr, (void *)e->stream));
     std::vector<uint32_t> counts((size_t)E * 2);
     if (E) {
         CUDA_TRY(e, cudaMemcpyAsync(counts.data(), e->d_edge_counts.ptr, counts.size() * 4,
                                     cudaMemcpyDeviceToHost, e->stream));
         CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     }
-    if (e->timing) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
+    if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
     e->d2h_bytes += counts.size() * 4;
     return gfe_edge_weights_from_counts(edge_from, edge_to, E, counts.data(), weights);
 }

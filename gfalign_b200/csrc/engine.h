@@ -24,7 +24,9 @@ struct gfe_engine {
     int device = 0;
     int sm_count = 148;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // last timed launch (points into ev_ring)
+    std::vector<cudaEvent_t> ev_ring;           // pairs recorded since the last gfe_kernel_time_stats
+    size_t ev_used = 0;
     bool timing = false;
     float last_kernel_ms = 0.f;
     char error[512] = "";
@@ -39,14 +41,18 @@ struct gfe_engine {
     // universe-local view
     std::vector<uint32_t> node2local;
     DevBuf<uint32_t> d_node2local;
-    DevBuf<uint16_t> d_lstep;
+    DevBuf<uint16_t> d_bstep;        // length-bucketed local steps
+    DevBuf<uint2> d_ldesc;
+    DevBuf<uint32_t> d_perm, d_hist, d_cursors;
+    gfe::Buckets bk{};
+    uint64_t bstep_elems = 0;
     uint32_t L = 0, tab_stride = 8;
     bool have_universe = false;
 
     // candidate-path staging and results
     PinBuf<unsigned char> h_stage;
     DevBuf<unsigned char> d_stage;
-    DevBuf<uint16_t> d_ptab, d_plocal;
+    DevBuf<uint16_t> d_ptab, d_plocal, d_pnext;
     DevBuf<uint32_t> d_counts, d_err;
     PinBuf<uint32_t> h_counts;
     uint32_t h_wc_storage[4] = {0, 0, 0, 0};
@@ -70,8 +76,9 @@ struct gfe_engine {
     void free_all() {
         auto fd = [](void *p) { if (p) cudaFree(p); };
         auto fh = [](void *p) { if (p) cudaFreeHost(p); };
-        fd(own_off.ptr); fd(own_steps.ptr); fd(d_node2local.ptr); fd(d_lstep.ptr);
-        fd(d_stage.ptr); fd(d_ptab.ptr); fd(d_plocal.ptr); fd(d_counts.ptr); fd(d_err.ptr);
+        fd(own_off.ptr); fd(own_steps.ptr); fd(d_node2local.ptr); fd(d_bstep.ptr);
+        fd(d_ldesc.ptr); fd(d_perm.ptr); fd(d_hist.ptr); fd(d_cursors.ptr);
+        fd(d_stage.ptr); fd(d_ptab.ptr); fd(d_plocal.ptr); fd(d_pnext.ptr); fd(d_counts.ptr); fd(d_err.ptr);
         fd(d_work.ptr); fd(d_work_count.ptr); fd(d_pair_work.ptr); fd(d_tfw.ptr); fd(d_trc.ptr);
         fd(d_row_off.ptr); fd(d_edge_counts.ptr); fd(d_row_ent.ptr);
         fh(h_stage.ptr); fh(h_counts.ptr);

@@ -8,37 +8,81 @@ namespace gfe {
 namespace {
 
 constexpr unsigned kFull = 0xFFFFFFFFu;
-enum Verdict : int { kNone = 0, kBad = 1, kGood = 2, kExact = 3 };
+enum Verdict : int { kNone = 0, kBad = 1, kGood = 2, kExact = 3, kSlow = 4 };
 
 __device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }
 
 // ------------------------------------------------------------------------------------------------
-// K0a: global-id steps -> universe-local 16-bit steps.  One pass, 16 B in / 8 B out per thread
-// iteration; the node->local map (4 B/node) is gathered through L2.
+// K0a: histogram of alignment lengths (buckets 0, 1..kMaxBucket, long), max length, long steps.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock)
-localize_steps_kernel(const uint32_t *__restrict__ steps, const uint32_t *__restrict__ map,
-                      uint16_t *__restrict__ out, uint64_t S) {
-    const uint64_t nvec = S >> 2;
+length_histogram_kernel(const uint32_t *__restrict__ off, uint64_t A, uint32_t *__restrict__ hist) {
+    __shared__ uint32_t s_h[kNumBuckets + 2];
+    if (threadIdx.x < kNumBuckets + 2) s_h[threadIdx.x] = 0;
+    __syncthreads();
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t v = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += stride) {
-        uint4 s = __ldg(reinterpret_cast<const uint4 *>(steps) + v);
-        uint32_t a = (__ldg(map + (s.x >> 1)) << 1) | (s.x & 1u);
-        uint32_t b = (__ldg(map + (s.y >> 1)) << 1) | (s.y & 1u);
-        uint32_t c = (__ldg(map + (s.z >> 1)) << 1) | (s.z & 1u);
-        uint32_t d = (__ldg(map + (s.w >> 1)) << 1) | (s.w & 1u);
-        uint2 o = make_uint2(a | (b << 16), c | (d << 16));
-        reinterpret_cast<uint2 *>(out)[v] = o;
+    for (uint64_t a = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; a < A; a += stride) {
+        const uint32_t m = __ldg(off + a + 1) - __ldg(off + a);
+        const uint32_t b = m <= (uint32_t)kMaxBucket ? m : (uint32_t)kLongBucket;
+        atomicAdd(&s_h[b], 1u);
+        atomicMax(&s_h[kNumBuckets], m);
+        if (b == (uint32_t)kLongBucket) atomicAdd(&s_h[kNumBuckets + 1], m);
     }
-    const uint64_t tail = nvec << 2;
-    uint64_t t = tail + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t < S) {
-        uint32_t s = steps[t];
-        out[t] = (uint16_t)((map[s >> 1] << 1) | (s & 1u));
+    __syncthreads();
+    if (threadIdx.x < kNumBuckets + 2 && s_h[threadIdx.x]) {
+        if (threadIdx.x == kNumBuckets) atomicMax(&hist[threadIdx.x], s_h[threadIdx.x]);
+        else atomicAdd(&hist[threadIdx.x], s_h[threadIdx.x]);
     }
 }
 
-// K0b: candidate paths (global ids) -> local ids; a node outside the universe raises *err.
+// K0b: scatter every alignment into its length bucket, translating steps to universe-local 16-bit
+// ids on the way (node2local gathered through L2).  Row order inside a bucket is arbitrary; perm
+// remembers the original index.  Slots are handed out per CTA (shared-memory ranks + one global
+// atomic per bucket per CTA).
+__global__ void __launch_bounds__(kBlock)
+bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ steps,
+                      const uint32_t *__restrict__ map, uint64_t A, const Buckets bk,
+                      uint16_t *__restrict__ bstep, uint2 *__restrict__ ldesc,
+                      uint32_t *__restrict__ perm, uint32_t *__restrict__ cursors) {
+    __shared__ uint32_t s_cnt[kNumBuckets + 1], s_base[kNumBuckets + 1];
+    const uint64_t n_tiles = (A + kBlock - 1) / kBlock;
+    for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        if (threadIdx.x <= kNumBuckets) s_cnt[threadIdx.x] = 0;
+        __syncthreads();
+        const uint64_t a = tile * kBlock + threadIdx.x;
+        uint32_t o0 = 0, m = 0, b = 0, rank = 0, lrank = 0;
+        const bool valid = a < A;
+        if (valid) {
+            o0 = __ldg(off + a);
+            m = __ldg(off + a + 1) - o0;
+            b = m <= (uint32_t)kMaxBucket ? m : (uint32_t)kLongBucket;
+            rank = atomicAdd(&s_cnt[b], 1u);
+            if (b == (uint32_t)kLongBucket) lrank = atomicAdd(&s_cnt[kNumBuckets], m);
+        }
+        __syncthreads();
+        if (threadIdx.x <= kNumBuckets && s_cnt[threadIdx.x])
+            s_base[threadIdx.x] = atomicAdd(&cursors[threadIdx.x], s_cnt[threadIdx.x]);
+        __syncthreads();
+        if (valid) {
+            const uint32_t slot = s_base[b] + rank;
+            perm[bk.row_start[b] + slot] = (uint32_t)a;
+            uint32_t dst;
+            if (b == (uint32_t)kLongBucket) {
+                dst = bk.step_base[b] + s_base[kNumBuckets] + lrank;
+                ldesc[slot] = make_uint2(dst, m);
+            } else {
+                dst = bk.step_base[b] + slot * m;
+            }
+            for (uint32_t j = 0; j < m; ++j) {
+                const uint32_t s = __ldg(steps + o0 + j);
+                bstep[dst + j] = (uint16_t)((__ldg(map + (s >> 1)) << 1) | (s & 1u));
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// K0b': candidate paths (global ids) -> local ids; a node outside the universe raises *err.
 __global__ void localize_paths_kernel(const uint32_t *__restrict__ psteps,
                                       const uint32_t *__restrict__ map, uint32_t n_nodes,
                                       uint32_t L, uint16_t *__restrict__ out, uint32_t total,
@@ -51,6 +95,53 @@ __global__ void localize_paths_kernel(const uint32_t *__restrict__ psteps,
     out[i] = (uint16_t)((l << 1) | (s & 1u));
 }
 
+// Which bucket a kBlock-row tile belongs to, and this thread's row in it.
+struct RowRef {
+    const uint16_t *ptr;
+    uint32_t m, sorted;
+    bool valid;
+};
+__device__ __forceinline__ int tile_bucket(const Buckets &bk, uint32_t tile) {
+    int b = 1;
+#pragma unroll
+    for (int k = 2; k < kNumBuckets; ++k) b += (tile >= bk.tile_start[k]) ? 1 : 0;
+    return b;
+}
+__device__ __forceinline__ RowRef tile_row(const Buckets &bk, int b, uint32_t tile) {
+    RowRef r;
+    const uint32_t row = (tile - bk.tile_start[b]) * kBlock + threadIdx.x;
+    r.valid = row < bk.count[b];
+    r.sorted = bk.row_start[b] + row;
+    if (b == kLongBucket) {
+        const uint2 d = r.valid ? __ldg(bk.ldesc + row) : make_uint2(bk.step_base[b], 0u);
+        r.ptr = bk.bstep + d.x;
+        r.m = d.y;
+    } else {
+        r.ptr = bk.bstep + bk.step_base[b] + (r.valid ? (size_t)row * b : 0);
+        r.m = (uint32_t)b;
+    }
+    return r;
+}
+// sorted row -> (steps, m); used by the exact-DP worklist kernels
+__device__ __forceinline__ RowRef locate_row(const Buckets &bk, uint32_t sorted) {
+    int b = 0;
+#pragma unroll
+    for (int k = 1; k < kNumBuckets; ++k) b += (sorted >= bk.row_start[k]) ? 1 : 0;
+    RowRef r;
+    const uint32_t row = sorted - bk.row_start[b];
+    r.valid = true;
+    r.sorted = sorted;
+    if (b == kLongBucket) {
+        const uint2 d = __ldg(bk.ldesc + row);
+        r.ptr = bk.bstep + d.x;
+        r.m = d.y;
+    } else {
+        r.ptr = bk.bstep + bk.step_base[b] + (size_t)row * b;
+        r.m = (uint32_t)b;
+    }
+    return r;
+}
+
 // ------------------------------------------------------------------------------------------------
 // K0c: node -> first-position table of each candidate path.  One CTA per path; the 32-bit working
 // row lives in shared memory ((L+1)*4 B <= 128 KB).  atomicMin on (pos<<1|minus) keeps the first
@@ -59,7 +150,8 @@ __global__ void localize_paths_kernel(const uint32_t *__restrict__ psteps,
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kBlock)
 build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restrict__ pstep,
-                    uint32_t L, uint32_t stride, uint16_t *__restrict__ ptab) {
+                    uint32_t L, uint32_t stride, uint16_t *__restrict__ ptab,
+                    uint16_t *__restrict__ pnext) {
     extern __shared__ uint32_t row[];
     const uint32_t p = blockIdx.x;
     const uint32_t o0 = poff[p], n = poff[p + 1] - o0;
@@ -81,8 +173,18 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
         uint32_t v = i <= L ? row[i] : 0xFFFFFFFFu;
         uint32_t e = 0;
         if (v != 0xFFFFFFFFu)
-            e = ((((v & 0x7FFFFFFFu) >> 1) + 1u) << 2) | ((v & 1u) << 1) | (v >> 31);
+            e = ((((v & 0x7FFFFFFFu) >> 1) + 1u) << 2) | ((v & 1u) << 1) | (v >> 31);   // see TabEntry
         dst[i] = (uint16_t)e;
+    }
+    // next visit of the same node (0xFFFF = none): only positions of twice-visited nodes scan
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const uint32_t node = s[i] >> 1;
+        uint32_t nx = 0xFFFFu;
+        if (node < L && (row[node] >> 31) && row[node] != 0xFFFFFFFFu) {
+            for (uint32_t k = i + 1; k < n; ++k)
+                if ((uint32_t)(s[k] >> 1) == node) { nx = k; break; }
+        }
+        pnext[o0 + i] = (uint16_t)nx;
     }
 }
 
@@ -232,64 +334,179 @@ __device__ int warp_exact_T(const uint16_t *__restrict__ A, int n, const uint16_
 // ------------------------------------------------------------------------------------------------
 // K1: score_paths — evaluatePath(filter) for a chunk of candidate paths x a stream of alignments.
 // grid = (alignment-tile workers, path chunks).  The chunk's node->position tables sit in shared
-// memory; one thread owns one alignment (steps in registers when m <= kRegSteps) and tests it
-// against every table of the chunk: one shared-memory lookup per step answers the id filter, the
-// forward occurrence and the reverse-complement occurrence at once.  Per path the warp's verdicts
-// are combined with two ballots and one shared-memory atomic per warp; the CTA flushes its
-// chunk x {bad, good} counters with global atomics at the end.
+// memory; one thread owns one alignment row (its M steps in registers — rows are bucketed by
+// length, so the step loop is fully unrolled and branch-free) and tests it against every table of
+// the chunk: one shared-memory lookup per step answers the id filter, the forward occurrence and
+// the reverse-complement occurrence at once.
+//
+// Table entry e = (pos+1)<<2 | minus<<1 | twice, 0 = absent.  With x_j = e_j ^ (minus(B_j)<<1):
+//   B occurs forward at pos(B_0)      <=>  all (x_j - 4j) == x_0 above bit 0, bit 1 of x_0 clear
+//   rc(B) occurs ending at pos(B_0)   <=>  all (x_j + 4j) == x_0 above bit 0, bit 1 of x_0 set
+//   every node on the path            <=>  min_j e_j != 0;   touches path[0]  <=>  min_j e_j < 8
 // Verdict rule (proved + fuzzed against the reference, SURVEY.md Appendix A.3, tests/):
 //   filtered out -> nothing;  m > n -> good;  B or rc(B) occurs contiguously -> good;
-//   otherwise bad unless B touches the path's first node or a node visited twice -> exact DP.
+//   otherwise bad, unless B touches a node visited twice (search every visit) or the node of
+//   path[0] with a suffix/prefix overhang (exact DP worklist).
+// Per path the warp's verdicts are two ballots; lane (p mod 32) keeps the popcounts in registers,
+// so the inner loop has no atomics.  The CTA flushes chunk x {bad, good} once at the end.
 // ------------------------------------------------------------------------------------------------
-template <bool kFilter, bool kRegs>
-__device__ __forceinline__ int test_alignment(const uint16_t *__restrict__ tab, int n,
-                                              const uint32_t (&B)[kRegSteps],
-                                              const uint16_t *__restrict__ bglob, int m) {
-    bool pass = true, fw = true, rc = true;
-    uint32_t special = 0;    // bit0: node visited twice, bit1: node of path[0]
-    int p0 = 0;
-    if (kRegs) {
-#pragma unroll
-        for (int j = 0; j < kRegSteps; ++j) {
-            if (j >= m) break;
-            const uint32_t st = B[j];
-            const uint32_t e = tab[st >> 1];
-            if (e == kTabAbsent) {
-                pass = false;
-                if (kFilter) break;
-                fw = rc = false;
-                continue;
+
+// Rare second look at an alignment the table test could not settle (m <= n, no occurrence found
+// through first positions).  A = the path (local ids), nxt = next visit of the same node.
+__device__ __noinline__ int slow_verdict(const uint16_t *__restrict__ A,
+                                         const uint16_t *__restrict__ nxt, int n,
+                                         const uint16_t *__restrict__ tab,
+                                         const uint16_t *__restrict__ b, int m, bool twice) {
+    if (twice) {
+        // try every visit of B[0]'s node as the start of a forward occurrence and as the end of a
+        // reverse-complement occurrence, comparing steps directly
+        const uint32_t e = tab[b[0] >> 1];
+        if (e != kTabAbsent) {
+            for (int q = (int)(e >> 2) - 1; q != 0xFFFF; q = nxt[q]) {
+                if (q + m <= n) {
+                    bool ok = true;
+                    for (int j = 0; j < m && ok; ++j) ok = (A[q + j] == b[j]);
+                    if (ok) return kGood;
+                }
+                if (q - (m - 1) >= 0) {
+                    bool ok = true;
+                    for (int j = 0; j < m && ok; ++j) ok = (A[q - j] == (uint16_t)(b[j] ^ 1u));
+                    if (ok) return kGood;
+                }
             }
-            const int pos = (int)(e >> 2) - 1;
-            const uint32_t o = (e >> 1) & 1u, bo = st & 1u;
-            special |= (e & 1u) | ((pos == 0) ? 2u : 0u);
-            if (j == 0) p0 = pos;
-            fw = fw && (pos == p0 + j) && (o == bo);
-            rc = rc && (pos == p0 - j) && (o != bo);
-        }
-    } else {
-        for (int j = 0; j < m; ++j) {
-            const uint32_t st = bglob[j];
-            const uint32_t e = tab[st >> 1];
-            if (e == kTabAbsent) {
-                pass = false;
-                if (kFilter) break;
-                fw = rc = false;
-                continue;
-            }
-            const int pos = (int)(e >> 2) - 1;
-            const uint32_t o = (e >> 1) & 1u, bo = st & 1u;
-            special |= (e & 1u) | ((pos == 0) ? 2u : 0u);
-            if (j == 0) p0 = pos;
-            fw = fw && (pos == p0 + j) && (o == bo);
-            rc = rc && (pos == p0 - j) && (o != bo);
         }
     }
-    if (kFilter && !pass) return kNone;
-    if (m > n) return kGood;
-    if (fw || rc) return kGood;
-    if (special) return kExact;
+    // only if a proper suffix of B (or of rc(B)) equals a prefix of A can the traceback still
+    // score 0 (SURVEY.md Appendix A.3 class iv) -> exact DP
+    for (int k = 1; k < m; ++k) {
+        bool fw = true, rc = true;
+        for (int t = 0; t < k && (fw || rc); ++t) {
+            const uint16_t a = A[t];
+            fw = fw && (b[m - k + t] == a);
+            rc = rc && ((uint16_t)(b[k - 1 - t] ^ 1u) == a);
+        }
+        if (fw || rc) return kExact;
+    }
     return kBad;
+}
+
+struct Accum {
+    uint32_t bad[kMaxChunk / 32], good[kMaxChunk / 32];
+};
+
+// verdict bookkeeping shared by the fixed-length and the long-row paths
+template <bool kFilter>
+__device__ __forceinline__ void settle(const ScoreArgs &a, uint32_t p_glob, const uint16_t *tab,
+                                       int n, const uint16_t *row_ptr, int m, uint32_t sorted,
+                                       bool valid, uint32_t mn, uint32_t mn_present,
+                                       uint32_t orall, uint32_t accf, uint32_t accr, uint32_t x0,
+                                       bool &good, bool &bad) {
+    const bool pass = mn != 0;
+    const bool occ = pass && ((((accf & 0xFFFEu) == 0) && !(x0 & 2u)) ||
+                              (((accr & 0xFFFEu) == 0) && (x0 & 2u)));
+    const bool gt = m > n;
+    const bool twice = orall & 1u;
+    const bool special = twice || ((kFilter ? mn : mn_present) >> 2) == 1u;
+    const bool in = valid && (kFilter ? pass : true);
+    good = in && (gt || occ);
+    bad = in && !gt && !occ && !special;
+    if (in && !gt && !occ && special) {
+        const uint32_t po = a.poff[p_glob];
+        const int v = slow_verdict(a.pstep + po, a.pnext + po, n, tab, row_ptr, m, twice);
+        good = v == kGood;
+        bad = v == kBad;
+        if (v == kExact) {
+            const uint32_t idx = atomicAdd(a.work_count, 1u);
+            if (idx < a.work_cap) a.work[idx] = make_uint2(p_glob, sorted);
+            else atomicOr(a.work_count + 1, 1u);
+        }
+    }
+}
+
+template <int M, bool kFilter>
+__device__ __forceinline__ void score_tile_fixed(const ScoreArgs &a, const uint16_t *s_tab,
+                                                 const uint32_t *s_n, uint32_t pc, uint32_t p_base,
+                                                 const RowRef &r, Accum &acc, int lane) {
+    uint32_t boff[M], bo2[M];   // byte offset of the node's table entry; minus(B_j) << 1
+#pragma unroll
+    for (int j = 0; j < M; ++j) {
+        const uint32_t st = __ldg(r.ptr + j);
+        boff[j] = st & 0xFFFEu;
+        bo2[j] = (st & 1u) << 1;
+    }
+    const unsigned char *tabb = reinterpret_cast<const unsigned char *>(s_tab);
+    const uint32_t stride_b = a.tab_stride * 2;
+#pragma unroll
+    for (int h = 0; h < kMaxChunk / 32; ++h) {
+        const uint32_t p_lo = h * 32;
+        if (p_lo >= pc) break;
+        const uint32_t p_hi = min(pc, p_lo + 32);
+        for (uint32_t p = p_lo; p < p_hi; ++p) {
+            const unsigned char *row = tabb + (size_t)p * stride_b;
+            uint32_t e = *reinterpret_cast<const uint16_t *>(row + boff[0]);
+            const uint32_t x0 = e ^ bo2[0];
+            uint32_t mn = e, mnp = e ? e : 0xFFFFu, orall = e, accf = 0, accr = 0;
+#pragma unroll
+            for (int j = 1; j < M; ++j) {
+                e = *reinterpret_cast<const uint16_t *>(row + boff[j]);
+                const uint32_t x = e ^ bo2[j];
+                accf |= (x - 4u * j) ^ x0;
+                accr |= (x + 4u * j) ^ x0;
+                mn = min(mn, e);
+                if (!kFilter) mnp = min(mnp, e ? e : 0xFFFFu);
+                orall |= e;
+            }
+            bool good, bad;
+            settle<kFilter>(a, p_base + p, reinterpret_cast<const uint16_t *>(row), (int)s_n[p],
+                            r.ptr, M, r.sorted, r.valid, mn, mnp, orall, accf, accr, x0, good, bad);
+            const unsigned gm = __ballot_sync(kFull, good);
+            const unsigned bm = __ballot_sync(kFull, bad);
+            if ((uint32_t)lane == (p & 31u)) {
+                acc.good[h] += (uint32_t)__popc(gm);
+                acc.bad[h] += (uint32_t)__popc(bm);
+            }
+        }
+    }
+}
+
+template <bool kFilter>
+__device__ __forceinline__ void score_tile_long(const ScoreArgs &a, const uint16_t *s_tab,
+                                                const uint32_t *s_n, uint32_t pc, uint32_t p_base,
+                                                const RowRef &r, Accum &acc, int lane) {
+    const int m = (int)r.m;
+#pragma unroll
+    for (int h = 0; h < kMaxChunk / 32; ++h) {
+        const uint32_t p_lo = h * 32;
+        if (p_lo >= pc) break;
+        const uint32_t p_hi = min(pc, p_lo + 32);
+        for (uint32_t p = p_lo; p < p_hi; ++p) {
+            const uint16_t *tab = s_tab + (size_t)p * a.tab_stride;
+            uint32_t mn = 0xFFFFu, mnp = 0xFFFFu, orall = 0, accf = 0, accr = 0, x0 = 0;
+            if (r.valid) {
+                for (int j = 0; j < m; ++j) {
+                    const uint32_t st = __ldg(r.ptr + j);
+                    const uint32_t e = tab[st >> 1];
+                    const uint32_t x = e ^ ((st & 1u) << 1);
+                    if (j == 0) x0 = x;
+                    accf |= (x - 4u * j) ^ x0;
+                    accr |= (x + 4u * j) ^ x0;
+                    mn = min(mn, e);
+                    mnp = min(mnp, e ? e : 0xFFFFu);
+                    orall |= e;
+                    if (kFilter && e == 0) break;
+                }
+            }
+            bool good, bad;
+            settle<kFilter>(a, p_base + p, tab, (int)s_n[p], r.ptr, m, r.sorted, r.valid, mn, mnp,
+                            orall, accf, accr, x0, good, bad);
+            const unsigned gm = __ballot_sync(kFull, good);
+            const unsigned bm = __ballot_sync(kFull, bad);
+            if ((uint32_t)lane == (p & 31u)) {
+                acc.good[h] += (uint32_t)__popc(gm);
+                acc.bad[h] += (uint32_t)__popc(bm);
+            }
+        }
+    }
 }
 
 template <bool kFilter>
@@ -314,47 +531,39 @@ score_paths_kernel(const ScoreArgs a) {
     __syncthreads();
 
     const int lane = threadIdx.x & 31;
-    const uint64_t n_tiles = (a.A + kBlock - 1) / kBlock;
-    for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const uint64_t ai = tile * kBlock + threadIdx.x;
-        const bool valid = ai < a.A;
-        uint32_t o0 = 0, o1 = 0;
-        if (valid) {
-            o0 = __ldg(a.off + ai);
-            o1 = __ldg(a.off + ai + 1);
-        }
-        const int m = (int)(o1 - o0);
-        const uint16_t *bglob = a.lstep + o0;
-        uint32_t B[kRegSteps];
-        const bool regs = m <= kRegSteps;
-        if (regs) {
+    Accum acc;
 #pragma unroll
-            for (int j = 0; j < kRegSteps; ++j) B[j] = (j < m) ? (uint32_t)__ldg(bglob + j) : 0u;
+    for (int h = 0; h < kMaxChunk / 32; ++h) acc.bad[h] = acc.good[h] = 0;
+
+    const uint32_t n_tiles = a.bk.tile_start[kNumBuckets];
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int b = tile_bucket(a.bk, tile);
+        const RowRef r = tile_row(a.bk, b, tile);
+        switch (b) {
+#define GFE_CASE(M_) case M_: score_tile_fixed<M_, kFilter>(a, s_tab, s_n, pc, p_base, r, acc, lane); break;
+            GFE_CASE(1) GFE_CASE(2) GFE_CASE(3) GFE_CASE(4) GFE_CASE(5) GFE_CASE(6) GFE_CASE(7)
+            GFE_CASE(8) GFE_CASE(9) GFE_CASE(10) GFE_CASE(11) GFE_CASE(12) GFE_CASE(13)
+            GFE_CASE(14) GFE_CASE(15) GFE_CASE(16)
+#undef GFE_CASE
+            default: score_tile_long<kFilter>(a, s_tab, s_n, pc, p_base, r, acc, lane); break;
         }
-        for (uint32_t p = 0; p < pc; ++p) {
-            const uint16_t *tab = s_tab + (size_t)p * a.tab_stride;
-            const int n = (int)s_n[p];
-            int v = kNone;
-            if (valid) {
-                v = regs ? test_alignment<kFilter, true>(tab, n, B, bglob, m)
-                         : test_alignment<kFilter, false>(tab, n, B, bglob, m);
-            }
-            const unsigned gm = __ballot_sync(kFull, v == kGood);
-            const unsigned bm = __ballot_sync(kFull, v == kBad);
-            if (lane == 0) {
-                if (bm) atomicAdd(&s_cnt[2 * p], (uint32_t)__popc(bm));
-                if (gm) atomicAdd(&s_cnt[2 * p + 1], (uint32_t)__popc(gm));
-            }
-            if (v == kExact) {
-                const uint32_t idx = atomicAdd(a.work_count, 1u);
-                if (idx < a.work_cap) a.work[idx] = make_uint2(p_base + p, (uint32_t)ai);
-                else atomicOr(a.work_count + 1, 1u);
-            }
+    }
+    // lane l of every warp holds the counts of paths l, l+32 of the chunk
+#pragma unroll
+    for (int h = 0; h < kMaxChunk / 32; ++h) {
+        const uint32_t p = h * 32 + lane;
+        if (p < pc) {
+            if (acc.bad[h]) atomicAdd(&s_cnt[2 * p], acc.bad[h]);
+            if (acc.good[h]) atomicAdd(&s_cnt[2 * p + 1], acc.good[h]);
         }
     }
     __syncthreads();
-    for (uint32_t i = threadIdx.x; i < 2 * pc; i += blockDim.x)
-        if (s_cnt[i]) atomicAdd(&a.counts[2 * (size_t)p_base + i], s_cnt[i]);
+    // alignments without steps pass the filter and score 0 against every path: good
+    const uint32_t empty_rows = blockIdx.x == 0 ? a.bk.count[0] : 0u;
+    for (uint32_t i = threadIdx.x; i < 2 * pc; i += blockDim.x) {
+        const uint32_t v = s_cnt[i] + ((i & 1u) ? empty_rows : 0u);
+        if (v) atomicAdd(&a.counts[2 * (size_t)p_base + i], v);
+    }
 }
 
 // K1b: exact verdict for the worklist of ambiguous (path, alignment) pairs.
@@ -364,13 +573,13 @@ exact_worklist_kernel(const ScoreArgs a) {
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < cnt;
          idx += gridDim.x * blockDim.x) {
         const uint2 w = a.work[idx];
-        const uint32_t o0 = a.off[w.y];
-        const int m = (int)(a.off[w.y + 1] - o0);
+        const RowRef r = locate_row(a.bk, w.y);
+        const int m = (int)r.m;
         if (m > kExactRegSteps) continue;   // long alignments: exact_worklist_long_kernel
         const uint32_t po = a.poff[w.x];
         const int n = (int)(a.poff[w.x + 1] - po);
         int tf, tr;
-        exact_both(a.pstep + po, n, a.lstep + o0, m, false, &tf, &tr);
+        exact_both(a.pstep + po, n, r.ptr, m, false, &tf, &tr);
         const bool good = (tf == 0) || (tr == 0);
         atomicAdd(&a.counts[2 * (size_t)w.x + (good ? 1 : 0)], 1u);
     }
@@ -382,15 +591,15 @@ exact_worklist_long_kernel(const ScoreArgs a) {
     const uint32_t cnt = min(a.work_count[0], a.work_cap);
     for (uint32_t idx = blockIdx.x; idx < cnt; idx += gridDim.x) {
         const uint2 w = a.work[idx];
-        const uint32_t o0 = a.off[w.y];
-        const int m = (int)(a.off[w.y + 1] - o0);
+        const RowRef r = locate_row(a.bk, w.y);
+        const int m = (int)r.m;
         if (m <= kExactRegSteps) continue;
         const uint32_t po = a.poff[w.x];
         const int n = (int)(a.poff[w.x + 1] - po);
-        int tf = warp_exact_T(a.pstep + po, n, a.lstep + o0, m, false, scratch);
+        int tf = warp_exact_T(a.pstep + po, n, r.ptr, m, false, scratch);
         __syncwarp();
         int tr = -1;
-        if (tf != 0) tr = warp_exact_T(a.pstep + po, n, a.lstep + o0, m, true, scratch);
+        if (tf != 0) tr = warp_exact_T(a.pstep + po, n, r.ptr, m, true, scratch);
         __syncwarp();
         if ((threadIdx.x & 31) == 0) {
             const bool good = (tf == 0) || (tr == 0);
@@ -416,45 +625,54 @@ pair_classify_kernel(const PairArgs a) {
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const int n = (int)a.n;
-    const uint64_t n_tiles = (a.A + kBlock - 1) / kBlock;
-    for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const uint64_t ai = tile * kBlock + threadIdx.x;
-        const bool valid = ai < a.A;
-        int v = kNone;
-        if (valid) {
-            const uint32_t o0 = __ldg(a.off + ai);
-            const int m = (int)(__ldg(a.off + ai + 1) - o0);
-            const uint16_t *b = a.lstep + o0;
-            bool touch = false, pass = true;
-            for (int j = 0; j < m; ++j) {
-                const uint32_t e = s_tab[__ldg(b + j) >> 1];
-                if (e == kTabAbsent) pass = false; else touch = true;
-            }
-            int t = 0;
-            bool queued = false;
-            if (a.filter && !pass) {
-                t = INT32_MIN;
-            } else if (m > n || m == 0) {
-                t = 0; v = kGood;
-            } else if (!touch) {
-                t = -m; v = kBad;
-            } else {
-                queued = true;
-                const uint32_t idx = atomicAdd(a.work_count, 1u);
-                if (idx < a.work_cap) a.work[idx] = (uint32_t)ai;
-                else atomicOr(a.work_count + 1, 1u);
-            }
-            if (!queued) {
-                if (a.t_fw) a.t_fw[ai] = t;
-                if (a.t_rc) a.t_rc[ai] = t;
-            }
+    uint32_t my_good = 0, my_bad = 0;
+    // rows without steps: T = 0 both ways (the walk only consumes the path, free)
+    for (uint32_t row = blockIdx.x * blockDim.x + threadIdx.x; row < a.bk.count[0];
+         row += gridDim.x * blockDim.x) {
+        const uint32_t ai = a.bk.perm[a.bk.row_start[0] + row];
+        if (a.t_fw) a.t_fw[ai] = 0;
+        if (a.t_rc) a.t_rc[ai] = 0;
+        ++my_good;
+    }
+    const uint32_t n_tiles = a.bk.tile_start[kNumBuckets];
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int b = tile_bucket(a.bk, tile);
+        const RowRef r = tile_row(a.bk, b, tile);
+        if (!r.valid) continue;
+        const int m = (int)r.m;
+        bool touch = false, pass = true;
+        for (int j = 0; j < m; ++j) {
+            const uint32_t e = s_tab[__ldg(r.ptr + j) >> 1];
+            if (e == kTabAbsent) pass = false; else touch = true;
         }
-        const unsigned gm = __ballot_sync(kFull, v == kGood);
-        const unsigned bm = __ballot_sync(kFull, v == kBad);
-        if (lane == 0) {
-            if (bm) atomicAdd(&s_cnt[0], (uint32_t)__popc(bm));
-            if (gm) atomicAdd(&s_cnt[1], (uint32_t)__popc(gm));
+        int t = 0;
+        bool queued = false;
+        if (a.filter && !pass) {
+            t = INT32_MIN;
+        } else if (m > n) {
+            t = 0; ++my_good;
+        } else if (!touch) {
+            t = -m; ++my_bad;
+        } else {
+            queued = true;
+            const uint32_t idx = atomicAdd(a.work_count, 1u);
+            if (idx < a.work_cap) a.work[idx] = r.sorted;
+            else atomicOr(a.work_count + 1, 1u);
         }
+        if (!queued && (a.t_fw || a.t_rc)) {
+            const uint32_t ai = __ldg(a.bk.perm + r.sorted);
+            if (a.t_fw) a.t_fw[ai] = t;
+            if (a.t_rc) a.t_rc[ai] = t;
+        }
+    }
+    // warp-reduce the private counters, one shared atomic per warp, one global per CTA
+    for (int o = 16; o; o >>= 1) {
+        my_good += __shfl_down_sync(kFull, my_good, o);
+        my_bad += __shfl_down_sync(kFull, my_bad, o);
+    }
+    if (lane == 0) {
+        if (my_bad) atomicAdd(&s_cnt[0], my_bad);
+        if (my_good) atomicAdd(&s_cnt[1], my_good);
     }
     __syncthreads();
     if (threadIdx.x < 2 && s_cnt[threadIdx.x]) atomicAdd(&a.counts[threadIdx.x], s_cnt[threadIdx.x]);
@@ -469,12 +687,12 @@ pair_exact_kernel(const PairArgs a) {
     const uint32_t cnt = min(a.work_count[0], a.work_cap);
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < cnt;
          idx += gridDim.x * blockDim.x) {
-        const uint32_t ai = a.work[idx];
-        const uint32_t o0 = a.off[ai];
-        const int m = (int)(a.off[ai + 1] - o0);
+        const RowRef r = locate_row(a.bk, a.work[idx]);
+        const int m = (int)r.m;
         if (m > kExactRegSteps) continue;
         int tf, tr;
-        exact_both(s_path, (int)a.n, a.lstep + o0, m, true, &tf, &tr);
+        exact_both(s_path, (int)a.n, r.ptr, m, true, &tf, &tr);
+        const uint32_t ai = a.bk.perm[r.sorted];
         if (a.t_fw) a.t_fw[ai] = tf;
         if (a.t_rc) a.t_rc[ai] = tr;
         const int best = tf > tr ? tf : tr;
@@ -487,15 +705,15 @@ pair_exact_long_kernel(const PairArgs a) {
     extern __shared__ int scratch[];
     const uint32_t cnt = min(a.work_count[0], a.work_cap);
     for (uint32_t idx = blockIdx.x; idx < cnt; idx += gridDim.x) {
-        const uint32_t ai = a.work[idx];
-        const uint32_t o0 = a.off[ai];
-        const int m = (int)(a.off[ai + 1] - o0);
+        const RowRef r = locate_row(a.bk, a.work[idx]);
+        const int m = (int)r.m;
         if (m <= kExactRegSteps) continue;
-        int tf = warp_exact_T(a.pstep, (int)a.n, a.lstep + o0, m, false, scratch);
+        int tf = warp_exact_T(a.pstep, (int)a.n, r.ptr, m, false, scratch);
         __syncwarp();
-        int tr = warp_exact_T(a.pstep, (int)a.n, a.lstep + o0, m, true, scratch);
+        int tr = warp_exact_T(a.pstep, (int)a.n, r.ptr, m, true, scratch);
         __syncwarp();
         if ((threadIdx.x & 31) == 0) {
+            const uint32_t ai = a.bk.perm[r.sorted];
             if (a.t_fw) a.t_fw[ai] = tf;
             if (a.t_rc) a.t_rc[ai] = tr;
             const int best = tf > tr ? tf : tr;
@@ -575,13 +793,21 @@ int configure_kernels() {
     return 0;
 }
 
-void launch_localize_steps(const uint32_t *steps, const uint32_t *node2local, uint16_t *lstep,
-                           uint64_t S, cudaStream_t st) {
-    if (S == 0) return;
-    uint64_t blocks = ((S >> 2) + kBlock - 1) / kBlock;
-    if (blocks < 1) blocks = 1;
-    if (blocks > 148 * 16) blocks = 148 * 16;
-    localize_steps_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(steps, node2local, lstep, S);
+void launch_length_histogram(const uint32_t *off, uint64_t A, uint32_t *hist, cudaStream_t st) {
+    if (A == 0) return;
+    uint64_t blocks = (A + kBlock - 1) / kBlock;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    length_histogram_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(off, A, hist);
+}
+
+void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local,
+                           uint64_t A, const Buckets &bk, uint16_t *bstep, uint2 *ldesc,
+                           uint32_t *perm, uint32_t *cursors, cudaStream_t st) {
+    if (A == 0) return;
+    uint64_t blocks = (A + kBlock - 1) / kBlock;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    bucket_scatter_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(off, steps, node2local, A, bk, bstep,
+                                                               ldesc, perm, cursors);
 }
 
 void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, uint32_t n_nodes,
@@ -593,14 +819,14 @@ void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, u
 }
 
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
-                         uint32_t tab_stride, uint16_t *ptab, cudaStream_t st) {
+                         uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, cudaStream_t st) {
     if (P == 0) return;
-    build_tables_kernel<<<P, kBlock, (size_t)(L + 1) * sizeof(uint32_t), st>>>(poff, pstep, L,
-                                                                                tab_stride, ptab);
+    build_tables_kernel<<<P, kBlock, (size_t)(L + 1) * sizeof(uint32_t), st>>>(
+        poff, pstep, L, tab_stride, ptab, pnext);
 }
 
 void launch_score_paths(const ScoreArgs &a, int sm_count, cudaStream_t st) {
-    if (a.P == 0 || a.A == 0) return;
+    if (a.P == 0) return;
     const size_t smem = score_smem_bytes(a);
     const uint32_t chunks = (a.P + a.chunk - 1) / a.chunk;
     int per_sm = 1;
@@ -609,7 +835,7 @@ void launch_score_paths(const ScoreArgs &a, int sm_count, cudaStream_t st) {
     else
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, score_paths_kernel<false>, kBlock, smem);
     if (per_sm < 1) per_sm = 1;
-    const uint64_t n_tiles = (a.A + kBlock - 1) / kBlock;
+    const uint64_t n_tiles = a.bk.tile_start[kNumBuckets];
     // resident CTAs = a multiple of the SM count; split between tile workers (x) and chunks (y)
     uint64_t gx = ((uint64_t)sm_count * per_sm + chunks - 1) / chunks;
     if (gx > n_tiles) gx = n_tiles;
@@ -628,10 +854,10 @@ void launch_exact_worklist_long(const ScoreArgs &a, uint32_t max_m, cudaStream_t
 }
 
 void launch_pair_classify(const PairArgs &a, int sm_count, cudaStream_t st) {
-    if (a.A == 0) return;
-    const uint64_t n_tiles = (a.A + kBlock - 1) / kBlock;
+    const uint64_t n_tiles = a.bk.tile_start[kNumBuckets];
     uint64_t gx = (uint64_t)sm_count * 8;
     if (gx > n_tiles) gx = n_tiles;
+    if (gx < 1) gx = 1;
     pair_classify_kernel<<<(unsigned)gx, kBlock, (size_t)a.tab_entries * 2, st>>>(a);
 }
 

@@ -81,7 +81,7 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
                     uint32_t P, int filter, uint32_t *counts);
 
 /* Same with every buffer already on the device and no host synchronisation: work is enqueued on
- * `cuda_stream` (a cudaStream_t; NULL = the engine's stream).  d_counts (P x 2, uint32) is zeroed
+ * `cuda_stream` (a cudaStream_t; NULL = the CUDA default stream).  d_counts (P x 2, uint32) is zeroed
  * and filled by the enqueued work, so a collective (NCCL all-reduce over alignment shards) can
  * be enqueued right behind it on the same stream. */
 int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
@@ -167,10 +167,18 @@ typedef struct gfe_counters {
     uint64_t h2d_bytes, d2h_bytes;
 } gfe_counters;
 int gfe_get_counters(const gfe_engine *e, gfe_counters *out);
+/* After the *_device entry points (which do not synchronise): waits for the device and reports
+ * sticky flags of the enqueued work — bit0: a candidate path named a node outside the universe,
+ * bit1: the exact-DP worklist overflowed (results of that batch are incomplete; re-run it through
+ * gfe_score_paths, which grows the list and retries by itself). */
+int gfe_device_status(gfe_engine *e, uint32_t *flags);
 /* Milliseconds the last scoring / edge-support call spent in its dominant kernel (CUDA events on
  * the engine's stream); 0 if timing was not enabled with gfe_set_timing(e, 1). */
 int gfe_set_timing(gfe_engine *e, int enabled);
 float gfe_last_kernel_ms(const gfe_engine *e);
+/* Synchronises the device, sums the CUDA-event durations of every dominant-kernel launch timed
+ * since the previous call (any stream the launches were enqueued on) and resets the record. */
+int gfe_kernel_time_stats(gfe_engine *e, double *total_ms, uint32_t *launches);
 
 #ifdef __cplusplus
 }
