@@ -62,13 +62,14 @@ class _Counters(C.Structure):
 
 
 _ROW_FN = C.CFUNCTYPE(None, C.POINTER(_SearchRow), C.c_void_p)
+_SCORE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, _u32p, _u32p, C.c_uint32, _u32p)
 
 # every symbol include/gfalign_b200.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "gfe_create", "gfe_destroy", "gfe_last_error", "gfe_version", "gfe_set_alignments",
     "gfe_set_alignments_device", "gfe_set_universe", "gfe_score_paths", "gfe_score_paths_device",
     "gfe_score_pairs", "gfe_edge_support", "gfe_edge_traversals_device",
-    "gfe_edge_weights_from_counts", "gfe_search", "gfe_get_counters", "gfe_set_timing",
+    "gfe_edge_weights_from_counts", "gfe_search", "gfe_search_with_scorer", "gfe_get_counters", "gfe_set_timing",
     "gfe_last_kernel_ms", "gfe_kernel_time_stats", "gfe_device_status",
 ]
 
@@ -106,6 +107,9 @@ def load_library() -> C.CDLL:
     lib.gfe_edge_weights_from_counts.argtypes = [_u32p, _u32p, C.c_uint32, _u32p, _u32p]
     lib.gfe_search.argtypes = [C.c_void_p, C.POINTER(_Graph), C.POINTER(_SearchParams), _ROW_FN,
                                C.c_void_p, C.POINTER(_SearchStats)]
+    lib.gfe_search_with_scorer.argtypes = [_SCORE_FN, C.c_void_p, C.POINTER(_Graph),
+                                           C.POINTER(_SearchParams), _ROW_FN, C.c_void_p,
+                                           C.POINTER(_SearchStats)]
     lib.gfe_get_counters.argtypes = [C.c_void_p, C.POINTER(_Counters)]
     lib.gfe_set_timing.argtypes = [C.c_void_p, C.c_int]
     lib.gfe_last_kernel_ms.argtypes = [C.c_void_p]
@@ -251,28 +255,10 @@ class Engine:
                min_nodes: int = 0, return_all_paths: bool = False, speculate: int = 0,
                on_row: Optional[Callable[[SearchRow], None]] = None):
         """dijkstra() of the reference on packed inputs -> (rows, stats dict)."""
-        ao, at = _u32(adj_offsets), _u32(adj_target)
-        o0 = np.ascontiguousarray(adj_or0, dtype=np.uint8)
-        o1 = np.ascontiguousarray(adj_or1, dtype=np.uint8)
-        bn, bc = _u32(budget_nodes), _u32(budget_counts)
-        g = _Graph(ao.size - 1, _ptr(ao), _ptr(at), _ptr(o0, _u8p), _ptr(o1, _u8p))
-        p = _SearchParams(source, destination, _ptr(bn), _ptr(bc), bn.size, node_count, max_steps,
-                          min_nodes, int(return_all_paths), speculate)
-        rows: List[SearchRow] = []
-
-        def _cb(rp, _user):
-            r = rp.contents
-            row = SearchRow(r.path_counter, r.bad, r.good, r.alt, r.size, r.uniques,
-                            bool(r.hamiltonian), [r.steps[i] for i in range(r.size)])
-            rows.append(row)
-            if on_row:
-                on_row(row)
-
-        cb = _ROW_FN(_cb)
-        st = _SearchStats()
-        self._check(self._lib.gfe_search(self._h, C.byref(g), C.byref(p), cb, None, C.byref(st)))
-        stats = {f: getattr(st, f) for f, _ in _SearchStats._fields_}
-        return rows, stats
+        return _run_search(lambda g, p, cb, st: self._check(
+            self._lib.gfe_search(self._h, g, p, cb, None, st)),
+            adj_offsets, adj_target, adj_or0, adj_or1, source, destination, budget_nodes,
+            budget_counts, node_count, max_steps, min_nodes, return_all_paths, speculate, on_row)
 
     # -- introspection -----------------------------------------------------------------------
     def counters(self) -> dict:
@@ -300,6 +286,71 @@ class Engine:
 
     # set_alignments records A so score_pairs can size its outputs
     _A_hint = 0
+
+
+def _run_search(call, adj_offsets, adj_target, adj_or0, adj_or1, source, destination,
+                budget_nodes, budget_counts, node_count, max_steps, min_nodes, return_all_paths,
+                speculate, on_row):
+    ao, at = _u32(adj_offsets), _u32(adj_target)
+    o0 = np.ascontiguousarray(adj_or0, dtype=np.uint8)
+    o1 = np.ascontiguousarray(adj_or1, dtype=np.uint8)
+    bn, bc = _u32(budget_nodes), _u32(budget_counts)
+    g = _Graph(ao.size - 1, _ptr(ao), _ptr(at), _ptr(o0, _u8p), _ptr(o1, _u8p))
+    p = _SearchParams(source, destination, _ptr(bn), _ptr(bc), bn.size, node_count, max_steps,
+                      min_nodes, int(return_all_paths), speculate)
+    rows: List[SearchRow] = []
+
+    def _cb(rp, _user):
+        r = rp.contents
+        row = SearchRow(r.path_counter, r.bad, r.good, r.alt, r.size, r.uniques,
+                        bool(r.hamiltonian), [r.steps[i] for i in range(r.size)])
+        rows.append(row)
+        if on_row:
+            on_row(row)
+
+    cb = _ROW_FN(_cb)
+    st = _SearchStats()
+    call(C.byref(g), C.byref(p), cb, C.byref(st))
+    stats = {f: getattr(st, f) for f, _ in _SearchStats._fields_}
+    return rows, stats
+
+
+def search_with_scorer(scorer: Callable[[np.ndarray, np.ndarray], np.ndarray], adj_offsets,
+                       adj_target, adj_or0, adj_or1, source: int, destination: int, budget_nodes,
+                       budget_counts, node_count: int, max_steps: int = 100000, min_nodes: int = 0,
+                       return_all_paths: bool = False, speculate: int = 0,
+                       on_row: Optional[Callable[[SearchRow], None]] = None):
+    """gfe_search_with_scorer: the reference's dijkstra() replay with evaluatePath answered by
+    `scorer(path_offsets, path_steps) -> (P, 2) uint32 (bad, good)` — e.g. alignment shards on
+    several GPUs summed with one all-reduce.  Needs no CUDA device by itself."""
+    lib = load_library()
+    failure = []
+
+    def _score(_user, po, ps, P, counts):
+        try:
+            off = np.ctypeslib.as_array(po, shape=(P + 1,)).copy()
+            st = np.ctypeslib.as_array(ps, shape=(int(off[-1]),)).copy()
+            out = np.ascontiguousarray(scorer(off, st), dtype=np.uint32).reshape(-1)
+            if out.size != 2 * P:
+                raise ValueError("scorer must return P x 2 counts")
+            C.memmove(counts, out.ctypes.data, out.nbytes)
+            return 0
+        except Exception as exc:  # surfaced after the C call returns
+            failure.append(exc)
+            return -2
+
+    fn = _SCORE_FN(_score)
+
+    def call(g, p, cb, st):
+        rc = lib.gfe_search_with_scorer(fn, None, g, p, cb, None, st)
+        if failure:
+            raise failure[0]
+        if rc != 0:
+            raise GfeError(rc, "gfe_search_with_scorer failed")
+
+    return _run_search(call, adj_offsets, adj_target, adj_or0, adj_or1, source, destination,
+                       budget_nodes, budget_counts, node_count, max_steps, min_nodes,
+                       return_all_paths, speculate, on_row)
 
 
 _orig_set = Engine.set_alignments

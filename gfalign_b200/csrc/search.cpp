@@ -183,7 +183,8 @@ struct PathNode {
 };
 
 struct Driver {
-    gfe_engine *eng;
+    gfe_score_fn score;
+    void *score_user;
     const gfe_graph *g;
     const gfe_search_params *prm;
     std::vector<PathNode> T;
@@ -301,7 +302,7 @@ struct Driver {
             const uint32_t P = (uint32_t)b_nodes.size();
             b_counts.resize((size_t)P * 2);
             auto t0 = std::chrono::steady_clock::now();
-            rc = gfe_score_paths(eng, b_off.data(), b_steps.data(), P, 1, b_counts.data());
+            rc = score(score_user, b_off.data(), b_steps.data(), P, b_counts.data());
             st.seconds_scoring +=
                 std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
             st.kernel_batches++;
@@ -328,13 +329,13 @@ struct Driver {
 
 }  // namespace
 
-extern "C" int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_params *p,
-                          gfe_row_fn emit, void *user, gfe_search_stats *stats) {
-    if (!e || !g || !p || !g->adj_offsets) return GFE_ERR_ARG;
-    if (p->source >= g->n_nodes || p->destination >= g->n_nodes) return GFE_ERR_ARG;
+static int run_search(gfe_score_fn score, void *score_user, const gfe_graph *g,
+                      const gfe_search_params *p, gfe_row_fn emit, void *user,
+                      gfe_search_stats *stats) {
     const auto t_begin = std::chrono::steady_clock::now();
     Driver d;
-    d.eng = e;
+    d.score = score;
+    d.score_user = score_user;
     d.g = g;
     d.prm = p;
     d.budget.assign(g->n_nodes, 0);
@@ -343,15 +344,6 @@ extern "C" int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_pa
         if (p->budget_nodes[i] >= g->n_nodes) return GFE_ERR_ARG;
         d.budget[p->budget_nodes[i]] = p->budget_counts[i];
     }
-    // universe = every node that owns a NodeTable record (nodelist + source + destination)
-    {
-        std::vector<uint32_t> uni;
-        for (uint32_t v = 0; v < g->n_nodes; ++v)
-            if (d.budget[v] || v == p->source || v == p->destination) uni.push_back(v);
-        int rc = gfe_set_universe(e, uni.data(), (uint32_t)uni.size());
-        if (rc != GFE_OK) return rc;
-    }
-
     OrderHeap Q;
     PathNode root;
     root.parent = kNoParent;
@@ -432,4 +424,46 @@ extern "C" int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_pa
         std::chrono::duration<double>(std::chrono::steady_clock::now() - t_begin).count();
     if (stats) *stats = d.st;
     return rc;
+}
+
+static int engine_scorer(void *user, const uint32_t *path_offsets, const uint32_t *path_steps,
+                         uint32_t P, uint32_t *counts) {
+    return gfe_score_paths(static_cast<gfe_engine *>(user), path_offsets, path_steps, P, 1, counts);
+}
+
+static int check_search_args(const gfe_graph *g, const gfe_search_params *p) {
+    if (!g || !p || !g->adj_offsets) return GFE_ERR_ARG;
+    if (p->source >= g->n_nodes || p->destination >= g->n_nodes) return GFE_ERR_ARG;
+    for (uint32_t i = 0; i < p->n_budget; ++i)
+        if (p->budget_nodes[i] >= g->n_nodes) return GFE_ERR_ARG;
+    return GFE_OK;
+}
+
+extern "C" int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_params *p,
+                          gfe_row_fn emit, void *user, gfe_search_stats *stats) {
+    if (!e) return GFE_ERR_ARG;
+    int rc = check_search_args(g, p);
+    if (rc != GFE_OK) return rc;
+    // universe = every node that owns a NodeTable record (nodelist + source + destination)
+    std::vector<uint32_t> uni;
+    {
+        std::vector<uint8_t> in(g->n_nodes, 0);
+        for (uint32_t i = 0; i < p->n_budget; ++i)
+            if (p->budget_counts[i]) in[p->budget_nodes[i]] = 1;
+        in[p->source] = in[p->destination] = 1;
+        for (uint32_t v = 0; v < g->n_nodes; ++v)
+            if (in[v]) uni.push_back(v);
+    }
+    rc = gfe_set_universe(e, uni.data(), (uint32_t)uni.size());
+    if (rc != GFE_OK) return rc;
+    return run_search(engine_scorer, e, g, p, emit, user, stats);
+}
+
+extern "C" int gfe_search_with_scorer(gfe_score_fn score, void *score_user, const gfe_graph *g,
+                                      const gfe_search_params *p, gfe_row_fn emit, void *user,
+                                      gfe_search_stats *stats) {
+    if (!score) return GFE_ERR_ARG;
+    int rc = check_search_args(g, p);
+    if (rc != GFE_OK) return rc;
+    return run_search(score, score_user, g, p, emit, user, stats);
 }

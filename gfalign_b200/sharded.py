@@ -1,0 +1,81 @@
+"""Alignment shards over the GPUs of one box (one process per GPU, torch.distributed).
+
+The hot path shards by alignment: every rank keeps a contiguous range of the CSR in its own HBM,
+scores the same batch of candidate paths against it, and the small P x {bad, good} record is
+summed with ONE all-reduce (NCCL over NVLink on GPUs; gloo in the CPU tests).  Integer addition
+commutes, so the result is bit-identical to the single-GPU one.  The search itself is not
+sharded: every rank replays the same canonical heap (reference src/eval.cpp:134-189) on the same
+summed counts, so all ranks stay in lock step and emit the same rows.
+
+evalGFA shards the same way: per-rank traversal counters (2 per L line), one all-reduce, then the
+reference's 2k-1 hairpin rule on the summed counters.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Tuple
+
+import numpy as np
+
+from . import capi
+
+
+def shard_bounds(offsets: np.ndarray, world: int) -> np.ndarray:
+    """Row boundaries (world+1) of contiguous shards balanced on streamed bytes (m + 1 words per
+    row).  Deterministic; empty shards are legal."""
+    offsets = np.asarray(offsets, dtype=np.int64)
+    A = offsets.size - 1
+    cost = offsets[1:] + np.arange(1, A + 1, dtype=np.int64)      # prefix of (m + 1)
+    total = int(cost[-1]) if A else 0
+    cuts = [0]
+    for r in range(1, world):
+        cuts.append(int(np.searchsorted(cost, total * r / world, side="left")) if A else 0)
+    cuts.append(A)
+    return np.maximum.accumulate(np.array(cuts, dtype=np.int64))
+
+
+def take_shard(offsets: np.ndarray, steps: np.ndarray, lo: int, hi: int) -> Tuple[np.ndarray, np.ndarray]:
+    o = np.asarray(offsets[lo:hi + 1], dtype=np.int64)
+    return (o - o[0]).astype(np.uint32), np.ascontiguousarray(steps[int(o[0]):int(o[-1])], dtype=np.uint32)
+
+
+class ShardedScorer:
+    """scorer(path_offsets, path_steps) -> summed (P, 2) counts over all ranks of `group`.
+
+    `local` scores the batch against this rank's shard: Engine.score_paths on a GPU rank.  With
+    `device` set (a torch cuda device) the counts travel as a device tensor (NCCL)."""
+
+    def __init__(self, local: Callable[[np.ndarray, np.ndarray], np.ndarray], group=None, device=None):
+        import torch.distributed as dist
+        self.local, self.group, self.device, self.dist = local, group, device, dist
+        self.calls = 0
+
+    def __call__(self, path_offsets: np.ndarray, path_steps: np.ndarray) -> np.ndarray:
+        import torch
+        counts = np.ascontiguousarray(self.local(path_offsets, path_steps), dtype=np.uint32)
+        t = torch.from_numpy(counts.astype(np.int64))
+        if self.device is not None:
+            t = t.to(self.device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM, group=self.group)
+        self.calls += 1
+        return t.cpu().numpy().astype(np.uint32)
+
+
+def sharded_search(scorer: ShardedScorer, tangle, nodes, counts, node_count, **kw):
+    """`gfalign search` over sharded alignments: identical rows on every rank."""
+    return capi.search_with_scorer(scorer, tangle.adj_offsets, tangle.adj_target, tangle.adj_or0,
+                                   tangle.adj_or1, tangle.source, tangle.destination, nodes, counts,
+                                   node_count, **kw)
+
+
+def sharded_edge_support(local_traversals: Callable[[], np.ndarray], edge_from, edge_to,
+                         group=None, device=None) -> np.ndarray:
+    """`local_traversals()` -> this rank's 2*E raw traversal counters (slot 2i = events equal to L
+    line i, 2i+1 = its reverse complement; gfe_edge_traversals_device).  Returns RC:i weights."""
+    import torch
+    import torch.distributed as dist
+    c = np.ascontiguousarray(local_traversals(), dtype=np.uint32)
+    t = torch.from_numpy(c.astype(np.int64))
+    if device is not None:
+        t = t.to(device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return capi.Engine.edge_weights_from_counts(edge_from, edge_to, t.cpu().numpy().astype(np.uint32))

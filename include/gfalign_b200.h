@@ -160,6 +160,18 @@ typedef struct gfe_search_stats {
 int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_params *p, gfe_row_fn emit,
                void *user, gfe_search_stats *stats);
 
+/* The same driver with the evaluatePath calls answered by a caller-supplied backend: `score`
+ * receives a batch of P candidate paths (CSR, oriented steps) and must fill counts[2p] = bad,
+ * counts[2p+1] = good exactly as gfe_score_paths(filter = 1) would; non-zero return aborts the
+ * search with that status.  This is the seam for alignment tables sharded over several engines /
+ * GPUs (score every shard, sum the counts: one all-reduce) — the emission order stays that of
+ * the single canonical heap replay (reference src/eval.cpp:134-189). */
+typedef int (*gfe_score_fn)(void *score_user, const uint32_t *path_offsets,
+                            const uint32_t *path_steps, uint32_t P, uint32_t *counts);
+int gfe_search_with_scorer(gfe_score_fn score, void *score_user, const gfe_graph *g,
+                           const gfe_search_params *p, gfe_row_fn emit, void *user,
+                           gfe_search_stats *stats);
+
 /* ---- introspection (bench / tests) --------------------------------------------------------------*/
 typedef struct gfe_counters {
     uint64_t kernel_launches;     /* kernels of this library launched since gfe_create */

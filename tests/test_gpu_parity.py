@@ -95,3 +95,117 @@ def test_edge_support_hairpins_random(engine, oracle):
     got = engine.edge_support(ef, et)
     want = oracle.edge_support(off, steps, 4, ef, et)
     assert np.array_equal(got, want)
+
+
+# ---- against the golden fixtures generated from the compiled reference --------------------------
+
+def _cases():
+    import gzip, json, os
+    p = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cli.json.gz")
+    with gzip.open(p, "rt") as f:
+        return json.load(f)["cases"]
+
+
+def test_golden_search_rows(engine):
+    """gfe_search (CUDA-scored) reproduces the reference CLI's emitted rows, in order."""
+    from test_oracle import _search_inputs, search_rows_text
+    seen = 0
+    for c in _cases():
+        if "_search" not in c["name"]:
+            continue
+        t, off, st, kw = _search_inputs(c)
+        nodes, counts, node_count = synth.node_table(t)
+        engine.set_alignments(off, st, t.n_nodes)
+        for spec in (0, 1, 1024):
+            rows, stats = engine.search(t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source,
+                                        t.destination, nodes, counts, node_count, speculate=spec, **kw)
+            assert search_rows_text(rows, stats, t.names, kw) == c["stdout"].splitlines(), (c["name"], spec)
+        seen += 1
+    assert seen >= 13
+
+
+def test_golden_evalpath_scores(engine):
+    from gfalign_b200 import textio
+    from test_oracle import _evalpath_expect
+    seen = 0
+    for c in _cases():
+        if "_evalpath_" not in c["name"]:
+            continue
+        gfa = next(v for k, v in c["files"].items() if k.endswith(".gfa"))
+        gaf = next(v for k, v in c["files"].items() if k.endswith(".gaf"))
+        names, _, _ = textio.parse_gfa(gfa)
+        _, off, st = textio.parse_gaf(gaf, names)
+        path = textio.parse_path(c["args"][c["args"].index("-p") + 1], names)
+        engine.set_alignments(off, st, len(names))
+        tf, tr, bad, good = engine.score_pairs(path, filter=False)
+        scores, totals = _evalpath_expect(c)
+        assert np.maximum(tf, tr).tolist() == scores, c["name"]
+        uniques = len(set((path >> 1).tolist()))
+        assert [bad, good, bad - good - uniques, path.size, uniques] == totals, c["name"]
+        seen += 1
+    assert seen >= 18
+
+
+def test_golden_evalgfa_weights(engine):
+    from gfalign_b200 import textio
+    seen = 0
+    for c in _cases():
+        if not c["name"].endswith("_evalgfa"):
+            continue
+        gfa = next(v for k, v in c["files"].items() if k.endswith(".gfa"))
+        gaf = next(v for k, v in c["files"].items() if k.endswith(".gaf"))
+        names, ef, et = textio.parse_gfa(gfa)
+        _, off, st = textio.parse_gaf(gaf, names)
+        engine.set_alignments(off, st, len(names))
+        want = [int(l.split("RC:i:")[1].split("\t")[0]) for l in c["out_L_lines"]]
+        assert engine.edge_support(ef, et).tolist() == want, c["name"]
+        seen += 1
+    assert seen >= 6
+
+
+def test_empty_and_ragged_inputs(engine, oracle):
+    # no alignments at all; alignments without steps; a single-step path
+    engine.set_alignments(np.zeros(1, np.uint32), np.zeros(0, np.uint32), 4)
+    engine.set_universe(np.arange(4, dtype=np.uint32))
+    po, ps = np.array([0, 1, 3], np.uint32), np.array([0, 2, 5], np.uint32)
+    assert engine.score_paths(po, ps).tolist() == [[0, 0], [0, 0]]
+    off = np.array([0, 0, 2, 2, 3], np.uint32)
+    st = np.array([2, 5, 0], np.uint32)
+    engine.set_alignments(off, st, 4)
+    engine.set_universe(np.arange(4, dtype=np.uint32))
+    for filt in (True, False):
+        assert np.array_equal(engine.score_paths(po, ps, filter=filt),
+                              oracle.evaluate_paths(po, ps, off, st, filt, 1))
+    assert engine.edge_support(np.zeros(0, np.uint32), np.zeros(0, np.uint32)).size == 0
+
+
+def test_limits_rejected(engine):
+    import gfalign_b200
+    engine.set_alignments(np.array([0, 1], np.uint32), np.array([0], np.uint32), 2)
+    engine.set_universe(np.arange(2, dtype=np.uint32))
+    long_path = np.zeros(1001, np.uint32)
+    with pytest.raises(gfalign_b200.GfeError):
+        engine.score_paths(np.array([0, 1001], np.uint32), long_path)
+    with pytest.raises(gfalign_b200.GfeError):
+        engine.set_alignments(np.array([0, 1001], np.uint32), np.zeros(1001, np.uint32), 2)
+    with pytest.raises(gfalign_b200.GfeError):   # node outside the universe
+        engine.set_alignments(np.array([0, 1], np.uint32), np.array([0], np.uint32), 4)
+        engine.set_universe(np.array([0, 1], np.uint32))
+        engine.score_paths(np.array([0, 1], np.uint32), np.array([6], np.uint32))
+
+
+def test_max_size_path_evalpath(engine, oracle):
+    """n = 1000 (the reference's MAX_N - 1) x alignments up to 40 steps, scores bit-exact."""
+    rng = np.random.default_rng(3)
+    n_nodes = 600
+    path = (rng.permutation(n_nodes)[:500].repeat(2)[:1000] * 2 + rng.integers(0, 2, 1000)).astype(np.uint32)
+    off, steps = _rand_csr(rng, 3000, n_nodes, [1, 2, 3, 5, 8, 40])
+    # plant sub-walks of the path so occurrences and near-occurrences exist
+    for a in range(0, 3000, 3):
+        m = off[a + 1] - off[a]
+        s = int(rng.integers(0, 1000 - m))
+        steps[off[a]:off[a + 1]] = path[s:s + m] if a % 2 else (path[s:s + m][::-1] ^ 1)
+    engine.set_alignments(off, steps, n_nodes)
+    tf, tr, bad, good = engine.score_pairs(path)
+    ob, og, otf, otr = oracle.evaluate_path(path, off, steps, False, scores=True)
+    assert np.array_equal(tf, otf) and np.array_equal(tr, otr) and (bad, good) == (ob, og)
