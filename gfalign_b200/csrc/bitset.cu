@@ -1,0 +1,322 @@
+// gfalign_b200/csrc/bitset.cu — K1: score_bitset, the path x alignment scoring kernel of
+// `gfalign search` (evaluatePath with the id filter, reference src/eval.cpp:67-108) in bit-parallel
+// form: one machine word carries the verdict of 32 candidate paths.
+//
+// Per batch the host side (build_tables_kernel) turns the candidate paths into bitsets over the
+// paths of a chunk (32*W paths, W words per entry), resident in shared memory for the whole kernel:
+//   N[v]  paths that contain node v                      (the id filter, src/eval.cpp:81-91)
+//   T[v]  paths that visit node v more than once         (NodeTable counts > 1)
+//   F[v]  paths whose first node is v
+//   LM[m] paths shorter than m steps                     (m > n: always good, SURVEY.md A.3 rule 1)
+//   M[q]  paths that take the oriented pair q = (x -> y) consecutively; q^1 = its reverse complement
+// An alignment B = b_0..b_{m-1} is stored as its m local steps followed by the ids of its m-1
+// consecutive pairs.  For the 32 paths of one word:
+//   pass = AND_j N[b_j]                      every node on the path
+//   cand = AND_j M[q_j]  |  AND_j M[q_j^1]   every pair of B (or of rc(B)) is taken by the path
+// If no node of B is visited twice by the path, every node has one position and cand is exactly
+// "B or rc(B) occurs contiguously" (rule 2).  So, with spec = (cand & OR_j T[b_j]) | OR_j F[b_j]:
+//   good = pass & (LM[m] | (cand & ~OR_j T[b_j]))
+//   bad  = pass & ~LM[m] & ~cand... & ~spec          (no occurrence possible, no start overhang)
+//   slow = pass & ~LM[m] & ~good & spec              -> (path, row) worklist: visit chains, overhang
+//                                                       test and the exact DP (kernels.cu)
+// A lane owns one word (32 paths) of one row; W lanes cover a row's chunk, 32/W rows per warp step.
+// All lanes of a group read the same table entry at consecutive words: conflict-free LDS.
+// Counts are kept bit-sliced in registers (kPlanes planes per lane for good and for bad; eight rows
+// are folded with 3:2 carry-save adders before touching the planes), so the inner loop has no
+// atomics and no cross-lane traffic.  The table is brought in with one TMA bulk copy.
+#include "kernels.cuh"
+
+namespace gfe {
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+// ---- TMA 1-D bulk copy global -> shared, completion on an mbarrier ------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+// ---- bit-sliced counters -------------------------------------------------------------------------
+// 3:2 carry-save adder on 32 independent bit columns: two LOP3s.
+__device__ __forceinline__ void csa(uint32_t &sum, uint32_t &carry, uint32_t a, uint32_t b, uint32_t c) {
+    const uint32_t u = a ^ b;
+    carry = (a & b) | (u & c);
+    sum = u ^ c;
+}
+
+struct Planes {
+    uint32_t p[kPlanes];
+    __device__ __forceinline__ void clear() {
+#pragma unroll
+        for (int k = 0; k < kPlanes; ++k) p[k] = 0;
+    }
+    // add eight 1-bit-per-column masks
+    __device__ __forceinline__ void add8(const uint32_t (&x)[8]) {
+        uint32_t c0, c1, c2, c3, d0, d1, e0;
+        csa(p[0], c0, p[0], x[0], x[1]);
+        csa(p[0], c1, p[0], x[2], x[3]);
+        csa(p[0], c2, p[0], x[4], x[5]);
+        csa(p[0], c3, p[0], x[6], x[7]);
+        csa(p[1], d0, p[1], c0, c1);
+        csa(p[1], d1, p[1], c2, c3);
+        csa(p[2], e0, p[2], d0, d1);
+#pragma unroll
+        for (int k = 3; k < kPlanes; ++k) {   // ripple the weight-8 carry
+            const uint32_t t = p[k] & e0;
+            p[k] ^= e0;
+            e0 = t;
+        }
+    }
+    // column c of the counter
+    __device__ __forceinline__ uint32_t value(int c) const {
+        uint32_t v = 0;
+#pragma unroll
+        for (int k = 0; k < kPlanes; ++k) v |= ((p[k] >> c) & 1u) << k;
+        return v;
+    }
+};
+
+__device__ __forceinline__ int unit_bucket(const Buckets &bk, uint32_t unit) {
+    int b = 1;
+#pragma unroll
+    for (int k = 2; k <= kMaxBucket; ++k) b += (unit >= bk.unit_start[k]) ? 1 : 0;
+    return b;
+}
+
+// push the set bits of `mask` (paths word_base .. word_base+31) as (path, row) work items
+__device__ __forceinline__ void push_slow(const BitsetArgs &a, uint32_t mask, uint32_t word_base,
+                                          uint32_t sorted_row) {
+    const uint32_t n = (uint32_t)__popc(mask);
+    uint32_t idx = atomicAdd(a.work_count + 2, n);
+    while (mask) {
+        const uint32_t c = (uint32_t)__ffs(mask) - 1u;
+        mask &= mask - 1u;
+        if (idx < a.slow_cap) a.slow[idx] = make_uint2(word_base + c, sorted_row);
+        else atomicOr(a.work_count + 3, 1u);
+        ++idx;
+    }
+}
+
+// One row of length M against this lane's word.  tab = shared-memory table + lane's word offset.
+template <int M, int W>
+__device__ __forceinline__ void score_row(const BitsetArgs &a, const uint32_t *__restrict__ tab,
+                                          const uint16_t *__restrict__ rp, uint32_t lm,
+                                          uint32_t &good, uint32_t &bad, uint32_t &slow) {
+    constexpr int RS = (int)row_stride(M);
+    uint32_t q[RS / 2];   // two u16 per register
+    {
+        const uint2 *src = reinterpret_cast<const uint2 *>(rp);
+#pragma unroll
+        for (int k = 0; k < RS / 4; ++k) {
+            const uint2 t = __ldg(src + k);
+            q[2 * k] = t.x;
+            q[2 * k + 1] = t.y;
+        }
+    }
+    auto elem = [&](int i) -> uint32_t { return (i & 1) ? (q[i >> 1] >> 16) : (q[i >> 1] & 0xFFFFu); };
+    uint32_t pass = 0xFFFFFFFFu, tacc = 0, facc = 0;
+#pragma unroll
+    for (int j = 0; j < M; ++j) {
+        const uint32_t *e = tab + (elem(j) >> 1) * (3u * W);
+        pass &= e[0];
+        tacc |= e[W];
+        facc |= e[2 * W];
+    }
+    const uint32_t in = a.filter ? pass : 0xFFFFFFFFu;
+    if (M == 1) {
+        // a single step occurs (forward or reverse-complemented) iff its node is on the path
+        good = in & (lm | pass);
+        bad = in & ~(lm | pass);
+        slow = 0;
+        return;
+    }
+    uint32_t fw = 0xFFFFFFFFu, rc = 0xFFFFFFFFu;
+    const uint32_t *mt = tab + a.mg.pair_base * W;
+#pragma unroll
+    for (int j = 0; j < M - 1; ++j) {
+        const uint32_t pid = elem(M + j);
+        fw &= mt[pid * W];
+        rc &= mt[(pid ^ 1u) * W];
+    }
+    const uint32_t cand = fw | rc;
+    const uint32_t sure = cand & ~tacc;
+    const uint32_t open = in & ~lm & ~sure;
+    const uint32_t spec = (cand & tacc) | facc;
+    good = in & (lm | sure);
+    slow = open & spec;
+    bad = open & ~spec;
+}
+
+template <int M, int W>
+__device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint32_t *__restrict__ tab,
+                                           uint32_t unit, uint32_t word_base, Planes &G, Planes &B,
+                                           int lane) {
+    constexpr int R = 32 / W;                       // rows per warp step
+    constexpr int RS = (int)row_stride(M);
+    const uint32_t row0 = (unit - a.bk.unit_start[M]) * (uint32_t)kUnit;
+    const uint32_t nrows = min((uint32_t)kUnit, a.bk.count[M] - row0);
+    const uint16_t *base = a.bk.bstep + a.bk.step_base[M] + (size_t)row0 * RS;
+    const uint32_t sorted0 = a.bk.row_start[M] + row0;
+    const uint32_t lm = tab[(a.mg.lm_base + M) * W];
+    const uint32_t sub = (uint32_t)lane / W;
+    for (uint32_t it = 0; it < nrows; it += 8 * R) {
+        uint32_t gm[8], bm[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            gm[u] = 0;
+            bm[u] = 0;
+            if (it + u * R >= nrows) continue;      // warp-uniform
+            const uint32_t r = it + u * R + sub;
+            const bool valid = r < nrows;
+            uint32_t good, bad, slow;
+            score_row<M, W>(a, tab, base + (size_t)(valid ? r : 0u) * RS, lm, good, bad, slow);
+            if (valid) {
+                gm[u] = good;
+                bm[u] = bad;
+                if (slow) push_slow(a, slow, word_base, sorted0 + r);
+            }
+        }
+        G.add8(gm);
+        B.add8(bm);
+    }
+}
+
+template <int W>
+__global__ void __launch_bounds__(kBitThreads, 1)
+score_bitset_kernel(const BitsetArgs a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint32_t *s_tab = reinterpret_cast<uint32_t *>(smem);
+    const uint32_t tab_words = a.mg.entries * W;
+    uint32_t *s_cnt = s_tab + tab_words;                       // 32*W paths x {bad, good}
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_cnt + 64 * W);
+    __shared__ uint32_t s_unit[kBitThreads / 32];
+
+    const uint32_t chunk = blockIdx.y;
+    const uint32_t p_base = chunk * 32u * W;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) mbar_init(s_bar, 1);
+    for (uint32_t i = threadIdx.x; i < 64u * W; i += blockDim.x) s_cnt[i] = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // one TMA bulk copy per <= 64 KB slice of this chunk's table
+        const uint32_t bytes = tab_words * 4u;
+        const unsigned char *src =
+            reinterpret_cast<const unsigned char *>(a.masks + (size_t)chunk * tab_words);
+        mbar_expect_tx(s_bar, bytes);
+        for (uint32_t o = 0; o < bytes; o += 65536u)
+            bulk_g2s(smem + o, src + o, min(65536u, bytes - o), s_bar);
+    }
+    mbar_wait(s_bar, 0);
+
+    const uint32_t w = (uint32_t)lane % W;
+    const uint32_t *tab = s_tab + w;
+    const uint32_t word_base = p_base + 32u * w;
+    Planes G, B;
+    G.clear();
+    B.clear();
+    uint32_t rows_acc = 0;
+    const uint32_t n_units = a.bk.unit_start[kMaxBucket + 1];
+
+    auto flush = [&]() {
+#pragma unroll 4
+        for (int c = 0; c < 32; ++c) {
+            const uint32_t g = G.value(c), b = B.value(c);
+            if (b) atomicAdd(&s_cnt[2 * (32 * w + c)], b);
+            if (g) atomicAdd(&s_cnt[2 * (32 * w + c) + 1], g);
+        }
+        G.clear();
+        B.clear();
+        rows_acc = 0;
+    };
+
+    for (;;) {
+        if (lane == 0) s_unit[warp] = atomicAdd(a.unit_ctr + chunk, 1u);
+        __syncwarp();
+        const uint32_t unit = s_unit[warp];
+        __syncwarp();
+        if (unit >= n_units) break;
+        const int b = unit_bucket(a.bk, unit);
+        switch (b) {
+#define GFE_CASE(M_) case M_: score_unit<M_, W>(a, tab, unit, word_base, G, B, lane); break;
+            GFE_CASE(1) GFE_CASE(2) GFE_CASE(3) GFE_CASE(4) GFE_CASE(5) GFE_CASE(6) GFE_CASE(7)
+            GFE_CASE(8) GFE_CASE(9) GFE_CASE(10) GFE_CASE(11) GFE_CASE(12) GFE_CASE(13)
+            GFE_CASE(14) GFE_CASE(15) GFE_CASE(16)
+#undef GFE_CASE
+            default: break;
+        }
+        rows_acc += kUnit;
+        if (rows_acc > (1u << kPlanes) - 2u * kUnit) flush();
+    }
+    flush();
+    __syncthreads();
+    // alignments without steps pass the filter and score 0 against every path: good
+    const uint32_t empty_rows = blockIdx.x == 0 ? a.bk.count[0] : 0u;
+    for (uint32_t i = threadIdx.x; i < 64u * W; i += blockDim.x) {
+        const uint32_t p = p_base + (i >> 1);
+        if (p >= a.P) continue;
+        const uint32_t v = s_cnt[i] + ((i & 1u) ? empty_rows : 0u);
+        if (v) atomicAdd(&a.counts[2 * (size_t)p_base + i], v);
+    }
+}
+
+template <int W>
+void launch_w(const BitsetArgs &a, int sm_count, cudaStream_t st) {
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(score_bitset_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(kBitsetSmemBudget + 1024));
+        configured = true;
+    }
+    const size_t smem = (size_t)a.mg.entries * W * 4 + 64 * W * 4 + 16;
+    const uint32_t chunks = (a.P + 32 * W - 1) / (32 * W);
+    uint32_t gx = (uint32_t)sm_count / chunks;
+    if (gx < 1) gx = 1;
+    const uint32_t n_units = a.bk.unit_start[kMaxBucket + 1];
+    const uint32_t max_gx = (n_units + (kBitThreads / 32) - 1) / (kBitThreads / 32);
+    if (gx > max_gx) gx = max_gx ? max_gx : 1;
+    score_bitset_kernel<W><<<dim3(gx, chunks), kBitThreads, smem, st>>>(a);
+}
+
+}  // namespace
+
+void launch_score_bitset(const BitsetArgs &a, int sm_count, cudaStream_t st) {
+    if (a.P == 0) return;
+    switch (a.mg.W) {
+        case 1: launch_w<1>(a, sm_count, st); break;
+        case 2: launch_w<2>(a, sm_count, st); break;
+        case 4: launch_w<4>(a, sm_count, st); break;
+        case 8: launch_w<8>(a, sm_count, st); break;
+        case 16: launch_w<16>(a, sm_count, st); break;
+        default: launch_w<32>(a, sm_count, st); break;
+    }
+}
+
+}  // namespace gfe

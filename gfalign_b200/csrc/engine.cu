@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <unordered_map>
 
@@ -100,6 +101,10 @@ int gfe_create(int cuda_device, gfe_engine **out) {
     gfe_engine *e = new (std::nothrow) gfe_engine();
     if (!e) return GFE_ERR_NOMEM;
     e->device = cuda_device;
+    {
+        const char *fl = getenv("GFE_FORCE_LEGACY");
+        e->force_legacy = (fl && fl[0] == '1') ? 1 : 0;
+    }
     err = cudaSetDevice(cuda_device);
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
     cudaDeviceProp prop;
@@ -157,12 +162,12 @@ int gfe_device_status(gfe_engine *e, uint32_t *flags) {
     if (!e || !flags) return GFE_ERR_ARG;
     CUDA_TRY(e, cudaSetDevice(e->device));
     CUDA_TRY(e, cudaDeviceSynchronize());
-    uint32_t err = 0, wc[2] = {0, 0};
+    uint32_t err = 0, wc[4] = {0, 0, 0, 0};
     if (e->d_err.ptr)
         CUDA_TRY(e, cudaMemcpy(&err, e->d_err.ptr, sizeof(err), cudaMemcpyDeviceToHost));
     if (e->d_work_count.ptr)
         CUDA_TRY(e, cudaMemcpy(wc, e->d_work_count.ptr, sizeof(wc), cudaMemcpyDeviceToHost));
-    *flags = (err ? 1u : 0u) | (wc[1] ? 2u : 0u);
+    *flags = (err ? 1u : 0u) | ((wc[1] || wc[3]) ? 2u : 0u);
     return GFE_OK;
 }
 
@@ -222,19 +227,23 @@ static int build_bucket_geometry(gfe_engine *e) {
     CUDA_TRY(e, cudaMemcpyAsync(hist, e->d_hist.ptr, sizeof(hist), cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     Buckets &bk = e->bk;
-    uint64_t row = 0, tile = 0, base = 0;
+    uint64_t row = 0, tile = 0, base = 0, unit = 0;
     for (int b = 0; b < kNumBuckets; ++b) {
         bk.count[b] = hist[b];
         bk.row_start[b] = (uint32_t)row;
         bk.tile_start[b] = (uint32_t)tile;
         base = (base + 7) & ~7ull;            // 16-byte aligned matrices
         bk.step_base[b] = (uint32_t)base;
+        bk.unit_start[b] = (uint32_t)unit;
         row += hist[b];
         if (b >= 1) tile += (hist[b] + kBlock - 1) / kBlock;
-        base += b == kLongBucket ? (uint64_t)hist[kNumBuckets + 1] : (uint64_t)hist[b] * b;
+        if (b >= 1 && b <= kMaxBucket) unit += (hist[b] + kUnit - 1) / kUnit;
+        base += b == kLongBucket ? (uint64_t)hist[kNumBuckets + 1]
+                                 : (uint64_t)hist[b] * row_stride(b);
     }
     bk.row_start[kNumBuckets] = (uint32_t)row;
     bk.tile_start[kNumBuckets] = (uint32_t)tile;
+    bk.unit_start[kNumBuckets] = (uint32_t)unit;
     if (base + 8 >= 0xFFFFFFFFull) {
         set_error(e, "alignment shard has too many steps for 32-bit element offsets; shard it");
         return GFE_ERR_LIMIT;
@@ -334,8 +343,40 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) 
     e->bk.bstep = e->d_bstep.ptr;
     e->bk.ldesc = e->d_ldesc.ptr;
     e->bk.perm = e->d_perm.ptr;
+    // pair dictionary: distinct in-universe consecutive pairs of the alignments.  It must leave
+    // room for the mask table of at least 32 paths in shared memory; otherwise (huge universes)
+    // the engine keeps to the position-table kernel.
+    PairDict pd{nullptr, nullptr, nullptr};
+    e->have_dict = false;
+    e->n_pairs = 0;
+    {
+        const int64_t word_budget = (int64_t)(kBitsetSmemBudget / 4) - 64 - 8;
+        int64_t max_pairs = (word_budget - 3 * ((int64_t)e->L + 1) - (kMaxBucket + 1) - 2 - 3) / 2;
+        max_pairs = std::min<int64_t>(max_pairs, 32766);
+        if (max_pairs >= 1 && !e->force_legacy) {
+            TRY(ensure_dev(e, e->d_pair_keys, kPairHashCap));
+            TRY(ensure_dev(e, e->d_pair_ids, kPairHashCap));
+            TRY(ensure_dev(e, e->d_pair_ctr, 4));
+            CUDA_TRY(e, cudaMemsetAsync(e->d_pair_keys.ptr, 0xFF, kPairHashCap * sizeof(uint32_t), e->stream));
+            CUDA_TRY(e, cudaMemsetAsync(e->d_pair_ctr.ptr, 0, 4 * sizeof(uint32_t), e->stream));
+            pd = PairDict{e->d_pair_keys.ptr, e->d_pair_ids.ptr, e->d_pair_ctr.ptr};
+            launch_pair_collect(e->d_off, e->d_steps, e->d_node2local.ptr, e->A, e->L,
+                                (uint32_t)max_pairs, pd, e->stream);
+            launch_pair_assign(pd, e->stream);
+            e->kernel_launches += (e->A ? 1 : 0) + 1;
+            uint32_t ctr[4];
+            CUDA_TRY(e, cudaMemcpyAsync(ctr, e->d_pair_ctr.ptr, sizeof(ctr), cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+            e->d2h_bytes += sizeof(ctr);
+            if (ctr[2] == 0 && ctr[0] <= (uint32_t)max_pairs) {
+                e->have_dict = true;
+                e->n_pairs = ctr[0];
+            }
+        }
+    }
     launch_bucket_scatter(e->d_off, e->d_steps, e->d_node2local.ptr, e->A, e->bk, e->d_bstep.ptr,
-                          e->d_ldesc.ptr, e->d_perm.ptr, e->d_cursors.ptr, e->stream);
+                          e->d_ldesc.ptr, e->d_perm.ptr, e->d_cursors.ptr, pd,
+                          e->have_dict ? e->n_pairs : 0xFFFFFFFFu, e->stream);
     e->kernel_launches += e->A ? 1 : 0;
     CUDA_TRY(e, cudaGetLastError());
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
@@ -373,7 +414,6 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     }
     CUDA_TRY(e, cudaMemsetAsync(d_counts, 0, (size_t)P * 2 * sizeof(uint32_t), st));
     CUDA_TRY(e, cudaMemsetAsync(e->d_work_count.ptr, 0, 4 * sizeof(uint32_t), st));
-    launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr, st);
     ScoreArgs a;
     a.bk = e->bk;
     a.poff = d_poff;
@@ -388,13 +428,75 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     a.work = e->d_work.ptr;
     a.work_count = e->d_work_count.ptr;
     a.work_cap = (uint32_t)std::min<size_t>(e->d_work.cap, 0xFFFFFFFFu);
-    if (e->timing) {
-        TRY(next_event_pair(e));
-        CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    const PairDict pd{e->d_pair_keys.ptr, e->d_pair_ids.ptr, e->d_pair_ctr.ptr};
+    const uint32_t long_lo = e->bk.tile_start[kLongBucket], long_hi = e->bk.tile_start[kNumBuckets];
+    if (e->have_dict && !e->force_legacy) {
+        // ---- bitset kernel: 32*W paths per CTA pass, mask table in shared memory ----------------
+        MaskGeom mg;
+        mg.L = e->L;
+        mg.lm_base = 3 * (e->L + 1);
+        mg.pair_base = mg.lm_base + kMaxBucket + 1;
+        mg.n_pairs = e->n_pairs;
+        mg.entries = (mg.pair_base + 2 * e->n_pairs + 2 + 3) & ~3u;
+        uint32_t W = 1;
+        while (W < 32 && 32 * W < P) W <<= 1;
+        while (W > 1 && (size_t)mg.entries * W * 4 + 64 * W * 4 + 16 > kBitsetSmemBudget) W >>= 1;
+        mg.W = W;
+        const uint32_t chunks = (P + 32 * W - 1) / (32 * W);
+        const size_t mask_words = (size_t)chunks * mg.entries * W;
+        {
+            const uint64_t want = std::min<uint64_t>(
+                std::max<uint64_t>((uint64_t)P * e->A / 64, 1u << 20), 1ull << 28);
+            if (want > e->slow_cap) e->slow_cap = (size_t)want;
+            if (e->d_slow.cap < e->slow_cap || e->d_masks.cap < mask_words ||
+                e->d_unit_ctr.cap < chunks)
+                CUDA_TRY(e, cudaStreamSynchronize(st));
+            TRY(ensure_dev(e, e->d_slow, e->slow_cap));
+            TRY(ensure_dev(e, e->d_masks, mask_words));
+            TRY(ensure_dev(e, e->d_unit_ctr, chunks));
+        }
+        CUDA_TRY(e, cudaMemsetAsync(e->d_masks.ptr, 0, mask_words * 4, st));
+        CUDA_TRY(e, cudaMemsetAsync(e->d_unit_ctr.ptr, 0, (size_t)chunks * 4, st));
+        launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr,
+                            e->d_masks.ptr, mg, pd, st);
+        BitsetArgs b;
+        b.bk = e->bk;
+        b.mg = mg;
+        b.masks = e->d_masks.ptr;
+        b.P = P;
+        b.filter = filter;
+        b.counts = d_counts;
+        b.unit_ctr = e->d_unit_ctr.ptr;
+        b.slow = e->d_slow.ptr;
+        b.work_count = e->d_work_count.ptr;
+        b.slow_cap = (uint32_t)std::min<size_t>(e->d_slow.cap, 0xFFFFFFFFu);
+        if (e->timing) {
+            TRY(next_event_pair(e));
+            CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+        }
+        launch_score_bitset(b, e->sm_count, st);
+        if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
+        e->kernel_launches += 2;
+        if (long_hi > long_lo) {   // alignments longer than kMaxBucket steps: position-table kernel
+            launch_score_paths(a, e->sm_count, long_lo, long_hi, false, st);
+            e->kernel_launches += 1;
+        }
+        if (e->A) {
+            launch_slow_worklist(a, e->d_slow.ptr, e->d_work_count.ptr + 2, b.slow_cap, st);
+            e->kernel_launches += 1;
+        }
+    } else {
+        MaskGeom mg{};
+        launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr,
+                            nullptr, mg, pd, st);
+        if (e->timing) {
+            TRY(next_event_pair(e));
+            CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+        }
+        launch_score_paths(a, e->sm_count, 0, long_hi, true, st);
+        if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
+        e->kernel_launches += 2;
     }
-    launch_score_paths(a, e->sm_count, st);
-    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
-    e->kernel_launches += 2;
     if (e->A) {
         launch_exact_worklist(a, st);
         e->kernel_launches += 1;
@@ -457,15 +559,33 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
     TRY(enqueue_score(e, d_poff, d_pstep, P, total, filter, e->d_counts.ptr, e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, (size_t)P * 2 * sizeof(uint32_t),
                                 cudaMemcpyDeviceToHost, e->stream));
-    uint32_t wc[2] = {0, 0};
-    CUDA_TRY(e, cudaMemcpyAsync(e->h_wc, e->d_work_count.ptr, 2 * sizeof(uint32_t),
+    uint32_t wc[4] = {0, 0, 0, 0};
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_wc, e->d_work_count.ptr, 4 * sizeof(uint32_t),
                                 cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-    wc[0] = e->h_wc[0];
-    wc[1] = e->h_wc[1];
+    for (int i = 0; i < 4; ++i) wc[i] = e->h_wc[i];
     if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
     e->h2d_bytes += bytes;
-    e->d2h_bytes += (size_t)P * 2 * sizeof(uint32_t) + 8;
+    e->d2h_bytes += (size_t)P * 2 * sizeof(uint32_t) + 16;
+    if (wc[3]) {
+        // the list of pairs the bitsets could not settle overflowed: grow it, or halve the batch
+        if (e->d_slow.cap < (1ull << 28)) {
+            e->slow_cap = std::min<size_t>(std::max<size_t>(e->d_slow.cap * 4, (size_t)wc[2] + 1024),
+                                           (size_t)1 << 28);
+            TRY(ensure_dev(e, e->d_slow, e->slow_cap));
+            return gfe_score_paths(e, path_offsets, path_steps, P, filter, counts);
+        }
+        if (P < 2) {
+            set_error(e, "gfe_score_paths: work list overflow on a single path");
+            return GFE_ERR_LIMIT;
+        }
+        const uint32_t h = P / 2;
+        std::vector<uint32_t> off2(path_offsets + h, path_offsets + P + 1);
+        for (uint32_t &o : off2) o -= path_offsets[h];
+        TRY(gfe_score_paths(e, path_offsets, path_steps, h, filter, counts));
+        return gfe_score_paths(e, off2.data(), path_steps + path_offsets[h], P - h, filter,
+                               counts + 2 * (size_t)h);
+    }
     if (wc[1]) {
         // the exact-DP worklist overflowed: grow it and redo the batch (never silently wrong)
         e->work_cap = std::max<size_t>(e->d_work.cap * 2, (size_t)wc[0] + 1024);
@@ -555,7 +675,12 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
     CUDA_TRY(e, cudaMemsetAsync(e->d_counts.ptr, 0, 2 * sizeof(uint32_t), st));
     CUDA_TRY(e, cudaMemsetAsync(e->d_work_count.ptr, 0, 4 * sizeof(uint32_t), st));
     TRY(ensure_dev(e, e->d_pnext, (size_t)n + 8));
-    launch_build_tables(d_poff, d_pstep, 1, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr, st);
+    {
+        MaskGeom mg{};
+        PairDict pd{nullptr, nullptr, nullptr};
+        launch_build_tables(d_poff, d_pstep, 1, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr,
+                            nullptr, mg, pd, st);
+    }
     PairArgs a;
     a.bk = e->bk;
     a.pstep = d_pstep;

@@ -49,6 +49,14 @@ struct gfe_engine {
     uint32_t L = 0, tab_stride = 8;
     bool have_universe = false;
 
+    // pair dictionary of the universe-local view + per-batch bitsets (bitset kernel)
+    DevBuf<uint32_t> d_pair_keys, d_pair_ids, d_pair_ctr, d_masks, d_unit_ctr;
+    DevBuf<uint2> d_slow;
+    uint32_t n_pairs = 0;
+    bool have_dict = false;
+    size_t slow_cap = 1u << 20;
+    int force_legacy = 0;            // GFE_FORCE_LEGACY=1: A/B runs of the pre-bitset kernel
+
     // candidate-path staging and results
     PinBuf<unsigned char> h_stage;
     DevBuf<unsigned char> d_stage;
@@ -81,6 +89,8 @@ struct gfe_engine {
         fd(d_stage.ptr); fd(d_ptab.ptr); fd(d_plocal.ptr); fd(d_pnext.ptr); fd(d_counts.ptr); fd(d_err.ptr);
         fd(d_work.ptr); fd(d_work_count.ptr); fd(d_pair_work.ptr); fd(d_tfw.ptr); fd(d_trc.ptr);
         fd(d_row_off.ptr); fd(d_edge_counts.ptr); fd(d_row_ent.ptr);
+        fd(d_pair_keys.ptr); fd(d_pair_ids.ptr); fd(d_pair_ctr.ptr); fd(d_masks.ptr);
+        fd(d_unit_ctr.ptr); fd(d_slow.ptr);
         fh(h_stage.ptr); fh(h_counts.ptr);
     }
 };

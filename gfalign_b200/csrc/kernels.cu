@@ -35,6 +35,72 @@ length_histogram_kernel(const uint32_t *__restrict__ off, uint64_t A, uint32_t *
     }
 }
 
+// Pair dictionary.  A consecutive oriented pair (x, y) of local steps and its reverse complement
+// (y^1, x^1) share one canonical key; pair id = 2*c + (key != canonical), so id^1 names the
+// reverse complement.  A self-reverse-complement pair (y == x^1) has flip 0.
+__device__ __forceinline__ uint32_t pair_canonical(uint32_t x, uint32_t y, uint32_t *flip) {
+    const uint32_t key = (x << 16) | y, twin = ((y ^ 1u) << 16) | (x ^ 1u);
+    *flip = key > twin ? 1u : 0u;
+    return key > twin ? twin : key;
+}
+__device__ __forceinline__ uint32_t pair_hash(uint32_t key) {
+    return (key * 0x9E3779B1u) >> 16;   // kPairHashCap = 2^16 slots
+}
+// slot of `key`, or kPairEmpty when absent
+__device__ __forceinline__ uint32_t pair_find(const PairDict &pd, uint32_t key) {
+    uint32_t h = pair_hash(key);
+    for (uint32_t probe = 0; probe < kPairHashCap; ++probe) {
+        const uint32_t k = __ldg(pd.keys + h);
+        if (k == key) return h;
+        if (k == kPairEmpty) return kPairEmpty;
+        h = (h + 1) & (kPairHashCap - 1);
+    }
+    return kPairEmpty;
+}
+
+// K0p: insert the canonical key of every in-universe consecutive pair of every alignment.
+__global__ void __launch_bounds__(kBlock)
+pair_collect_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ steps,
+                    const uint32_t *__restrict__ map, uint64_t A, uint32_t L, uint32_t max_pairs,
+                    const PairDict pd) {
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t a = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; a < A; a += stride) {
+        const uint32_t o0 = __ldg(off + a), o1 = __ldg(off + a + 1);
+        if (o1 - o0 < 2 || o1 - o0 > (uint32_t)kMaxBucket) continue;   // long rows: legacy kernel
+        uint32_t s = __ldg(steps + o0);
+        uint32_t x = (__ldg(map + (s >> 1)) << 1) | (s & 1u);
+        for (uint32_t k = o0 + 1; k < o1; ++k) {
+            s = __ldg(steps + k);
+            const uint32_t y = (__ldg(map + (s >> 1)) << 1) | (s & 1u);
+            if ((x >> 1) < L && (y >> 1) < L) {
+                uint32_t flip;
+                const uint32_t key = pair_canonical(x, y, &flip);
+                uint32_t h = pair_hash(key);
+                bool done = false;
+                for (uint32_t probe = 0; probe < kPairHashCap && !done; ++probe) {
+                    uint32_t cur = pd.keys[h];
+                    if (cur == kPairEmpty) {
+                        if (pd.counter[0] >= max_pairs) break;   // too many pairs: no dictionary
+                        cur = atomicCAS(pd.keys + h, kPairEmpty, key);
+                        if (cur == kPairEmpty) atomicAdd(pd.counter, 1u);
+                        done = cur == kPairEmpty || cur == key;
+                    } else {
+                        done = cur == key;
+                    }
+                    h = (h + 1) & (kPairHashCap - 1);
+                }
+                if (!done) pd.counter[2] = 1u;
+            }
+            x = y;
+        }
+    }
+}
+
+__global__ void pair_assign_kernel(const PairDict pd) {
+    const uint32_t h = blockIdx.x * blockDim.x + threadIdx.x;
+    if (h < kPairHashCap && pd.keys[h] != kPairEmpty) pd.ids[h] = atomicAdd(pd.counter + 1, 1u);
+}
+
 // K0b: scatter every alignment into its length bucket, translating steps to universe-local 16-bit
 // ids on the way (node2local gathered through L2).  Row order inside a bucket is arbitrary; perm
 // remembers the original index.  Slots are handed out per CTA (shared-memory ranks + one global
@@ -43,7 +109,8 @@ __global__ void __launch_bounds__(kBlock)
 bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ steps,
                       const uint32_t *__restrict__ map, uint64_t A, const Buckets bk,
                       uint16_t *__restrict__ bstep, uint2 *__restrict__ ldesc,
-                      uint32_t *__restrict__ perm, uint32_t *__restrict__ cursors) {
+                      uint32_t *__restrict__ perm, uint32_t *__restrict__ cursors,
+                      const PairDict pd, uint32_t n_pairs) {
     __shared__ uint32_t s_cnt[kNumBuckets + 1], s_base[kNumBuckets + 1];
     const uint64_t n_tiles = (A + kBlock - 1) / kBlock;
     for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -71,12 +138,27 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
                 dst = bk.step_base[b] + s_base[kNumBuckets] + lrank;
                 ldesc[slot] = make_uint2(dst, m);
             } else {
-                dst = bk.step_base[b] + slot * m;
+                dst = bk.step_base[b] + slot * row_stride((int)m);
             }
+            uint32_t prev = 0;
             for (uint32_t j = 0; j < m; ++j) {
                 const uint32_t s = __ldg(steps + o0 + j);
-                bstep[dst + j] = (uint16_t)((__ldg(map + (s >> 1)) << 1) | (s & 1u));
+                const uint32_t l = (__ldg(map + (s >> 1)) << 1) | (s & 1u);
+                bstep[dst + j] = (uint16_t)l;
+                if (b != (uint32_t)kLongBucket && j > 0) {
+                    uint32_t pid = 2u * n_pairs;   // pair with a node outside the universe
+                    if (n_pairs != 0xFFFFFFFFu) {
+                        uint32_t flip;
+                        const uint32_t key = pair_canonical(prev, l, &flip);
+                        const uint32_t h = pair_find(pd, key);
+                        if (h != kPairEmpty) pid = 2u * pd.ids[h] + flip;
+                    }
+                    bstep[dst + m + j - 1] = (uint16_t)pid;
+                }
+                prev = l;
             }
+            if (b != (uint32_t)kLongBucket)
+                for (uint32_t j = 2 * m - 1; j < row_stride((int)m); ++j) bstep[dst + j] = 0;
         }
         __syncthreads();
     }
@@ -117,7 +199,7 @@ __device__ __forceinline__ RowRef tile_row(const Buckets &bk, int b, uint32_t ti
         r.ptr = bk.bstep + d.x;
         r.m = d.y;
     } else {
-        r.ptr = bk.bstep + bk.step_base[b] + (r.valid ? (size_t)row * b : 0);
+        r.ptr = bk.bstep + bk.step_base[b] + (r.valid ? (size_t)row * row_stride(b) : 0);
         r.m = (uint32_t)b;
     }
     return r;
@@ -136,7 +218,7 @@ __device__ __forceinline__ RowRef locate_row(const Buckets &bk, uint32_t sorted)
         r.ptr = bk.bstep + d.x;
         r.m = d.y;
     } else {
-        r.ptr = bk.bstep + bk.step_base[b] + (size_t)row * b;
+        r.ptr = bk.bstep + bk.step_base[b] + (size_t)row * row_stride(b);
         r.m = (uint32_t)b;
     }
     return r;
@@ -151,7 +233,8 @@ __device__ __forceinline__ RowRef locate_row(const Buckets &bk, uint32_t sorted)
 __global__ void __launch_bounds__(kBlock)
 build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restrict__ pstep,
                     uint32_t L, uint32_t stride, uint16_t *__restrict__ ptab,
-                    uint16_t *__restrict__ pnext) {
+                    uint16_t *__restrict__ pnext, uint32_t *__restrict__ masks, const MaskGeom mg,
+                    const PairDict pd) {
     extern __shared__ uint32_t row[];
     const uint32_t p = blockIdx.x;
     const uint32_t o0 = poff[p], n = poff[p + 1] - o0;
@@ -185,6 +268,31 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
                 if ((uint32_t)(s[k] >> 1) == node) { nx = k; break; }
         }
         pnext[o0 + i] = (uint16_t)nx;
+    }
+    if (masks == nullptr) return;
+    // ---- this path's bit in the batch's bitsets (chunk = 32*W paths, entry = W words) ----------
+    const uint32_t per_chunk = 32u * mg.W;
+    const uint32_t q = p % per_chunk;
+    uint32_t *tabw = masks + (size_t)(p / per_chunk) * mg.entries * mg.W + (q >> 5);
+    const uint32_t bit = 1u << (q & 31u);
+    for (uint32_t i = threadIdx.x; i < L; i += blockDim.x) {
+        const uint32_t v = row[i];
+        if (v == 0xFFFFFFFFu) continue;
+        atomicOr(tabw + (size_t)(3 * i) * mg.W, bit);                              // N
+        if (v >> 31) atomicOr(tabw + (size_t)(3 * i + 1) * mg.W, bit);             // T: twice
+        if (((v & 0x7FFFFFFFu) >> 1) == 0) atomicOr(tabw + (size_t)(3 * i + 2) * mg.W, bit);  // F
+    }
+    for (uint32_t m = threadIdx.x; m <= (uint32_t)kMaxBucket; m += blockDim.x)
+        if (n < m) atomicOr(tabw + (size_t)(mg.lm_base + m) * mg.W, bit);           // LM: n < m
+    for (uint32_t i = threadIdx.x; i + 1 < n; i += blockDim.x) {
+        uint32_t flip;
+        const uint32_t x = s[i], y = s[i + 1];
+        const uint32_t key = pair_canonical(x, y, &flip);
+        const uint32_t h = pair_find(pd, key);
+        if (h == kPairEmpty) continue;       // no alignment carries this pair
+        const uint32_t c2 = 2u * __ldg(pd.ids + h);
+        atomicOr(tabw + (size_t)(mg.pair_base + c2 + flip) * mg.W, bit);
+        if (y == (x ^ 1u)) atomicOr(tabw + (size_t)(mg.pair_base + c2 + 1u) * mg.W, bit);   // its own twin
     }
 }
 
@@ -511,7 +619,8 @@ __device__ __forceinline__ void score_tile_long(const ScoreArgs &a, const uint16
 
 template <bool kFilter>
 __global__ void __launch_bounds__(kBlock)
-score_paths_kernel(const ScoreArgs a) {
+score_paths_kernel(const ScoreArgs a, const uint32_t tile_lo, const uint32_t tile_hi,
+                   const bool add_empty) {
     extern __shared__ __align__(16) unsigned char smem[];
     uint16_t *s_tab = reinterpret_cast<uint16_t *>(smem);
     uint32_t *s_cnt = reinterpret_cast<uint32_t *>(smem + (size_t)a.chunk * a.tab_stride * 2);
@@ -535,8 +644,7 @@ score_paths_kernel(const ScoreArgs a) {
 #pragma unroll
     for (int h = 0; h < kMaxChunk / 32; ++h) acc.bad[h] = acc.good[h] = 0;
 
-    const uint32_t n_tiles = a.bk.tile_start[kNumBuckets];
-    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    for (uint32_t tile = tile_lo + blockIdx.x; tile < tile_hi; tile += gridDim.x) {
         const int b = tile_bucket(a.bk, tile);
         const RowRef r = tile_row(a.bk, b, tile);
         switch (b) {
@@ -559,10 +667,40 @@ score_paths_kernel(const ScoreArgs a) {
     }
     __syncthreads();
     // alignments without steps pass the filter and score 0 against every path: good
-    const uint32_t empty_rows = blockIdx.x == 0 ? a.bk.count[0] : 0u;
+    const uint32_t empty_rows = (add_empty && blockIdx.x == 0) ? a.bk.count[0] : 0u;
     for (uint32_t i = threadIdx.x; i < 2 * pc; i += blockDim.x) {
         const uint32_t v = s_cnt[i] + ((i & 1u) ? empty_rows : 0u);
         if (v) atomicAdd(&a.counts[2 * (size_t)p_base + i], v);
+    }
+}
+
+// K1s: the (path, alignment) pairs the bitset kernel could not settle — the alignment touches a
+// node the path visits twice (pair bitsets are then only necessary, not sufficient) or the node of
+// path[0] (start overhang, SURVEY.md Appendix A.3 class iv).  Same second look as the legacy
+// kernel: direct comparison along the visit chain, then the suffix/prefix test; what is still
+// open goes to the exact-DP worklist.
+__global__ void __launch_bounds__(128)
+slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
+                     const uint32_t *__restrict__ slow_count, const uint32_t slow_cap) {
+    const uint32_t cnt = min(slow_count[0], slow_cap);
+    for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < cnt;
+         idx += gridDim.x * blockDim.x) {
+        const uint2 w = slow[idx];
+        const RowRef r = locate_row(a.bk, w.y);
+        const int m = (int)r.m;
+        const uint32_t po = a.poff[w.x];
+        const int n = (int)(a.poff[w.x + 1] - po);
+        const uint16_t *tab = a.ptab + (size_t)w.x * a.tab_stride;
+        bool twice = false;
+        for (int j = 0; j < m; ++j) twice = twice || (tab[__ldg(r.ptr + j) >> 1] & 1u);
+        const int v = slow_verdict(a.pstep + po, a.pnext + po, n, tab, r.ptr, m, twice);
+        if (v == kExact) {
+            const uint32_t k = atomicAdd(a.work_count, 1u);
+            if (k < a.work_cap) a.work[k] = w;
+            else atomicOr(a.work_count + 1, 1u);
+        } else {
+            atomicAdd(&a.counts[2 * (size_t)w.x + (v == kGood ? 1 : 0)], 1u);
+        }
     }
 }
 
@@ -800,14 +938,28 @@ void launch_length_histogram(const uint32_t *off, uint64_t A, uint32_t *hist, cu
     length_histogram_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(off, A, hist);
 }
 
+void launch_pair_collect(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local,
+                         uint64_t A, uint32_t L, uint32_t max_pairs, const PairDict &pd,
+                         cudaStream_t st) {
+    if (A == 0) return;
+    uint64_t blocks = (A + kBlock - 1) / kBlock;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    pair_collect_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(off, steps, node2local, A, L, max_pairs, pd);
+}
+
+void launch_pair_assign(const PairDict &pd, cudaStream_t st) {
+    pair_assign_kernel<<<kPairHashCap / 256, 256, 0, st>>>(pd);
+}
+
 void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local,
                            uint64_t A, const Buckets &bk, uint16_t *bstep, uint2 *ldesc,
-                           uint32_t *perm, uint32_t *cursors, cudaStream_t st) {
+                           uint32_t *perm, uint32_t *cursors, const PairDict &pd, uint32_t n_pairs,
+                           cudaStream_t st) {
     if (A == 0) return;
     uint64_t blocks = (A + kBlock - 1) / kBlock;
     if (blocks > 148 * 8) blocks = 148 * 8;
     bucket_scatter_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(off, steps, node2local, A, bk, bstep,
-                                                               ldesc, perm, cursors);
+                                                               ldesc, perm, cursors, pd, n_pairs);
 }
 
 void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, uint32_t n_nodes,
@@ -819,13 +971,15 @@ void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, u
 }
 
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
-                         uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, cudaStream_t st) {
+                         uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, uint32_t *masks,
+                         const MaskGeom &mg, const PairDict &pd, cudaStream_t st) {
     if (P == 0) return;
     build_tables_kernel<<<P, kBlock, (size_t)(L + 1) * sizeof(uint32_t), st>>>(
-        poff, pstep, L, tab_stride, ptab, pnext);
+        poff, pstep, L, tab_stride, ptab, pnext, masks, mg, pd);
 }
 
-void launch_score_paths(const ScoreArgs &a, int sm_count, cudaStream_t st) {
+void launch_score_paths(const ScoreArgs &a, int sm_count, uint32_t tile_lo, uint32_t tile_hi,
+                        bool add_empty, cudaStream_t st) {
     if (a.P == 0) return;
     const size_t smem = score_smem_bytes(a);
     const uint32_t chunks = (a.P + a.chunk - 1) / a.chunk;
@@ -835,14 +989,19 @@ void launch_score_paths(const ScoreArgs &a, int sm_count, cudaStream_t st) {
     else
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, score_paths_kernel<false>, kBlock, smem);
     if (per_sm < 1) per_sm = 1;
-    const uint64_t n_tiles = a.bk.tile_start[kNumBuckets];
+    const uint64_t n_tiles = tile_hi - tile_lo;
     // resident CTAs = a multiple of the SM count; split between tile workers (x) and chunks (y)
     uint64_t gx = ((uint64_t)sm_count * per_sm + chunks - 1) / chunks;
     if (gx > n_tiles) gx = n_tiles;
     if (gx < 1) gx = 1;
     dim3 grid((unsigned)gx, chunks);
-    if (a.filter) score_paths_kernel<true><<<grid, kBlock, smem, st>>>(a);
-    else score_paths_kernel<false><<<grid, kBlock, smem, st>>>(a);
+    if (a.filter) score_paths_kernel<true><<<grid, kBlock, smem, st>>>(a, tile_lo, tile_hi, add_empty);
+    else score_paths_kernel<false><<<grid, kBlock, smem, st>>>(a, tile_lo, tile_hi, add_empty);
+}
+
+void launch_slow_worklist(const ScoreArgs &a, const uint2 *slow, const uint32_t *slow_count,
+                          uint32_t slow_cap, cudaStream_t st) {
+    slow_worklist_kernel<<<148 * 8, 128, 0, st>>>(a, slow, slow_count, slow_cap);
 }
 
 void launch_exact_worklist(const ScoreArgs &a, cudaStream_t st) {

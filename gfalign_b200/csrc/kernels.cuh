@@ -4,9 +4,17 @@
 //   off   u32[A+1]        CSR offsets of the alignment table            (as handed in)
 //   steps u32[S]          oriented steps, node<<1|minus, global dense node ids   (edge support)
 //   -- scoring view, rebuilt by gfe_set_universe (length-bucketed, universe-local, 16-bit) --
-//   bstep u16[..]         for every length m = 1..kMaxBucket a dense [count_m][m] matrix of local
-//                         steps (local<<1|minus; every node outside the universe is local id L),
-//                         then the steps of the "long" alignments (m > kMaxBucket) back to back
+//   bstep u16[..]         for every length m = 1..kMaxBucket a dense [count_m][row_stride(m)] matrix:
+//                         m local steps (local<<1|minus; every node outside the universe is
+//                         local id L), then m-1 PAIR IDS (id of the consecutive oriented pair
+//                         (B_j, B_j+1) in the pair dictionary, id^1 = its reverse complement;
+//                         2C = pair with a node outside the universe), zero padding to a multiple
+//                         of 4; then the steps of the "long" alignments (m > kMaxBucket) back to back
+//   pkeys/pids u32[H]     pair dictionary: open-addressing hash of canonical pair keys
+//                         min(x<<16|y, (y^1)<<16|(x^1)) -> canonical id c; pair id = 2c + flipped
+//   masks u32[chunks][E][W]  per batch: bitsets over the chunk's 32*W candidate paths, one entry per
+//                         node (N: on the path, T: visited twice, F: node of path[0]), per length
+//                         (LM[m]: n < m) and per pair id (M: the path takes this oriented pair)
 //   ldesc uint2[n_long]   long alignments: (element offset into bstep, m)
 //   perm  u32[A]          sorted row -> original alignment index (rows of length 0 first, then
 //                         m = 1, 2, ... kMaxBucket, then long)
@@ -33,11 +41,23 @@ constexpr int kLongBucket = kMaxBucket + 1;
 constexpr int kExactRegSteps = 32;    // widest alignment the register DP handles
 constexpr int kMaxChunk = 64;         // candidate paths per CTA pass (tables in shared memory)
 constexpr uint32_t kTabAbsent = 0;
+constexpr int kUnit = 64;             // rows per scheduling unit of the bitset kernel
+constexpr int kBitThreads = 512;      // threads per CTA of the bitset kernel (one CTA per SM)
+constexpr int kPlanes = 12;           // bit-sliced counter planes per lane (flush before 2^12 rows)
+constexpr uint32_t kPairHashCap = 1u << 16;   // slots of the pair dictionary
+constexpr uint32_t kPairEmpty = 0xFFFFFFFFu;
+constexpr size_t kBitsetSmemBudget = 208 * 1024;   // mask table + counters per CTA
+
+// u16 elements per row of the length-m matrix: m steps + (m-1) pair ids, padded to 8 bytes
+__host__ __device__ constexpr uint32_t row_stride(int m) {
+    return m <= 0 ? 0u : (uint32_t)((2 * m - 1 + 3) & ~3);
+}
 
 struct Buckets {
     uint32_t count[kNumBuckets];          // rows per bucket
     uint32_t row_start[kNumBuckets + 1];  // first sorted row of each bucket
     uint32_t tile_start[kNumBuckets + 1]; // first kBlock-row tile of each bucket (bucket 0: none)
+    uint32_t unit_start[kNumBuckets + 1]; // first kUnit-row unit of buckets 1..kMaxBucket (long: none)
     uint32_t step_base[kNumBuckets];      // element offset of the bucket's matrix in bstep
     const uint16_t *bstep;
     const uint2 *ldesc;
@@ -58,6 +78,35 @@ struct ScoreArgs {
     uint2 *work;              // exact-DP worklist (path, sorted row)
     uint32_t *work_count;     // [0] entries, [1] overflow flag
     uint32_t work_cap;
+};
+
+struct PairDict {
+    uint32_t *keys;           // kPairHashCap slots, kPairEmpty = free
+    uint32_t *ids;            // canonical id of the slot's key
+    uint32_t *counter;        // [0] distinct keys inserted, [1] ids handed out, [2] overflow flag
+};
+
+// mask-table geometry of one batch (entries are W words each)
+struct MaskGeom {
+    uint32_t W;               // words per entry = chunk paths / 32 (power of two <= 32)
+    uint32_t L;               // universe size; node entries at 3*node + {0 N, 1 T, 2 F}
+    uint32_t lm_base;         // LM[m] at lm_base + m, m = 0..kMaxBucket
+    uint32_t pair_base;       // M[pid] at pair_base + pid, pid <= 2C+1 (2C, 2C+1: always zero)
+    uint32_t entries;         // E, multiple of 4
+    uint32_t n_pairs;         // C
+};
+
+struct BitsetArgs {
+    Buckets bk;
+    MaskGeom mg;
+    const uint32_t *masks;    // [chunks][E][W]
+    uint32_t P;
+    int filter;
+    uint32_t *counts;         // P x {bad, good}
+    uint32_t *unit_ctr;       // per chunk: next unit (dynamic scheduling), zeroed per launch
+    uint2 *slow;              // (path, sorted row) pairs the bitsets cannot settle
+    uint32_t *work_count;     // [0..1] exact list count/overflow, [2..3] slow list count/overflow
+    uint32_t slow_cap;
 };
 
 struct PairArgs {             // evalPath: one path against every alignment
@@ -88,15 +137,28 @@ struct EdgeArgs {
 // hist: kNumBuckets counters, [kNumBuckets] = max length, [kNumBuckets+1] = steps of long rows
 void launch_length_histogram(const uint32_t *off, uint64_t A, uint32_t *hist, cudaStream_t st);
 // cursors: kNumBuckets row cursors + [kNumBuckets] long-step cursor (zeroed by the caller)
+void launch_pair_collect(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local,
+                         uint64_t A, uint32_t L, uint32_t max_pairs, const PairDict &pd,
+                         cudaStream_t st);
+void launch_pair_assign(const PairDict &pd, cudaStream_t st);
+// n_pairs = 0xFFFFFFFF: no dictionary (pair ids are not written)
 void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local,
                            uint64_t A, const Buckets &bk, uint16_t *bstep, uint2 *ldesc,
-                           uint32_t *perm, uint32_t *cursors, cudaStream_t st);
+                           uint32_t *perm, uint32_t *cursors, const PairDict &pd, uint32_t n_pairs,
+                           cudaStream_t st);
 void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, uint32_t n_nodes,
                            uint32_t L, uint16_t *out, uint32_t total, uint32_t *err,
                            cudaStream_t st);
+// masks == nullptr: tables only (legacy kernel); else also ORs path p into the batch's bitsets
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
-                         uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, cudaStream_t st);
-void launch_score_paths(const ScoreArgs &a, int sm_count, cudaStream_t st);
+                         uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, uint32_t *masks,
+                         const MaskGeom &mg, const PairDict &pd, cudaStream_t st);
+// tiles [tile_lo, tile_hi) of the bucket geometry; add_empty: count the step-less rows as good
+void launch_score_paths(const ScoreArgs &a, int sm_count, uint32_t tile_lo, uint32_t tile_hi,
+                        bool add_empty, cudaStream_t st);
+void launch_score_bitset(const BitsetArgs &a, int sm_count, cudaStream_t st);
+void launch_slow_worklist(const ScoreArgs &a, const uint2 *slow, const uint32_t *slow_count,
+                          uint32_t slow_cap, cudaStream_t st);
 void launch_exact_worklist(const ScoreArgs &a, cudaStream_t st);
 void launch_exact_worklist_long(const ScoreArgs &a, uint32_t max_m, cudaStream_t st);
 void launch_pair_classify(const PairArgs &a, int sm_count, cudaStream_t st);
