@@ -111,17 +111,38 @@ __device__ __forceinline__ int unit_bucket(const Buckets &bk, uint32_t unit) {
     return b;
 }
 
-// push the set bits of `mask` (paths word_base .. word_base+31) as (path, row) work items
-__device__ __forceinline__ void push_slow(const BitsetArgs &a, uint32_t mask, uint32_t word_base,
-                                          uint32_t sorted_row) {
-    const uint32_t n = (uint32_t)__popc(mask);
-    uint32_t idx = atomicAdd(a.work_count + 2, n);
-    while (mask) {
-        const uint32_t c = (uint32_t)__ffs(mask) - 1u;
-        mask &= mask - 1u;
-        if (idx < a.slow_cap) a.slow[idx] = make_uint2(word_base + c, sorted_row);
-        else atomicOr(a.work_count + 3, 1u);
-        ++idx;
+// Push the set bits of the eight masks of one warp step (paths word_base .. word_base+31, rows
+// row_first + u*row_step) as (path, row) work items.  Called by the whole warp: ONE atomic on the
+// list counter per call (a per-lane atomic serialises on a single L2 address).
+__device__ __noinline__ void push_slow8(uint2 *__restrict__ slow, uint32_t *work_count,
+                                        uint32_t slow_cap, uint32_t s0, uint32_t s1, uint32_t s2,
+                                        uint32_t s3, uint32_t s4, uint32_t s5, uint32_t s6,
+                                        uint32_t s7, uint32_t word_base, uint32_t row_first,
+                                        uint32_t row_step, int lane) {
+    const uint32_t sm[8] = {s0, s1, s2, s3, s4, s5, s6, s7};
+    uint32_t n = 0;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) n += (uint32_t)__popc(sm[u]);
+    uint32_t incl = n;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    uint32_t base = 0;
+    if (lane == 31) base = atomicAdd(work_count + 2, incl);
+    base = __shfl_sync(0xFFFFFFFFu, base, 31);
+    uint32_t idx = base + incl - n;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        uint32_t mask = sm[u];
+        while (mask) {
+            const uint32_t c = (uint32_t)__ffs(mask) - 1u;
+            mask &= mask - 1u;
+            if (idx < slow_cap) slow[idx] = make_uint2(word_base + c, row_first + u * row_step);
+            else atomicOr(work_count + 3, 1u);
+            ++idx;
+        }
     }
 }
 
@@ -188,11 +209,12 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint32_t *
     const uint32_t lm = tab[(a.mg.lm_base + M) * W];
     const uint32_t sub = (uint32_t)lane / W;
     for (uint32_t it = 0; it < nrows; it += 8 * R) {
-        uint32_t gm[8], bm[8];
+        uint32_t gm[8], bm[8], sm[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
             gm[u] = 0;
             bm[u] = 0;
+            sm[u] = 0;
             if (it + u * R >= nrows) continue;      // warp-uniform
             const uint32_t r = it + u * R + sub;
             const bool valid = r < nrows;
@@ -201,11 +223,15 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint32_t *
             if (valid) {
                 gm[u] = good;
                 bm[u] = bad;
-                if (slow) push_slow(a, slow, word_base, sorted0 + r);
+                sm[u] = slow;
             }
         }
         G.add8(gm);
         B.add8(bm);
+        const uint32_t any_slow = sm[0] | sm[1] | sm[2] | sm[3] | sm[4] | sm[5] | sm[6] | sm[7];
+        if (__any_sync(0xFFFFFFFFu, any_slow != 0))
+            push_slow8(a.slow, a.work_count, a.slow_cap, sm[0], sm[1], sm[2], sm[3], sm[4], sm[5],
+                       sm[6], sm[7], word_base, sorted0 + it + sub, (uint32_t)R, lane);
     }
 }
 
