@@ -104,11 +104,24 @@ struct Planes {
     }
 };
 
-__device__ __forceinline__ int unit_bucket(const Buckets &bk, uint32_t unit) {
+__device__ __forceinline__ int unit_bucket(const BitsetArgs &a, uint32_t unit) {
     int b = 1;
 #pragma unroll
-    for (int k = 2; k <= kMaxBucket; ++k) b += (unit >= bk.unit_start[k]) ? 1 : 0;
+    for (int k = 2; k <= kMaxBucket; ++k) b += (unit >= a.unit_start[k]) ? 1 : 0;
     return b;
+}
+
+// first row / row count / bytes of a unit; used to prefetch the next unit's rows into L1
+__device__ __forceinline__ void prefetch_unit(const BitsetArgs &a, uint32_t unit, int lane) {
+    if (unit >= a.unit_start[kMaxBucket + 1]) return;
+    const int b = unit_bucket(a, unit);
+    const uint32_t row0 = (unit - a.unit_start[b]) * a.unit_rows;
+    const uint32_t nrows = min(a.unit_rows, a.bk.count[b] - row0);
+    const uint32_t rs = row_stride(b);
+    const char *p = reinterpret_cast<const char *>(a.bk.bstep + a.bk.step_base[b] + (size_t)row0 * rs);
+    const uint32_t bytes = nrows * rs * 2u;
+    for (uint32_t o = (uint32_t)lane * 128u; o < bytes + 127u; o += 32u * 128u)
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(p + min(o, bytes - 1u)));
 }
 
 // Push the set bits of the eight masks of one warp step (paths word_base .. word_base+31, rows
@@ -202,8 +215,8 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint32_t *
                                            int lane) {
     constexpr int R = 32 / W;                       // rows per warp step
     constexpr int RS = (int)row_stride(M);
-    const uint32_t row0 = (unit - a.bk.unit_start[M]) * (uint32_t)kUnit;
-    const uint32_t nrows = min((uint32_t)kUnit, a.bk.count[M] - row0);
+    const uint32_t row0 = (unit - a.unit_start[M]) * a.unit_rows;
+    const uint32_t nrows = min(a.unit_rows, a.bk.count[M] - row0);
     const uint16_t *base = a.bk.bstep + a.bk.step_base[M] + (size_t)row0 * RS;
     const uint32_t sorted0 = a.bk.row_start[M] + row0;
     const uint32_t lm = tab[(a.mg.lm_base + M) * W];
@@ -243,11 +256,10 @@ score_bitset_kernel(const BitsetArgs a) {
     const uint32_t tab_words = a.mg.entries * W;
     uint32_t *s_cnt = s_tab + tab_words;                       // 32*W paths x {bad, good}
     uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_cnt + 64 * W);
-    __shared__ uint32_t s_unit[kBitThreads / 32];
 
     const uint32_t chunk = blockIdx.y;
     const uint32_t p_base = chunk * 32u * W;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
     if (threadIdx.x == 0) mbar_init(s_bar, 1);
     for (uint32_t i = threadIdx.x; i < 64u * W; i += blockDim.x) s_cnt[i] = 0;
     __syncthreads();
@@ -269,7 +281,7 @@ score_bitset_kernel(const BitsetArgs a) {
     G.clear();
     B.clear();
     uint32_t rows_acc = 0;
-    const uint32_t n_units = a.bk.unit_start[kMaxBucket + 1];
+    const uint32_t n_units = a.unit_start[kMaxBucket + 1];
 
     auto flush = [&]() {
 #pragma unroll 4
@@ -283,13 +295,21 @@ score_bitset_kernel(const BitsetArgs a) {
         rows_acc = 0;
     };
 
+    // Dynamic scheduling, two units ahead: `unit` is being scored, `next` is known to the warp and
+    // its rows are being prefetched into L1, `pending` is lane 0's atomic still in flight.
+    uint32_t next = 0, pending = 0;
+    if (lane == 0) {
+        next = atomicAdd(a.unit_ctr + chunk, 1u);
+        pending = atomicAdd(a.unit_ctr + chunk, 1u);
+    }
+    next = __shfl_sync(0xFFFFFFFFu, next, 0);
     for (;;) {
-        if (lane == 0) s_unit[warp] = atomicAdd(a.unit_ctr + chunk, 1u);
-        __syncwarp();
-        const uint32_t unit = s_unit[warp];
-        __syncwarp();
+        const uint32_t unit = next;
         if (unit >= n_units) break;
-        const int b = unit_bucket(a.bk, unit);
+        next = __shfl_sync(0xFFFFFFFFu, pending, 0);
+        if (lane == 0) pending = atomicAdd(a.unit_ctr + chunk, 1u);
+        prefetch_unit(a, next, lane);
+        const int b = unit_bucket(a, unit);
         switch (b) {
 #define GFE_CASE(M_) case M_: score_unit<M_, W>(a, tab, unit, word_base, G, B, lane); break;
             GFE_CASE(1) GFE_CASE(2) GFE_CASE(3) GFE_CASE(4) GFE_CASE(5) GFE_CASE(6) GFE_CASE(7)
@@ -298,8 +318,8 @@ score_bitset_kernel(const BitsetArgs a) {
 #undef GFE_CASE
             default: break;
         }
-        rows_acc += kUnit;
-        if (rows_acc > (1u << kPlanes) - 2u * kUnit) flush();
+        rows_acc += a.unit_rows;
+        if (rows_acc > (1u << kPlanes) - 2u * a.unit_rows) flush();
     }
     flush();
     __syncthreads();
@@ -325,7 +345,7 @@ void launch_w(const BitsetArgs &a, int sm_count, cudaStream_t st) {
     const uint32_t chunks = (a.P + 32 * W - 1) / (32 * W);
     uint32_t gx = (uint32_t)sm_count / chunks;
     if (gx < 1) gx = 1;
-    const uint32_t n_units = a.bk.unit_start[kMaxBucket + 1];
+    const uint32_t n_units = a.unit_start[kMaxBucket + 1];
     const uint32_t max_gx = (n_units + (kBitThreads / 32) - 1) / (kBitThreads / 32);
     if (gx > max_gx) gx = max_gx ? max_gx : 1;
     score_bitset_kernel<W><<<dim3(gx, chunks), kBitThreads, smem, st>>>(a);

@@ -227,23 +227,21 @@ static int build_bucket_geometry(gfe_engine *e) {
     CUDA_TRY(e, cudaMemcpyAsync(hist, e->d_hist.ptr, sizeof(hist), cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     Buckets &bk = e->bk;
-    uint64_t row = 0, tile = 0, base = 0, unit = 0;
+    uint64_t row = 0, tile = 0, base = 0;
     for (int b = 0; b < kNumBuckets; ++b) {
         bk.count[b] = hist[b];
         bk.row_start[b] = (uint32_t)row;
         bk.tile_start[b] = (uint32_t)tile;
         base = (base + 7) & ~7ull;            // 16-byte aligned matrices
         bk.step_base[b] = (uint32_t)base;
-        bk.unit_start[b] = (uint32_t)unit;
         row += hist[b];
         if (b >= 1) tile += (hist[b] + kBlock - 1) / kBlock;
-        if (b >= 1 && b <= kMaxBucket) unit += (hist[b] + kUnit - 1) / kUnit;
         base += b == kLongBucket ? (uint64_t)hist[kNumBuckets + 1]
                                  : (uint64_t)hist[b] * row_stride(b);
     }
     bk.row_start[kNumBuckets] = (uint32_t)row;
     bk.tile_start[kNumBuckets] = (uint32_t)tile;
-    bk.unit_start[kNumBuckets] = (uint32_t)unit;
+
     if (base + 8 >= 0xFFFFFFFFull) {
         set_error(e, "alignment shard has too many steps for 32-bit element offsets; shard it");
         return GFE_ERR_LIMIT;
@@ -470,6 +468,17 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         b.slow = e->d_slow.ptr;
         b.work_count = e->d_work_count.ptr;
         b.slow_cap = (uint32_t)std::min<size_t>(e->d_slow.cap, 0xFFFFFFFFu);
+        // scheduling units: eight warp steps of 32/W rows, at least 16 rows (short tail)
+        b.unit_rows = std::max<uint32_t>(16u, 8u * (32u / W));
+        {
+            uint32_t unit = 0;
+            b.unit_start[0] = 0;
+            for (int k = 1; k <= kMaxBucket; ++k) {
+                b.unit_start[k] = unit;
+                unit += (e->bk.count[k] + b.unit_rows - 1) / b.unit_rows;
+            }
+            b.unit_start[kMaxBucket + 1] = unit;
+        }
         if (e->timing) {
             TRY(next_event_pair(e));
             CUDA_TRY(e, cudaEventRecord(e->ev0, st));

@@ -41,7 +41,6 @@ constexpr int kLongBucket = kMaxBucket + 1;
 constexpr int kExactRegSteps = 32;    // widest alignment the register DP handles
 constexpr int kMaxChunk = 64;         // candidate paths per CTA pass (tables in shared memory)
 constexpr uint32_t kTabAbsent = 0;
-constexpr int kUnit = 64;             // rows per scheduling unit of the bitset kernel
 constexpr int kBitThreads = 512;      // threads per CTA of the bitset kernel (one CTA per SM)
 constexpr int kPlanes = 12;           // bit-sliced counter planes per lane (flush before 2^12 rows)
 constexpr uint32_t kPairHashCap = 1u << 16;   // slots of the pair dictionary
@@ -57,7 +56,6 @@ struct Buckets {
     uint32_t count[kNumBuckets];          // rows per bucket
     uint32_t row_start[kNumBuckets + 1];  // first sorted row of each bucket
     uint32_t tile_start[kNumBuckets + 1]; // first kBlock-row tile of each bucket (bucket 0: none)
-    uint32_t unit_start[kNumBuckets + 1]; // first kUnit-row unit of buckets 1..kMaxBucket (long: none)
     uint32_t step_base[kNumBuckets];      // element offset of the bucket's matrix in bstep
     const uint16_t *bstep;
     const uint2 *ldesc;
@@ -103,6 +101,8 @@ struct BitsetArgs {
     uint32_t P;
     int filter;
     uint32_t *counts;         // P x {bad, good}
+    uint32_t unit_rows;       // rows per scheduling unit (multiple of 8 * 32/W, set per launch)
+    uint32_t unit_start[kMaxBucket + 2];   // first unit of buckets 1..kMaxBucket; [kMaxBucket+1] = total
     uint32_t *unit_ctr;       // per chunk: next unit (dynamic scheduling), zeroed per launch
     uint2 *slow;              // (path, sorted row) pairs the bitsets cannot settle
     uint32_t *work_count;     // [0..1] exact list count/overflow, [2..3] slow list count/overflow
