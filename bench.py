@@ -369,7 +369,9 @@ def main():
     e2e = {"value": checks_per_step * args.steps / e_sec, "unit": UNIT,
            "h2d_bytes_per_step": (c_e1["h2d_bytes"] - c_e0["h2d_bytes"]) // args.steps,
            "d2h_bytes_per_step": (c_e1["d2h_bytes"] - c_e0["d2h_bytes"]) // args.steps,
-           "call": "gfe_score_paths(host path CSR) -> host counts; alignment table resident"}
+           "call": "gfe_score_paths(host path CSR) -> host counts; alignment table resident",
+           "slow_pairs_per_step": int(c_e1["slow_pairs"] - c_e0["slow_pairs"]) // args.steps,
+           "exact_pairs_per_step": int(c_e1["exact_pairs"] - c_e0["exact_pairs"]) // args.steps}
     assert np.array_equal(got.reshape(-1).astype(np.int64),
                           d_counts.cpu().numpy().astype(np.int64)), "host and device API disagree"
 

@@ -58,7 +58,7 @@ class _SearchStats(C.Structure):
 
 class _Counters(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("exact_pairs", C.c_uint64),
-                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("slow_pairs", C.c_uint64)]
 
 
 _ROW_FN = C.CFUNCTYPE(None, C.POINTER(_SearchRow), C.c_void_p)

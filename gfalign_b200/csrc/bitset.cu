@@ -161,7 +161,8 @@ __device__ __noinline__ void push_slow8(uint2 *__restrict__ slow, uint32_t *work
 
 // One row of length M against this lane's word.  tab = shared-memory table + lane's word offset.
 template <int M, int W>
-__device__ __forceinline__ void score_row(const BitsetArgs &a, const uint32_t *__restrict__ tab,
+__device__ __forceinline__ void score_row(const BitsetArgs &a, const uint4 *__restrict__ nt,
+                                          const uint32_t *__restrict__ tab,
                                           const uint16_t *__restrict__ rp, uint32_t lm,
                                           uint32_t &good, uint32_t &bad, uint32_t &slow) {
     constexpr int RS = (int)row_stride(M);
@@ -176,13 +177,17 @@ __device__ __forceinline__ void score_row(const BitsetArgs &a, const uint32_t *_
         }
     }
     auto elem = [&](int i) -> uint32_t { return (i & 1) ? (q[i >> 1] >> 16) : (q[i >> 1] & 0xFFFFu); };
-    uint32_t pass = 0xFFFFFFFFu, tacc = 0, facc = 0;
+    // node block: one LDS.128 per step -> {N, T, F, -} of this lane's 32 paths.  A node visited
+    // twice can only break the pair test when it is an INTERIOR step of B (it then joins two pairs
+    // that may sit at different visits); at either end of B it joins one pair, whose other end
+    // pins the visit.
+    uint32_t pass = 0xFFFFFFFFu, tacc = 0, over = 0;
 #pragma unroll
     for (int j = 0; j < M; ++j) {
-        const uint32_t *e = tab + (elem(j) >> 1) * (3u * W);
-        pass &= e[0];
-        tacc |= e[W];
-        facc |= e[2 * W];
+        const uint4 e = nt[(elem(j) >> 1) * W];
+        pass &= e.x;
+        if (j >= 1 && j <= M - 2) tacc |= e.y;
+        over |= e.z;
     }
     const uint32_t in = a.filter ? pass : 0xFFFFFFFFu;
     if (M == 1) {
@@ -193,7 +198,7 @@ __device__ __forceinline__ void score_row(const BitsetArgs &a, const uint32_t *_
         return;
     }
     uint32_t fw = 0xFFFFFFFFu, rc = 0xFFFFFFFFu;
-    const uint32_t *mt = tab + a.mg.pair_base * W;
+    const uint32_t *mt = tab + (size_t)a.mg.pair_base * W;
 #pragma unroll
     for (int j = 0; j < M - 1; ++j) {
         const uint32_t pid = elem(M + j);
@@ -203,15 +208,15 @@ __device__ __forceinline__ void score_row(const BitsetArgs &a, const uint32_t *_
     const uint32_t cand = fw | rc;
     const uint32_t sure = cand & ~tacc;
     const uint32_t open = in & ~lm & ~sure;
-    const uint32_t spec = (cand & tacc) | facc;
+    const uint32_t spec = (cand & tacc) | over;
     good = in & (lm | sure);
     slow = open & spec;
     bad = open & ~spec;
 }
 
 template <int M, int W>
-__device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint32_t *__restrict__ tab,
-                                           uint32_t unit, uint32_t word_base, Planes &G, Planes &B,
+__device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint4 *__restrict__ nt,
+                                           const uint32_t *__restrict__ tab, uint32_t unit, uint32_t word_base, Planes &G, Planes &B,
                                            int lane) {
     constexpr int R = 32 / W;                       // rows per warp step
     constexpr int RS = (int)row_stride(M);
@@ -232,7 +237,7 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint32_t *
             const uint32_t r = it + u * R + sub;
             const bool valid = r < nrows;
             uint32_t good, bad, slow;
-            score_row<M, W>(a, tab, base + (size_t)(valid ? r : 0u) * RS, lm, good, bad, slow);
+            score_row<M, W>(a, nt, tab, base + (size_t)(valid ? r : 0u) * RS, lm, good, bad, slow);
             if (valid) {
                 gm[u] = good;
                 bm[u] = bad;
@@ -275,6 +280,9 @@ score_bitset_kernel(const BitsetArgs a) {
     mbar_wait(s_bar, 0);
 
     const uint32_t w = (uint32_t)lane % W;
+    // node block: 4 words per (node, w) -> this lane's quad starts at 4*w; the plain entries
+    // (LM, pairs) live behind it at (entry * W + w)
+    const uint4 *nt = reinterpret_cast<const uint4 *>(s_tab) + w;
     const uint32_t *tab = s_tab + w;
     const uint32_t word_base = p_base + 32u * w;
     Planes G, B;
@@ -311,7 +319,7 @@ score_bitset_kernel(const BitsetArgs a) {
         prefetch_unit(a, next, lane);
         const int b = unit_bucket(a, unit);
         switch (b) {
-#define GFE_CASE(M_) case M_: score_unit<M_, W>(a, tab, unit, word_base, G, B, lane); break;
+#define GFE_CASE(M_) case M_: score_unit<M_, W>(a, nt, tab, unit, word_base, G, B, lane); break;
             GFE_CASE(1) GFE_CASE(2) GFE_CASE(3) GFE_CASE(4) GFE_CASE(5) GFE_CASE(6) GFE_CASE(7)
             GFE_CASE(8) GFE_CASE(9) GFE_CASE(10) GFE_CASE(11) GFE_CASE(12) GFE_CASE(13)
             GFE_CASE(14) GFE_CASE(15) GFE_CASE(16)

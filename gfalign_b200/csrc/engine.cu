@@ -177,6 +177,7 @@ int gfe_get_counters(const gfe_engine *e, gfe_counters *out) {
     out->exact_pairs = e->exact_pairs;
     out->h2d_bytes = e->h2d_bytes;
     out->d2h_bytes = e->d2h_bytes;
+    out->slow_pairs = e->slow_pairs;
     return GFE_OK;
 }
 
@@ -349,7 +350,7 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) 
     e->n_pairs = 0;
     {
         const int64_t word_budget = (int64_t)(kBitsetSmemBudget / 4) - 64 - 8;
-        int64_t max_pairs = (word_budget - 3 * ((int64_t)e->L + 1) - (kMaxBucket + 1) - 2 - 3) / 2;
+        int64_t max_pairs = (word_budget - 4 * ((int64_t)e->L + 1) - (kMaxBucket + 1) - 2 - 3) / 2;
         max_pairs = std::min<int64_t>(max_pairs, 32766);
         if (max_pairs >= 1 && !e->force_legacy) {
             TRY(ensure_dev(e, e->d_pair_keys, kPairHashCap));
@@ -432,7 +433,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         // ---- bitset kernel: 32*W paths per CTA pass, mask table in shared memory ----------------
         MaskGeom mg;
         mg.L = e->L;
-        mg.lm_base = 3 * (e->L + 1);
+        mg.lm_base = 4 * (e->L + 1);
         mg.pair_base = mg.lm_base + kMaxBucket + 1;
         mg.n_pairs = e->n_pairs;
         mg.entries = (mg.pair_base + 2 * e->n_pairs + 2 + 3) & ~3u;
@@ -602,6 +603,7 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
         return gfe_score_paths(e, path_offsets, path_steps, P, filter, counts);
     }
     e->exact_pairs += wc[0];
+    e->slow_pairs += wc[2];
     memcpy(counts, e->h_counts.ptr, (size_t)P * 2 * sizeof(uint32_t));
     return GFE_OK;
 }

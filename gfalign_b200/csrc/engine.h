@@ -79,7 +79,7 @@ struct gfe_engine {
     DevBuf<uint2> d_row_ent;
 
     // counters
-    uint64_t kernel_launches = 0, exact_pairs = 0, h2d_bytes = 0, d2h_bytes = 0;
+    uint64_t kernel_launches = 0, exact_pairs = 0, slow_pairs = 0, h2d_bytes = 0, d2h_bytes = 0;
 
     void free_all() {
         auto fd = [](void *p) { if (p) cudaFree(p); };

@@ -273,14 +273,17 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
     // ---- this path's bit in the batch's bitsets (chunk = 32*W paths, entry = W words) ----------
     const uint32_t per_chunk = 32u * mg.W;
     const uint32_t q = p % per_chunk;
-    uint32_t *tabw = masks + (size_t)(p / per_chunk) * mg.entries * mg.W + (q >> 5);
+    uint32_t *tab0 = masks + (size_t)(p / per_chunk) * mg.entries * mg.W;
+    uint32_t *tabw = tab0 + (q >> 5);
     const uint32_t bit = 1u << (q & 31u);
+    // node block: for node i and word w four consecutive words {N, T, F, 0}
     for (uint32_t i = threadIdx.x; i < L; i += blockDim.x) {
         const uint32_t v = row[i];
         if (v == 0xFFFFFFFFu) continue;
-        atomicOr(tabw + (size_t)(3 * i) * mg.W, bit);                              // N
-        if (v >> 31) atomicOr(tabw + (size_t)(3 * i + 1) * mg.W, bit);             // T: twice
-        if (((v & 0x7FFFFFFFu) >> 1) == 0) atomicOr(tabw + (size_t)(3 * i + 2) * mg.W, bit);  // F
+        uint32_t *e = tab0 + ((size_t)i * mg.W + (q >> 5)) * 4;
+        atomicOr(e, bit);                                                  // N: on the path
+        if (v >> 31) atomicOr(e + 1, bit);                                 // T: visited twice
+        if (((v & 0x7FFFFFFFu) >> 1) == 0) atomicOr(e + 2, bit);           // F: node of path[0]
     }
     for (uint32_t m = threadIdx.x; m <= (uint32_t)kMaxBucket; m += blockDim.x)
         if (n < m) atomicOr(tabw + (size_t)(mg.lm_base + m) * mg.W, bit);           // LM: n < m
@@ -691,9 +694,9 @@ slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
         const uint32_t po = a.poff[w.x];
         const int n = (int)(a.poff[w.x + 1] - po);
         const uint16_t *tab = a.ptab + (size_t)w.x * a.tab_stride;
-        bool twice = false;
-        for (int j = 0; j < m; ++j) twice = twice || (tab[__ldg(r.ptr + j) >> 1] & 1u);
-        const int v = slow_verdict(a.pstep + po, a.pnext + po, n, tab, r.ptr, m, twice);
+        // always walk the visit chain: a pair the bitsets flagged for a twice-visited node needs
+        // it, and for a start-overhang suspect it finds nothing at the cost of one table read
+        const int v = slow_verdict(a.pstep + po, a.pnext + po, n, tab, r.ptr, m, true);
         if (v == kExact) {
             const uint32_t k = atomicAdd(a.work_count, 1u);
             if (k < a.work_cap) a.work[k] = w;
@@ -1001,7 +1004,7 @@ void launch_score_paths(const ScoreArgs &a, int sm_count, uint32_t tile_lo, uint
 
 void launch_slow_worklist(const ScoreArgs &a, const uint2 *slow, const uint32_t *slow_count,
                           uint32_t slow_cap, cudaStream_t st) {
-    slow_worklist_kernel<<<148 * 8, 128, 0, st>>>(a, slow, slow_count, slow_cap);
+    slow_worklist_kernel<<<148 * 16, 128, 0, st>>>(a, slow, slow_count, slow_cap);
 }
 
 void launch_exact_worklist(const ScoreArgs &a, cudaStream_t st) {

@@ -13,7 +13,8 @@
 //   pkeys/pids u32[H]     pair dictionary: open-addressing hash of canonical pair keys
 //                         min(x<<16|y, (y^1)<<16|(x^1)) -> canonical id c; pair id = 2c + flipped
 //   masks u32[chunks][E][W]  per batch: bitsets over the chunk's 32*W candidate paths, one entry per
-//                         node (N: on the path, T: visited twice, F: node of path[0]), per length
+//                         node (N: on the path, T: visited twice, F: node of path[0]; 4 words
+//                         interleaved per path word), per length
 //                         (LM[m]: n < m) and per pair id (M: the path takes this oriented pair)
 //   ldesc uint2[n_long]   long alignments: (element offset into bstep, m)
 //   perm  u32[A]          sorted row -> original alignment index (rows of length 0 first, then
@@ -87,7 +88,7 @@ struct PairDict {
 // mask-table geometry of one batch (entries are W words each)
 struct MaskGeom {
     uint32_t W;               // words per entry = chunk paths / 32 (power of two <= 32)
-    uint32_t L;               // universe size; node entries at 3*node + {0 N, 1 T, 2 F}
+    uint32_t L;               // universe size; node v, word w: 4 words {N, T, F, 0} at (v*W + w)*4
     uint32_t lm_base;         // LM[m] at lm_base + m, m = 0..kMaxBucket
     uint32_t pair_base;       // M[pid] at pair_base + pid, pid <= 2C+1 (2C, 2C+1: always zero)
     uint32_t entries;         // E, multiple of 4

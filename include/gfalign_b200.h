@@ -177,6 +177,7 @@ typedef struct gfe_counters {
     uint64_t kernel_launches;     /* kernels of this library launched since gfe_create */
     uint64_t exact_pairs;         /* pairs that needed the exact DP (ambiguous class) */
     uint64_t h2d_bytes, d2h_bytes;
+    uint64_t slow_pairs;          // pairs the bitset kernel handed to the second-look kernel
 } gfe_counters;
 int gfe_get_counters(const gfe_engine *e, gfe_counters *out);
 /* After the *_device entry points (which do not synchronise): waits for the device and reports
