@@ -159,6 +159,54 @@ __device__ __noinline__ void push_slow8(uint2 *__restrict__ slow, uint32_t *work
     }
 }
 
+// Second, exact look at one row (runtime length m) for this lane's 32 paths; the warp calls it
+// when the fast test below leaves any (path, row) open.  Two refinements over the fast test:
+//  * a candidate through a twice-visited interior node is certified when none of B's triples is a
+//    broken triple of the path (BT, hashed; marked by build_tables_kernel);
+//  * a start overhang (SURVEY.md A.3 class iv) needs b_j == path[0] (oriented) and, unless b_j is
+//    B's last step, the pair (b_j, b_j+1) taken by the path; mirrored for rc(B).
+// What is still open after this goes to the (path, row) list of kernels.cu.
+template <int W>
+__device__ __noinline__ uint3 refine_row(const uint4 *__restrict__ nt, const uint32_t *__restrict__ tab,
+                                         const uint16_t *__restrict__ rp, int m, uint32_t pair_base,
+                                         uint32_t bt_base, uint32_t lm, int filter) {
+    const uint32_t *mt = tab + (size_t)pair_base * W;
+    const uint32_t *bt = tab + (size_t)bt_base * W;
+    uint32_t pass = 0xFFFFFFFFu, fw = 0xFFFFFFFFu, rc = 0xFFFFFFFFu, bfw = 0, brc = 0, over = 0;
+    uint32_t prev_pid = 0, prev_mr = 0;
+    for (int j = 0; j < m; ++j) {
+        const uint32_t v = __ldg(rp + j);
+        const uint4 e = nt[(v >> 1) * W];
+        const uint32_t ff = (v & 1u) ? e.w : e.z;   // path[0] == b_j
+        const uint32_t fr = (v & 1u) ? e.z : e.w;   // path[0] == rc of b_j
+        pass &= e.x;
+        uint32_t mf = 0xFFFFFFFFu, mr = 0xFFFFFFFFu, pid = 0;
+        if (j < m - 1) {
+            pid = __ldg(rp + m + j);
+            mf = mt[pid * W];
+            mr = mt[(pid ^ 1u) * W];
+            fw &= mf;
+            rc &= mr;
+        }
+        if (j == m - 1) over |= ff;                 // k = 1
+        else if (j >= 1) over |= ff & mf;           // k = m - j >= 2: first pair of the path
+        if (j == 0) over |= fr;                     // rc, k = 1
+        else if (j <= m - 2) over |= fr & prev_mr;  // rc, pair (b_j-1, b_j) reversed
+        if (j >= 1 && j <= m - 2) {
+            const uint32_t slot = triple_slot(prev_pid, pid);
+            bfw |= bt[slot * W];
+            brc |= bt[(slot ^ 1u) * W];
+        }
+        prev_pid = pid;
+        prev_mr = mr;
+    }
+    const uint32_t in = filter ? pass : 0xFFFFFFFFu;
+    const uint32_t sure = (fw & ~bfw) | (rc & ~brc);
+    const uint32_t amb = (fw & bfw) | (rc & brc);
+    const uint32_t open = in & ~lm & ~sure;
+    return make_uint3(in & (lm | sure), open & ~(amb | over), open & (amb | over));   // good, bad, slow
+}
+
 // One row of length M against this lane's word.  tab = shared-memory table + lane's word offset.
 template <int M, int W>
 __device__ __forceinline__ void score_row(const BitsetArgs &a, const uint4 *__restrict__ nt,
@@ -177,7 +225,7 @@ __device__ __forceinline__ void score_row(const BitsetArgs &a, const uint4 *__re
         }
     }
     auto elem = [&](int i) -> uint32_t { return (i & 1) ? (q[i >> 1] >> 16) : (q[i >> 1] & 0xFFFFu); };
-    // node block: one LDS.128 per step -> {N, T, F, -} of this lane's 32 paths.  A node visited
+    // node block: one LDS.128 per step -> {N, T, F+, F-} of this lane's 32 paths.  A node visited
     // twice can only break the pair test when it is an INTERIOR step of B (it then joins two pairs
     // that may sit at different visits); at either end of B it joins one pair, whose other end
     // pins the visit.
@@ -187,7 +235,7 @@ __device__ __forceinline__ void score_row(const BitsetArgs &a, const uint4 *__re
         const uint4 e = nt[(elem(j) >> 1) * W];
         pass &= e.x;
         if (j >= 1 && j <= M - 2) tacc |= e.y;
-        over |= e.z;
+        over |= e.z | e.w;
     }
     const uint32_t in = a.filter ? pass : 0xFFFFFFFFu;
     if (M == 1) {
@@ -237,7 +285,15 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint4 *__r
             const uint32_t r = it + u * R + sub;
             const bool valid = r < nrows;
             uint32_t good, bad, slow;
-            score_row<M, W>(a, nt, tab, base + (size_t)(valid ? r : 0u) * RS, lm, good, bad, slow);
+            const uint16_t *rp = base + (size_t)(valid ? r : 0u) * RS;
+            score_row<M, W>(a, nt, tab, rp, lm, good, bad, slow);
+            if (M >= 2 && __any_sync(0xFFFFFFFFu, valid && slow != 0))
+            {
+                const uint3 x = refine_row<W>(nt, tab, rp, M, a.mg.pair_base, a.mg.bt_base, lm, a.filter);
+                good = x.x;
+                bad = x.y;
+                slow = x.z;
+            }
             if (valid) {
                 gm[u] = good;
                 bm[u] = bad;

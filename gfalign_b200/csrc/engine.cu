@@ -350,7 +350,7 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) 
     e->n_pairs = 0;
     {
         const int64_t word_budget = (int64_t)(kBitsetSmemBudget / 4) - 64 - 8;
-        int64_t max_pairs = (word_budget - 4 * ((int64_t)e->L + 1) - (kMaxBucket + 1) - 2 - 3) / 2;
+        int64_t max_pairs = (word_budget - 4 * ((int64_t)e->L + 1) - (kMaxBucket + 1) - 2 - 3 - 2 * (int64_t)kBloom) / 2;
         max_pairs = std::min<int64_t>(max_pairs, 32766);
         if (max_pairs >= 1 && !e->force_legacy) {
             TRY(ensure_dev(e, e->d_pair_keys, kPairHashCap));
@@ -436,7 +436,8 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         mg.lm_base = 4 * (e->L + 1);
         mg.pair_base = mg.lm_base + kMaxBucket + 1;
         mg.n_pairs = e->n_pairs;
-        mg.entries = (mg.pair_base + 2 * e->n_pairs + 2 + 3) & ~3u;
+        mg.bt_base = mg.pair_base + 2 * e->n_pairs + 2;
+        mg.entries = (mg.bt_base + 2 * kBloom + 3) & ~3u;
         uint32_t W = 1;
         while (W < 32 && 32 * W < P) W <<= 1;
         while (W > 1 && (size_t)mg.entries * W * 4 + 64 * W * 4 + 16 > kBitsetSmemBudget) W >>= 1;

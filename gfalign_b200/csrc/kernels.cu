@@ -276,14 +276,14 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
     uint32_t *tab0 = masks + (size_t)(p / per_chunk) * mg.entries * mg.W;
     uint32_t *tabw = tab0 + (q >> 5);
     const uint32_t bit = 1u << (q & 31u);
-    // node block: for node i and word w four consecutive words {N, T, F, 0}
+    // node block: for node i and word w four consecutive words {N, T, F+, F-}
     for (uint32_t i = threadIdx.x; i < L; i += blockDim.x) {
         const uint32_t v = row[i];
         if (v == 0xFFFFFFFFu) continue;
         uint32_t *e = tab0 + ((size_t)i * mg.W + (q >> 5)) * 4;
         atomicOr(e, bit);                                                  // N: on the path
         if (v >> 31) atomicOr(e + 1, bit);                                 // T: visited twice
-        if (((v & 0x7FFFFFFFu) >> 1) == 0) atomicOr(e + 2, bit);           // F: node of path[0]
+        if (((v & 0x7FFFFFFFu) >> 1) == 0) atomicOr(e + 2 + (s[0] & 1u), bit);   // F+/F-: path[0]
     }
     for (uint32_t m = threadIdx.x; m <= (uint32_t)kMaxBucket; m += blockDim.x)
         if (n < m) atomicOr(tabw + (size_t)(mg.lm_base + m) * mg.W, bit);           // LM: n < m
@@ -296,6 +296,52 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
         const uint32_t c2 = 2u * __ldg(pd.ids + h);
         atomicOr(tabw + (size_t)(mg.pair_base + c2 + flip) * mg.W, bit);
         if (y == (x ^ 1u)) atomicOr(tabw + (size_t)(mg.pair_base + c2 + 1u) * mg.W, bit);   // its own twin
+    }
+    // Broken triples.  With a node visited more than once, "every pair of B is taken by the path"
+    // no longer implies "B occurs": (y, x) may sit at one visit of x and (x, z) at another.  Such a
+    // triple (y, x, z) — both pairs taken, never contiguous — is hashed into BT; so is every real
+    // triple around a pair the path takes twice.  B occurs  <=>  all its pairs are taken and none of
+    // its triples is broken (bitset.cu checks BT only for rows whose interior touches T).
+    __syncthreads();   // pnext of the whole path is written
+    auto pid_of = [&](uint32_t x, uint32_t y) -> uint32_t {
+        uint32_t flip;
+        const uint32_t key = pair_canonical(x, y, &flip);
+        const uint32_t h = pair_find(pd, key);
+        return h == kPairEmpty ? 0xFFFFFFFFu : 2u * __ldg(pd.ids + h) + flip;
+    };
+    auto mark = [&](uint32_t y, uint32_t x, uint32_t z) {
+        const uint32_t qa = pid_of(y, x), qb = pid_of(x, z);
+        if (qa == 0xFFFFFFFFu || qb == 0xFFFFFFFFu) return;   // no alignment carries it
+        // a self-reverse-complement pair answers to both of its ids (2c and 2c+1)
+        const uint32_t na = (x == (y ^ 1u)) ? 2u : 1u, nb = (z == (x ^ 1u)) ? 2u : 1u;
+        for (uint32_t ia = 0; ia < na; ++ia)
+            for (uint32_t ib = 0; ib < nb; ++ib) {
+                const uint32_t a2 = qa ^ ia, b2 = qb ^ ib;
+                const uint32_t slot = triple_slot(a2, b2);
+                atomicOr(tabw + (size_t)(mg.bt_base + slot) * mg.W, bit);
+                if (a2 == (b2 ^ 1u)) atomicOr(tabw + (size_t)(mg.bt_base + (slot ^ 1u)) * mg.W, bit);
+            }
+    };
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const uint32_t node = s[i] >> 1;
+        if (node >= L || !(row[node] >> 31) || row[node] == 0xFFFFFFFFu) continue;
+        const uint32_t first = (row[node] & 0x7FFFFFFFu) >> 1;
+        for (uint32_t v2 = first; v2 != 0xFFFFu; v2 = pnext[o0 + v2]) {
+            if (v2 == i || s[v2] != s[i]) continue;
+            if (i >= 1 && v2 + 1 < n) {
+                // cross triple (pred of visit i, x, succ of visit v2): real at some visit?
+                bool real = false;
+                for (uint32_t v = first; v != 0xFFFFu && !real; v = pnext[o0 + v])
+                    real = v >= 1 && v + 1 < n && s[v] == s[i] && s[v - 1] == s[i - 1] &&
+                           s[v + 1] == s[v2 + 1];
+                if (!real) mark(s[i - 1], s[i], s[v2 + 1]);
+            }
+            if (i + 1 < n && v2 + 1 < n && s[v2 + 1] == s[i + 1]) {
+                // the pair (x, succ) is taken twice: its surrounding real triples are ambiguous
+                if (i >= 1) mark(s[i - 1], s[i], s[i + 1]);
+                if (i + 2 < n) mark(s[i], s[i + 1], s[i + 2]);
+            }
+        }
     }
 }
 

@@ -46,9 +46,18 @@ constexpr int kBitThreads = 512;      // threads per CTA of the bitset kernel (o
 constexpr int kPlanes = 12;           // bit-sliced counter planes per lane (flush before 2^12 rows)
 constexpr uint32_t kPairHashCap = 1u << 16;   // slots of the pair dictionary
 constexpr uint32_t kPairEmpty = 0xFFFFFFFFu;
+constexpr uint32_t kBloom = 128;      // hashed "broken triple" entries per orientation (bitset kernel)
 constexpr size_t kBitsetSmemBudget = 208 * 1024;   // mask table + counters per CTA
 
 // u16 elements per row of the length-m matrix: m steps + (m-1) pair ids, padded to 8 bytes
+// Hash of the consecutive-pair pair (qa, qb) = the triple (b_j-1, b_j, b_j+1), symmetric under
+// reverse complement up to the low bit: triple_slot(qb^1, qa^1) == triple_slot(qa, qb) ^ 1.
+__host__ __device__ inline uint32_t triple_slot(uint32_t qa, uint32_t qb) {
+    const uint32_t key = (qa << 16) | qb, twin = ((qb ^ 1u) << 16) | (qa ^ 1u);
+    const uint32_t canon = key < twin ? key : twin;
+    return (((canon * 0x9E3779B1u) >> 25) << 1) | (key != canon ? 1u : 0u);   // 2*kBloom slots
+}
+
 __host__ __device__ constexpr uint32_t row_stride(int m) {
     return m <= 0 ? 0u : (uint32_t)((2 * m - 1 + 3) & ~3);
 }
@@ -91,6 +100,7 @@ struct MaskGeom {
     uint32_t L;               // universe size; node v, word w: 4 words {N, T, F, 0} at (v*W + w)*4
     uint32_t lm_base;         // LM[m] at lm_base + m, m = 0..kMaxBucket
     uint32_t pair_base;       // M[pid] at pair_base + pid, pid <= 2C+1 (2C, 2C+1: always zero)
+    uint32_t bt_base;         // BT[h] at bt_base + h, h < 2*kBloom: paths with a broken triple hashing to h
     uint32_t entries;         // E, multiple of 4
     uint32_t n_pairs;         // C
 };
