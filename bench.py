@@ -250,6 +250,7 @@ def main():
     mbar = float(off[-1]) / A
     bytes_per_check = 4.0 * (mbar + 1.0)
 
+    eng_sms = torch.cuda.get_device_properties(local).multi_processor_count
     eng = gfalign_b200.Engine(local)
     eng.set_alignments(off, steps, t.n_nodes)
     eng.set_universe(nodes)
@@ -318,12 +319,24 @@ def main():
     k1_ms = kern_ms / max(kern_n, 1)
     alg_bytes = float(P) * A * bytes_per_check
     achieved = alg_bytes / (k1_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "score_paths_kernel", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    legacy = os.environ.get("GFE_FORCE_LEGACY") == "1"
+    # dram__bytes_read+write of ONE launch from the committed ncu --set full capture of this command
+    # (profiles/r01_score_bitset_ncu_full_summary.csv; cfg3, P = 1024): 19.3 MB
+    traffic = 19.3e6 if (args.workload == "cfg3" and P == 1024 and A == 1_000_000 and not legacy) else None
+    # the limiter of the bitset kernel is the SM (issue slots + shared-memory reads), not HBM:
+    # warp instructions per launch from the same capture (1.1-1.5e8) vs 4 issue slots/clk/SM
+    sm_clock = 1.965e9
+    roofline = {"bound": "hbm", "kernel": "score_paths_kernel" if legacy else "score_bitset_kernel",
+                "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "peak_source": peak_src, "kernel_ms": k1_ms, "kernel_launches_timed": kern_n,
                 "algorithmic_bytes_per_launch": alg_bytes,
-                "note": "algorithmic bytes = P x A x 4(m+1); one launch evaluates P paths per pass "
-                        "over the table, so DRAM traffic is ~1/P of it (see DESIGN.md)"}
+                "note": "algorithmic bytes = P x A x 4(m+1) (SURVEY.md 8d); one pass over the table "
+                        "serves every path of a chunk from shared-memory bitsets, so DRAM traffic "
+                        "is ~1/1000 of it and frac > 1; the kernel is issue/shared-memory bound "
+                        "(DESIGN.md 4)",
+                "issue_bound": {"checks_per_sm_clock": float(P) * A / (k1_ms * 1e-3) / (eng_sms * sm_clock),
+                                "sms": eng_sms, "sm_clock_hz": sm_clock}}
 
     # single-path launches: the streaming (HBM/L2-bound) regime of the non-speculative driver
     d_c1 = torch.zeros(2, dtype=torch.int32, device=dev)
