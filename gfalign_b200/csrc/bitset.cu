@@ -207,23 +207,12 @@ __device__ __noinline__ uint3 refine_row(const uint4 *__restrict__ nt, const uin
     return make_uint3(in & (lm | sure), open & ~(amb | over), open & (amb | over));   // good, bad, slow
 }
 
-// One row of length M against this lane's word.  tab = shared-memory table + lane's word offset.
+// One row of length M (its u16 elements packed two per register in q) against this lane's word.
+// nt / tab = shared-memory table at this lane's word (node quads / plain entries).
 template <int M, int W>
-__device__ __forceinline__ void score_row(const BitsetArgs &a, const uint4 *__restrict__ nt,
-                                          const uint32_t *__restrict__ tab,
-                                          const uint16_t *__restrict__ rp, uint32_t lm,
-                                          uint32_t &good, uint32_t &bad, uint32_t &slow) {
-    constexpr int RS = (int)row_stride(M);
-    uint32_t q[RS / 2];   // two u16 per register
-    {
-        const uint2 *src = reinterpret_cast<const uint2 *>(rp);
-#pragma unroll
-        for (int k = 0; k < RS / 4; ++k) {
-            const uint2 t = __ldg(src + k);
-            q[2 * k] = t.x;
-            q[2 * k + 1] = t.y;
-        }
-    }
+__device__ __forceinline__ void eval_row(const uint4 *__restrict__ nt, const uint32_t *__restrict__ mt,
+                                         const uint32_t (&q)[row_stride(M) / 2], uint32_t lm,
+                                         bool filter, uint32_t &good, uint32_t &bad, uint32_t &slow) {
     auto elem = [&](int i) -> uint32_t { return (i & 1) ? (q[i >> 1] >> 16) : (q[i >> 1] & 0xFFFFu); };
     // node block: one LDS.128 per step -> {N, T, F+, F-} of this lane's 32 paths.  A node visited
     // twice can only break the pair test when it is an INTERIOR step of B (it then joins two pairs
@@ -237,7 +226,7 @@ __device__ __forceinline__ void score_row(const BitsetArgs &a, const uint4 *__re
         if (j >= 1 && j <= M - 2) tacc |= e.y;
         over |= e.z | e.w;
     }
-    const uint32_t in = a.filter ? pass : 0xFFFFFFFFu;
+    const uint32_t in = filter ? pass : 0xFFFFFFFFu;
     if (M == 1) {
         // a single step occurs (forward or reverse-complemented) iff its node is on the path
         good = in & (lm | pass);
@@ -246,7 +235,6 @@ __device__ __forceinline__ void score_row(const BitsetArgs &a, const uint4 *__re
         return;
     }
     uint32_t fw = 0xFFFFFFFFu, rc = 0xFFFFFFFFu;
-    const uint32_t *mt = tab + (size_t)a.mg.pair_base * W;
 #pragma unroll
     for (int j = 0; j < M - 1; ++j) {
         const uint32_t pid = elem(M + j);
@@ -258,46 +246,70 @@ __device__ __forceinline__ void score_row(const BitsetArgs &a, const uint4 *__re
     const uint32_t open = in & ~lm & ~sure;
     const uint32_t spec = (cand & tacc) | over;
     good = in & (lm | sure);
-    slow = open & spec;
+    slow = open & spec;     // refined by refine_row before it counts
     bad = open & ~spec;
 }
 
+// One scheduling unit (rows of one length M).  Eight rows per lane and iteration; the rows of a
+// sub-batch are loaded first (independent LDG.64s in flight together), then scored, then ONE warp
+// vote decides whether any of them needs the exact second look.
 template <int M, int W>
 __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint4 *__restrict__ nt,
-                                           const uint32_t *__restrict__ tab, uint32_t unit, uint32_t word_base, Planes &G, Planes &B,
-                                           int lane) {
+                                           const uint32_t *__restrict__ tab, uint32_t unit,
+                                           uint32_t word_base, Planes &G, Planes &B, int lane) {
     constexpr int R = 32 / W;                       // rows per warp step
     constexpr int RS = (int)row_stride(M);
+    constexpr int UB = M <= 4 ? 8 : (M <= 8 ? 4 : 2);   // rows whose data is held in registers at once
     const uint32_t row0 = (unit - a.unit_start[M]) * a.unit_rows;
     const uint32_t nrows = min(a.unit_rows, a.bk.count[M] - row0);
     const uint16_t *base = a.bk.bstep + a.bk.step_base[M] + (size_t)row0 * RS;
     const uint32_t sorted0 = a.bk.row_start[M] + row0;
     const uint32_t lm = tab[(a.mg.lm_base + M) * W];
+    const uint32_t *mt = tab + (size_t)a.mg.pair_base * W;
     const uint32_t sub = (uint32_t)lane / W;
+    const bool filter = a.filter != 0;
     for (uint32_t it = 0; it < nrows; it += 8 * R) {
         uint32_t gm[8], bm[8], sm[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            gm[u] = 0;
-            bm[u] = 0;
-            sm[u] = 0;
-            if (it + u * R >= nrows) continue;      // warp-uniform
-            const uint32_t r = it + u * R + sub;
-            const bool valid = r < nrows;
-            uint32_t good, bad, slow;
-            const uint16_t *rp = base + (size_t)(valid ? r : 0u) * RS;
-            score_row<M, W>(a, nt, tab, rp, lm, good, bad, slow);
-            if (M >= 2 && __any_sync(0xFFFFFFFFu, valid && slow != 0))
-            {
-                const uint3 x = refine_row<W>(nt, tab, rp, M, a.mg.pair_base, a.mg.bt_base, lm, a.filter);
-                good = x.x;
-                bad = x.y;
-                slow = x.z;
+        for (int u = 0; u < 8; ++u) gm[u] = bm[u] = sm[u] = 0;
+#pragma unroll
+        for (int sb = 0; sb < 8 / UB; ++sb) {
+            if (it + sb * UB * R >= nrows) break;   // warp-uniform
+            uint32_t q[UB][RS / 2];
+            bool valid[UB];
+#pragma unroll
+            for (int k = 0; k < UB; ++k) {
+                const uint32_t r = it + (sb * UB + k) * R + sub;
+                valid[k] = r < nrows;
+                const uint2 *src = reinterpret_cast<const uint2 *>(base + (size_t)(valid[k] ? r : 0u) * RS);
+#pragma unroll
+                for (int c = 0; c < RS / 4; ++c) {
+                    const uint2 t = __ldg(src + c);
+                    q[k][2 * c] = t.x;
+                    q[k][2 * c + 1] = t.y;
+                }
             }
-            if (valid) {
-                gm[u] = good;
-                bm[u] = bad;
-                sm[u] = slow;
+            uint32_t any_slow = 0;
+#pragma unroll
+            for (int k = 0; k < UB; ++k) {
+                uint32_t good, bad, slow;
+                eval_row<M, W>(nt, mt, q[k], lm, filter, good, bad, slow);
+                gm[sb * UB + k] = valid[k] ? good : 0u;
+                bm[sb * UB + k] = valid[k] ? bad : 0u;
+                sm[sb * UB + k] = valid[k] ? slow : 0u;
+                any_slow |= sm[sb * UB + k];
+            }
+            if (M >= 2 && __any_sync(0xFFFFFFFFu, any_slow != 0)) {
+#pragma unroll
+                for (int k = 0; k < UB; ++k) {
+                    if (!__any_sync(0xFFFFFFFFu, sm[sb * UB + k] != 0)) continue;
+                    const uint32_t r = it + (sb * UB + k) * R + sub;
+                    const uint3 x = refine_row<W>(nt, tab, base + (size_t)(valid[k] ? r : 0u) * RS, M,
+                                                  a.mg.pair_base, a.mg.bt_base, lm, a.filter);
+                    gm[sb * UB + k] = valid[k] ? x.x : 0u;
+                    bm[sb * UB + k] = valid[k] ? x.y : 0u;
+                    sm[sb * UB + k] = valid[k] ? x.z : 0u;
+                }
             }
         }
         G.add8(gm);
