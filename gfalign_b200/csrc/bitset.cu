@@ -95,6 +95,29 @@ struct Planes {
             e0 = t;
         }
     }
+    // add four / two masks (3:2 compressors first, then ripple the carry of weight 4 / 2)
+    __device__ __forceinline__ void add(const uint32_t (&x)[4]) {
+        uint32_t c0, c1, d0;
+        csa(p[0], c0, p[0], x[0], x[1]);
+        csa(p[0], c1, p[0], x[2], x[3]);
+        csa(p[1], d0, p[1], c0, c1);
+#pragma unroll
+        for (int k = 2; k < kPlanes; ++k) {
+            const uint32_t t = p[k] & d0;
+            p[k] ^= d0;
+            d0 = t;
+        }
+    }
+    __device__ __forceinline__ void add(const uint32_t (&x)[2]) {
+        uint32_t c0;
+        csa(p[0], c0, p[0], x[0], x[1]);
+#pragma unroll
+        for (int k = 1; k < kPlanes; ++k) {
+            const uint32_t t = p[k] & c0;
+            p[k] ^= c0;
+            c0 = t;
+        }
+    }
     // column c of the counter
     __device__ __forceinline__ uint32_t value(int c) const {
         uint32_t v = 0;
@@ -211,8 +234,10 @@ __device__ __noinline__ uint3 refine_row(const uint4 *__restrict__ nt, const uin
 // nt / tab = shared-memory table at this lane's word (node quads / plain entries).
 template <int M, int W>
 __device__ __forceinline__ void eval_row(const uint4 *__restrict__ nt, const uint32_t *__restrict__ mt,
+                                         const uint32_t *__restrict__ bt,
                                          const uint32_t (&q)[row_stride(M) / 2], uint32_t lm,
-                                         bool filter, uint32_t &good, uint32_t &bad, uint32_t &slow) {
+                                         bool filter, uint32_t &good, uint32_t &bad, uint32_t &slow,
+                                         uint32_t &over_open) {
     auto elem = [&](int i) -> uint32_t { return (i & 1) ? (q[i >> 1] >> 16) : (q[i >> 1] & 0xFFFFu); };
     // node block: one LDS.128 per step -> {N, T, F+, F-} of this lane's 32 paths.  A node visited
     // twice can only break the pair test when it is an INTERIOR step of B (it then joins two pairs
@@ -232,6 +257,7 @@ __device__ __forceinline__ void eval_row(const uint4 *__restrict__ nt, const uin
         good = in & (lm | pass);
         bad = in & ~(lm | pass);
         slow = 0;
+        over_open = 0;
         return;
     }
     uint32_t fw = 0xFFFFFFFFu, rc = 0xFFFFFFFFu;
@@ -241,83 +267,91 @@ __device__ __forceinline__ void eval_row(const uint4 *__restrict__ nt, const uin
         fw &= mt[pid * W];
         rc &= mt[(pid ^ 1u) * W];
     }
-    const uint32_t cand = fw | rc;
-    const uint32_t sure = cand & ~tacc;
+    // broken triples of the path among B's triples (one slot byte per interior step)
+    uint32_t bfw = 0, brc = 0;
+#pragma unroll
+    for (int j = 0; j < M - 2; ++j) {
+        constexpr int kByte0 = 2 * (2 * M - 1);
+        const uint32_t slot = (q[(kByte0 + j) >> 2] >> (8 * ((kByte0 + j) & 3))) & 0xFFu;
+        bfw |= bt[slot * W];
+        brc |= bt[(slot ^ 1u) * W];
+    }
+    (void)tacc;
+    const uint32_t sure = (fw & ~bfw) | (rc & ~brc);
+    const uint32_t amb = (fw & bfw) | (rc & brc);
     const uint32_t open = in & ~lm & ~sure;
-    const uint32_t spec = (cand & tacc) | over;
     good = in & (lm | sure);
-    slow = open & spec;     // refined by refine_row before it counts
-    bad = open & ~spec;
+    slow = open & amb;                // a broken (or hash-colliding) triple: second-look kernel
+    over_open = open & ~amb & over;   // start-overhang suspects: refine_row decides
+    bad = open & ~amb & ~over;
 }
 
-// One scheduling unit (rows of one length M).  Eight rows per lane and iteration; the rows of a
-// sub-batch are loaded first (independent LDG.64s in flight together), then scored, then ONE warp
-// vote decides whether any of them needs the exact second look.
+// One scheduling unit (rows of one length M).  Four (two for M > 8) rows per lane and loop trip:
+// their data is loaded first (independent LDG.64s in flight together), then scored, then ONE warp
+// vote decides whether any of them needs the second look at the start overhang.  The loop is kept
+// rolled and short so that the body stays in the instruction cache.
 template <int M, int W>
 __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint4 *__restrict__ nt,
                                            const uint32_t *__restrict__ tab, uint32_t unit,
                                            uint32_t word_base, Planes &G, Planes &B, int lane) {
     constexpr int R = 32 / W;                       // rows per warp step
     constexpr int RS = (int)row_stride(M);
-    constexpr int UB = M <= 4 ? 8 : (M <= 8 ? 4 : 2);   // rows whose data is held in registers at once
+    constexpr int UB = M <= 8 ? 4 : 2;   // rows scored per loop trip (their data is loaded first)
     const uint32_t row0 = (unit - a.unit_start[M]) * a.unit_rows;
     const uint32_t nrows = min(a.unit_rows, a.bk.count[M] - row0);
     const uint16_t *base = a.bk.bstep + a.bk.step_base[M] + (size_t)row0 * RS;
     const uint32_t sorted0 = a.bk.row_start[M] + row0;
     const uint32_t lm = tab[(a.mg.lm_base + M) * W];
     const uint32_t *mt = tab + (size_t)a.mg.pair_base * W;
+    const uint32_t *bt = tab + (size_t)a.mg.bt_base * W;
     const uint32_t sub = (uint32_t)lane / W;
     const bool filter = a.filter != 0;
-    for (uint32_t it = 0; it < nrows; it += 8 * R) {
-        uint32_t gm[8], bm[8], sm[8];
+#pragma unroll 1
+    for (uint32_t it = 0; it < nrows; it += UB * R) {
+        uint32_t q[UB][RS / 2];
+        bool valid[UB];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) gm[u] = bm[u] = sm[u] = 0;
+        for (int k = 0; k < UB; ++k) {
+            const uint32_t r = it + k * R + sub;
+            valid[k] = r < nrows;
+            const uint2 *src = reinterpret_cast<const uint2 *>(base + (size_t)(valid[k] ? r : 0u) * RS);
 #pragma unroll
-        for (int sb = 0; sb < 8 / UB; ++sb) {
-            if (it + sb * UB * R >= nrows) break;   // warp-uniform
-            uint32_t q[UB][RS / 2];
-            bool valid[UB];
-#pragma unroll
-            for (int k = 0; k < UB; ++k) {
-                const uint32_t r = it + (sb * UB + k) * R + sub;
-                valid[k] = r < nrows;
-                const uint2 *src = reinterpret_cast<const uint2 *>(base + (size_t)(valid[k] ? r : 0u) * RS);
-#pragma unroll
-                for (int c = 0; c < RS / 4; ++c) {
-                    const uint2 t = __ldg(src + c);
-                    q[k][2 * c] = t.x;
-                    q[k][2 * c + 1] = t.y;
-                }
-            }
-            uint32_t any_slow = 0;
-#pragma unroll
-            for (int k = 0; k < UB; ++k) {
-                uint32_t good, bad, slow;
-                eval_row<M, W>(nt, mt, q[k], lm, filter, good, bad, slow);
-                gm[sb * UB + k] = valid[k] ? good : 0u;
-                bm[sb * UB + k] = valid[k] ? bad : 0u;
-                sm[sb * UB + k] = valid[k] ? slow : 0u;
-                any_slow |= sm[sb * UB + k];
-            }
-            if (M >= 2 && __any_sync(0xFFFFFFFFu, any_slow != 0)) {
-#pragma unroll
-                for (int k = 0; k < UB; ++k) {
-                    if (!__any_sync(0xFFFFFFFFu, sm[sb * UB + k] != 0)) continue;
-                    const uint32_t r = it + (sb * UB + k) * R + sub;
-                    const uint3 x = refine_row<W>(nt, tab, base + (size_t)(valid[k] ? r : 0u) * RS, M,
-                                                  a.mg.pair_base, a.mg.bt_base, lm, a.filter);
-                    gm[sb * UB + k] = valid[k] ? x.x : 0u;
-                    bm[sb * UB + k] = valid[k] ? x.y : 0u;
-                    sm[sb * UB + k] = valid[k] ? x.z : 0u;
-                }
+            for (int c = 0; c < RS / 4; ++c) {
+                const uint2 t = __ldg(src + c);
+                q[k][2 * c] = t.x;
+                q[k][2 * c + 1] = t.y;
             }
         }
-        G.add8(gm);
-        B.add8(bm);
-        const uint32_t any_slow = sm[0] | sm[1] | sm[2] | sm[3] | sm[4] | sm[5] | sm[6] | sm[7];
+        uint32_t gm[UB], bm[UB], sm[UB], ov[UB], any_over = 0, any_slow = 0;
+#pragma unroll
+        for (int k = 0; k < UB; ++k) {
+            eval_row<M, W>(nt, mt, bt, q[k], lm, filter, gm[k], bm[k], sm[k], ov[k]);
+            gm[k] = valid[k] ? gm[k] : 0u;
+            bm[k] = valid[k] ? bm[k] : 0u;
+            sm[k] = valid[k] ? sm[k] : 0u;
+            ov[k] = valid[k] ? ov[k] : 0u;
+            any_over |= ov[k];
+        }
+        if (M >= 2 && __any_sync(0xFFFFFFFFu, any_over != 0)) {
+#pragma unroll
+            for (int k = 0; k < UB; ++k) {
+                if (!__any_sync(0xFFFFFFFFu, ov[k] != 0)) continue;
+                const uint32_t r = it + k * R + sub;
+                const uint3 x = refine_row<W>(nt, tab, base + (size_t)(valid[k] ? r : 0u) * RS, M,
+                                              a.mg.pair_base, a.mg.bt_base, lm, a.filter);
+                gm[k] = valid[k] ? x.x : 0u;
+                bm[k] = valid[k] ? x.y : 0u;
+                sm[k] = valid[k] ? x.z : 0u;
+            }
+        }
+        G.add(gm);
+        B.add(bm);
+#pragma unroll
+        for (int k = 0; k < UB; ++k) any_slow |= sm[k];
         if (__any_sync(0xFFFFFFFFu, any_slow != 0))
-            push_slow8(a.slow, a.work_count, a.slow_cap, sm[0], sm[1], sm[2], sm[3], sm[4], sm[5],
-                       sm[6], sm[7], word_base, sorted0 + it + sub, (uint32_t)R, lane);
+            push_slow8(a.slow, a.work_count, a.slow_cap, sm[0], sm[1], UB > 2 ? sm[UB > 2 ? 2 : 0] : 0u,
+                       UB > 2 ? sm[UB > 2 ? 3 : 0] : 0u, 0u, 0u, 0u, 0u, word_base, sorted0 + it + sub,
+                       (uint32_t)R, lane);
     }
 }
 

@@ -471,7 +471,14 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         b.work_count = e->d_work_count.ptr;
         b.slow_cap = (uint32_t)std::min<size_t>(e->d_slow.cap, 0xFFFFFFFFu);
         // scheduling units: eight warp steps of 32/W rows, at least 16 rows (short tail)
-        b.unit_rows = std::max<uint32_t>(16u, 8u * (32u / W));
+        // scheduling units: a multiple of four warp steps (32/W rows each); small enough that every
+        // warp of the grid gets several units, large enough to amortise the fetch
+        {
+            const uint32_t step = 4u * (32u / W);
+            const uint64_t warps = (uint64_t)e->sm_count * (kBitThreads / 32);
+            uint64_t want = e->A / (8 * warps) / step * step;
+            b.unit_rows = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(want, step), 8 * step);
+        }
         {
             uint32_t unit = 0;
             b.unit_start[0] = 0;

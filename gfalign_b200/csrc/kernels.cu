@@ -140,7 +140,8 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
             } else {
                 dst = bk.step_base[b] + slot * row_stride((int)m);
             }
-            uint32_t prev = 0;
+            uint32_t prev = 0, prev_pid = 0;
+            unsigned char *slots = reinterpret_cast<unsigned char *>(bstep + dst + 2 * m - 1);
             for (uint32_t j = 0; j < m; ++j) {
                 const uint32_t s = __ldg(steps + o0 + j);
                 const uint32_t l = (__ldg(map + (s >> 1)) << 1) | (s & 1u);
@@ -154,11 +155,14 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
                         if (h != kPairEmpty) pid = 2u * pd.ids[h] + flip;
                     }
                     bstep[dst + m + j - 1] = (uint16_t)pid;
+                    if (j >= 2) slots[j - 2] = (unsigned char)triple_slot(prev_pid, pid);
+                    prev_pid = pid;
                 }
                 prev = l;
             }
-            if (b != (uint32_t)kLongBucket)
-                for (uint32_t j = 2 * m - 1; j < row_stride((int)m); ++j) bstep[dst + j] = 0;
+            if (b != (uint32_t)kLongBucket)   // zero the padding behind the slot bytes
+                for (uint32_t j = 2 * (2 * m - 1) + (m > 2 ? m - 2 : 0); j < 2 * row_stride((int)m); ++j)
+                    reinterpret_cast<unsigned char *>(bstep + dst)[j] = 0;
         }
         __syncthreads();
     }

@@ -49,7 +49,6 @@ constexpr uint32_t kPairEmpty = 0xFFFFFFFFu;
 constexpr uint32_t kBloom = 128;      // hashed "broken triple" entries per orientation (bitset kernel)
 constexpr size_t kBitsetSmemBudget = 208 * 1024;   // mask table + counters per CTA
 
-// u16 elements per row of the length-m matrix: m steps + (m-1) pair ids, padded to 8 bytes
 // Hash of the consecutive-pair pair (qa, qb) = the triple (b_j-1, b_j, b_j+1), symmetric under
 // reverse complement up to the low bit: triple_slot(qb^1, qa^1) == triple_slot(qa, qb) ^ 1.
 __host__ __device__ inline uint32_t triple_slot(uint32_t qa, uint32_t qb) {
@@ -58,8 +57,10 @@ __host__ __device__ inline uint32_t triple_slot(uint32_t qa, uint32_t qb) {
     return (((canon * 0x9E3779B1u) >> 25) << 1) | (key != canon ? 1u : 0u);   // 2*kBloom slots
 }
 
+// (row = m steps + (m-1) pair ids as u16, then (m-2) one-byte triple slots — triple_slot of the two
+// pairs around each interior step — padded to 8 bytes)
 __host__ __device__ constexpr uint32_t row_stride(int m) {
-    return m <= 0 ? 0u : (uint32_t)((2 * m - 1 + 3) & ~3);
+    return m <= 0 ? 0u : (uint32_t)((2 * m - 1 + (m > 2 ? (m - 1) / 2 : 0) + 3) & ~3);
 }
 
 struct Buckets {
