@@ -175,7 +175,10 @@ __device__ __noinline__ void push_slow8(uint2 *__restrict__ slow, uint32_t *work
         while (mask) {
             const uint32_t c = (uint32_t)__ffs(mask) - 1u;
             mask &= mask - 1u;
-            if (idx < slow_cap) slow[idx] = make_uint2(word_base + c, row_first + u * row_step);
+            // masks 0-3: rows counted good for now, masks 4-7: the same rows counted bad for now
+            if (idx < slow_cap)
+                slow[idx] = make_uint2((word_base + c) | (u < 4 ? 0x80000000u : 0u),
+                                       row_first + (u & 3) * row_step);
             else atomicOr(work_count + 3, 1u);
             ++idx;
         }
@@ -190,7 +193,7 @@ __device__ __noinline__ void push_slow8(uint2 *__restrict__ slow, uint32_t *work
 //    B's last step, the pair (b_j, b_j+1) taken by the path; mirrored for rc(B).
 // What is still open after this goes to the (path, row) list of kernels.cu.
 template <int W>
-__device__ __noinline__ uint3 refine_row(const uint4 *__restrict__ nt, const uint32_t *__restrict__ tab,
+__device__ __noinline__ uint4 refine_row(const uint4 *__restrict__ nt, const uint32_t *__restrict__ tab,
                                          const uint16_t *__restrict__ rp, int m, uint32_t pair_base,
                                          uint32_t bt_base, uint32_t lm, int filter) {
     const uint32_t *mt = tab + (size_t)pair_base * W;
@@ -227,7 +230,9 @@ __device__ __noinline__ uint3 refine_row(const uint4 *__restrict__ nt, const uin
     const uint32_t sure = (fw & ~bfw) | (rc & ~brc);
     const uint32_t amb = (fw & bfw) | (rc & brc);
     const uint32_t open = in & ~lm & ~sure;
-    return make_uint3(in & (lm | sure), open & ~(amb | over), open & (amb | over));   // good, bad, slow
+    // good / bad include the optimistic guesses for what goes to the second-look list:
+    // an ambiguous candidate is most likely an occurrence, an overhang suspect most likely not
+    return make_uint4((in & (lm | sure)) | (open & amb), open & ~amb, open & amb, open & ~amb & over);
 }
 
 // One row of length M (its u16 elements packed two per register in q) against this lane's word.
@@ -281,6 +286,7 @@ __device__ __forceinline__ void eval_row(const uint4 *__restrict__ nt, const uin
     const uint32_t amb = (fw & bfw) | (rc & brc);
     const uint32_t open = in & ~lm & ~sure;
     good = in & (lm | sure);
+    good |= open & amb;               // optimistic: counted good now, corrected by the second look
     slow = open & amb;                // a broken (or hash-colliding) triple: second-look kernel
     over_open = open & ~amb & over;   // start-overhang suspects: refine_row decides
     bad = open & ~amb & ~over;
@@ -322,7 +328,7 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint4 *__r
                 q[k][2 * c + 1] = t.y;
             }
         }
-        uint32_t gm[UB], bm[UB], sm[UB], ov[UB], any_over = 0, any_slow = 0;
+        uint32_t gm[UB], bm[UB], sm[UB], sb[UB], ov[UB], any_over = 0, any_slow = 0;
 #pragma unroll
         for (int k = 0; k < UB; ++k) {
             eval_row<M, W>(nt, mt, bt, q[k], lm, filter, gm[k], bm[k], sm[k], ov[k]);
@@ -330,6 +336,7 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint4 *__r
             bm[k] = valid[k] ? bm[k] : 0u;
             sm[k] = valid[k] ? sm[k] : 0u;
             ov[k] = valid[k] ? ov[k] : 0u;
+            sb[k] = 0;
             any_over |= ov[k];
         }
         if (M >= 2 && __any_sync(0xFFFFFFFFu, any_over != 0)) {
@@ -337,21 +344,22 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint4 *__r
             for (int k = 0; k < UB; ++k) {
                 if (!__any_sync(0xFFFFFFFFu, ov[k] != 0)) continue;
                 const uint32_t r = it + k * R + sub;
-                const uint3 x = refine_row<W>(nt, tab, base + (size_t)(valid[k] ? r : 0u) * RS, M,
+                const uint4 x = refine_row<W>(nt, tab, base + (size_t)(valid[k] ? r : 0u) * RS, M,
                                               a.mg.pair_base, a.mg.bt_base, lm, a.filter);
                 gm[k] = valid[k] ? x.x : 0u;
                 bm[k] = valid[k] ? x.y : 0u;
                 sm[k] = valid[k] ? x.z : 0u;
+                sb[k] = valid[k] ? x.w : 0u;
             }
         }
         G.add(gm);
         B.add(bm);
 #pragma unroll
-        for (int k = 0; k < UB; ++k) any_slow |= sm[k];
+        for (int k = 0; k < UB; ++k) any_slow |= sm[k] | sb[k];
         if (__any_sync(0xFFFFFFFFu, any_slow != 0))
             push_slow8(a.slow, a.work_count, a.slow_cap, sm[0], sm[1], UB > 2 ? sm[UB > 2 ? 2 : 0] : 0u,
-                       UB > 2 ? sm[UB > 2 ? 3 : 0] : 0u, 0u, 0u, 0u, 0u, word_base, sorted0 + it + sub,
-                       (uint32_t)R, lane);
+                       UB > 2 ? sm[UB > 2 ? 3 : 0] : 0u, sb[0], sb[1], UB > 2 ? sb[UB > 2 ? 2 : 0] : 0u,
+                       UB > 2 ? sb[UB > 2 ? 3 : 0] : 0u, word_base, sorted0 + it + sub, (uint32_t)R, lane);
     }
 }
 

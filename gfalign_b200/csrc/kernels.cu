@@ -738,7 +738,9 @@ slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
     const uint32_t cnt = min(slow_count[0], slow_cap);
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < cnt;
          idx += gridDim.x * blockDim.x) {
-        const uint2 w = slow[idx];
+        uint2 w = slow[idx];
+        const uint32_t guess = w.x >> 31;   // the bitset kernel already counted this pair good (1) / bad (0)
+        w.x &= 0x7FFFFFFFu;
         const RowRef r = locate_row(a.bk, w.y);
         const int m = (int)r.m;
         const uint32_t po = a.poff[w.x];
@@ -748,11 +750,13 @@ slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
         // it, and for a start-overhang suspect it finds nothing at the cost of one table read
         const int v = slow_verdict(a.pstep + po, a.pnext + po, n, tab, r.ptr, m, true);
         if (v == kExact) {
+            atomicSub(&a.counts[2 * (size_t)w.x + guess], 1u);   // the exact DP adds the right one
             const uint32_t k = atomicAdd(a.work_count, 1u);
             if (k < a.work_cap) a.work[k] = w;
             else atomicOr(a.work_count + 1, 1u);
-        } else {
-            atomicAdd(&a.counts[2 * (size_t)w.x + (v == kGood ? 1 : 0)], 1u);
+        } else if ((v == kGood ? 1u : 0u) != guess) {          // correct the rare wrong guess
+            atomicSub(&a.counts[2 * (size_t)w.x + guess], 1u);
+            atomicAdd(&a.counts[2 * (size_t)w.x + (guess ^ 1u)], 1u);
         }
     }
 }
