@@ -209,3 +209,32 @@ def test_max_size_path_evalpath(engine, oracle):
     tf, tr, bad, good = engine.score_pairs(path)
     ob, og, otf, otr = oracle.evaluate_path(path, off, steps, False, scores=True)
     assert np.array_equal(tf, otf) and np.array_equal(tr, otr) and (bad, good) == (ob, og)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_repeated_nodes_stress(engine, oracle, seed):
+    """Paths that revisit nodes many times (and take self-reverse-complement pairs): the bitset
+    kernel's broken-triple certification and start-overhang test against the oracle."""
+    rng = np.random.default_rng(100 + seed)
+    alpha = int(rng.integers(2, 7))
+    off, steps = _rand_csr(rng, 6000, alpha, [1, 2, 2, 3, 3, 4, 4, 5, 6, 8, 12, 16])
+    P = int(rng.integers(33, 200))
+    plen = rng.integers(1, 60, size=P)
+    po = np.zeros(P + 1, dtype=np.uint32)
+    po[1:] = np.cumsum(plen)
+    ps = (rng.integers(0, alpha, size=int(po[-1])) * 2 + rng.integers(0, 2, size=int(po[-1]))).astype(np.uint32)
+    # plant sub-walks of the paths (both orientations) so that occurrences are common
+    for a in range(0, 6000, 2):
+        m = int(off[a + 1] - off[a])
+        p = int(rng.integers(0, P))
+        n = int(po[p + 1] - po[p])
+        if m <= n:
+            s = int(rng.integers(0, n - m + 1))
+            w = ps[po[p] + s: po[p] + s + m]
+            steps[off[a]:off[a + 1]] = w if a % 4 else (w[::-1] ^ 1)
+    engine.set_alignments(off, steps, alpha)
+    engine.set_universe(np.arange(alpha, dtype=np.uint32))
+    for filt in (True, False):
+        got = engine.score_paths(po, ps, filter=filt)
+        want = oracle.evaluate_paths(po, ps, off, steps, filt, 8)
+        assert np.array_equal(got, want), (seed, alpha, filt)
