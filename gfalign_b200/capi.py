@@ -42,6 +42,12 @@ class _Graph(C.Structure):
                 ("adj_or0", _u8p), ("adj_or1", _u8p)]
 
 
+class _TextView(C.Structure):
+    _fields_ = [("n_nodes", C.c_uint32), ("n_links", C.c_uint32), ("edge_from", _u32p),
+                ("edge_to", _u32p), ("graph", _Graph), ("A", C.c_uint64), ("offsets", _u32p),
+                ("steps", _u32p)]
+
+
 class _SearchParams(C.Structure):
     _fields_ = [("source", C.c_uint32), ("destination", C.c_uint32), ("budget_nodes", _u32p),
                 ("budget_counts", _u32p), ("n_budget", C.c_uint32), ("node_count", C.c_uint32),
@@ -71,6 +77,9 @@ EXPORTS = [
     "gfe_score_pairs", "gfe_edge_support", "gfe_edge_traversals_device",
     "gfe_edge_weights_from_counts", "gfe_search", "gfe_search_with_scorer", "gfe_get_counters", "gfe_set_timing",
     "gfe_last_kernel_ms", "gfe_kernel_time_stats", "gfe_device_status",
+    "gfe_trace_pairs", "gfe_filter_alignments",
+    "gfe_text_open", "gfe_text_close", "gfe_text_get", "gfe_text_node_name", "gfe_text_node_id",
+    "gfe_text_qname",
 ]
 
 _lib = None
@@ -116,6 +125,20 @@ def load_library() -> C.CDLL:
     lib.gfe_last_kernel_ms.restype = C.c_float
     lib.gfe_device_status.argtypes = [C.c_void_p, _u32p]
     lib.gfe_kernel_time_stats.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_uint32)]
+    lib.gfe_trace_pairs.argtypes = [C.c_void_p, _u32p, C.c_uint32, C.c_uint64, C.c_uint32, _u8p, _u8p,
+                                    C.c_uint64, C.POINTER(C.c_uint64), _u32p, _i32p]
+    lib.gfe_filter_alignments.argtypes = [C.c_void_p, _u32p, C.c_uint32, C.c_int32, _u8p]
+    lib.gfe_text_open.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_void_p), C.c_char_p,
+                                  C.c_size_t]
+    lib.gfe_text_close.argtypes = [C.c_void_p]
+    lib.gfe_text_close.restype = None
+    lib.gfe_text_get.argtypes = [C.c_void_p, C.POINTER(_TextView)]
+    lib.gfe_text_node_name.argtypes = [C.c_void_p, C.c_uint32]
+    lib.gfe_text_node_name.restype = C.c_char_p
+    lib.gfe_text_node_id.argtypes = [C.c_void_p, C.c_char_p]
+    lib.gfe_text_node_id.restype = C.c_int64
+    lib.gfe_text_qname.argtypes = [C.c_void_p, C.c_uint64, _u32p]
+    lib.gfe_text_qname.restype = C.c_void_p
     _lib = lib
     return lib
 
@@ -226,6 +249,32 @@ class Engine:
         self._check(self._lib.gfe_score_pairs(self._h, _ptr(ps), ps.size, int(filter), None, None,
                                               C.byref(bad), C.byref(good)))
         return None, None, bad.value, good.value
+
+    def trace_pairs(self, path_steps, first: int, count: int, use_rc, offsets):
+        """evalPath detail: per pair the traceback columns (list of uint8 arrays; 0 equal, 1
+        different, 2 path step vs gap, 3 alignment step vs gap in the path) and the score."""
+        ps = _u32(path_steps)
+        off = np.asarray(offsets, dtype=np.int64)
+        cap = int(off[first + count] - off[first]) + count * ps.size
+        ops = np.zeros(max(cap, 1), dtype=np.uint8)
+        rc = np.ascontiguousarray(use_rc, dtype=np.uint8)
+        start = np.zeros(max(count, 1), dtype=np.uint64)
+        ln = np.zeros(max(count, 1), dtype=np.uint32)
+        score = np.zeros(max(count, 1), dtype=np.int32)
+        self._check(self._lib.gfe_trace_pairs(self._h, _ptr(ps), ps.size, first, count, _ptr(rc, _u8p),
+                                              _ptr(ops, _u8p), cap,
+                                              start.ctypes.data_as(C.POINTER(C.c_uint64)), _ptr(ln),
+                                              _ptr(score, _i32p)))
+        cols = [ops[int(start[k]):int(start[k]) + int(ln[k])] for k in range(count)]
+        return cols, score[:count]
+
+    def filter_alignments(self, nodes, min_nodes: int = 0) -> np.ndarray:
+        """filter mode: keep[a] = all nodes of alignment a in `nodes` and m >= min_nodes."""
+        nd = _u32(nodes)
+        keep = np.zeros(max(self._A_hint, 1), dtype=np.uint8)
+        self._check(self._lib.gfe_filter_alignments(self._h, _ptr(nd), nd.size, int(min_nodes),
+                                                    _ptr(keep, _u8p)))
+        return keep[:self._A_hint].astype(bool)
 
     # -- edge support ------------------------------------------------------------------------
     def edge_support(self, edge_from, edge_to) -> np.ndarray:
@@ -362,3 +411,44 @@ def _set_alignments(self, offsets, steps, n_nodes):
 
 
 Engine.set_alignments = _set_alignments
+
+
+class TextPack:
+    """GFA1 (+ GAF) text packed by the C++ host packers (gfe_text_*); arrays are copies."""
+
+    def __init__(self, gfa_path: str, gaf_path: Optional[str] = None, threads: int = 0):
+        lib = load_library()
+        h = C.c_void_p()
+        err = C.create_string_buffer(512)
+        rc = lib.gfe_text_open(gfa_path.encode(), gaf_path.encode() if gaf_path else None, threads,
+                               C.byref(h), err, 512)
+        if rc != 0:
+            raise GfeError(rc, err.value.decode(errors="replace"))
+        try:
+            v = _TextView()
+            lib.gfe_text_get(h, C.byref(v))
+            take = lambda p, n, dt: (np.ctypeslib.as_array(p, shape=(n,)).astype(dt).copy()  # noqa: E731
+                                     if n else np.zeros(0, dtype=dt))
+            self.n_nodes = v.n_nodes
+            self.names = [lib.gfe_text_node_name(h, i).decode() for i in range(v.n_nodes)]
+            self.edge_from = take(v.edge_from, v.n_links, np.uint32)
+            self.edge_to = take(v.edge_to, v.n_links, np.uint32)
+            self.adj_offsets = take(v.graph.adj_offsets, v.n_nodes + 1, np.uint32)
+            n_adj = int(self.adj_offsets[-1]) if v.n_nodes else 0
+            self.adj_target = take(v.graph.adj_target, n_adj, np.uint32)
+            self.adj_or0 = take(v.graph.adj_or0, n_adj, np.uint8)
+            self.adj_or1 = take(v.graph.adj_or1, n_adj, np.uint8)
+            self.A = int(v.A)
+            self.offsets = take(v.offsets, self.A + 1, np.uint32) if gaf_path else np.zeros(1, np.uint32)
+            self.steps = take(v.steps, int(self.offsets[-1]), np.uint32)
+            self.qnames = []
+            ln = C.c_uint32()
+            for a in range(self.A if self.A <= 200000 else 0):
+                p = lib.gfe_text_qname(h, a, C.byref(ln))
+                self.qnames.append(C.string_at(p, ln.value).decode(errors="replace"))
+            assert all(lib.gfe_text_node_id(h, nm.encode()) == i
+                       for i, nm in enumerate(self.names[:1000]))
+            self._ids = {nm: i for i, nm in enumerate(self.names)}
+            self.node_id = lambda name: self._ids.get(name, -1)
+        finally:
+            lib.gfe_text_close(h)

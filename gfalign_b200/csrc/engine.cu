@@ -863,4 +863,176 @@ int gfe_edge_support(gfe_engine *e, const uint32_t *edge_from, const uint32_t *e
     return gfe_edge_weights_from_counts(edge_from, edge_to, E, counts.data(), weights);
 }
 
+// ---- evalPath detail: traceback columns ----------------------------------------------------------
+
+int gfe_trace_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, uint64_t first,
+                    uint32_t count, const uint8_t *use_rc, uint8_t *ops, uint64_t ops_capacity,
+                    uint64_t *ops_first, uint32_t *ops_len, int32_t *score) {
+    if (!e || !path_steps || !ops_first || !ops_len || (!ops && ops_capacity)) return GFE_ERR_ARG;
+    if (!e->have_alignments) {
+        set_error(e, "gfe_trace_pairs: call gfe_set_alignments first");
+        return GFE_ERR_STATE;
+    }
+    if (n == 0 || n > GFE_MAX_STEPS) {
+        set_error(e, "gfe_trace_pairs: path has %u steps; allowed 1..%u", n, GFE_MAX_STEPS);
+        return n == 0 ? GFE_ERR_ARG : GFE_ERR_LIMIT;
+    }
+    if (first > e->A || count > e->A - first) {
+        set_error(e, "gfe_trace_pairs: alignments [%llu, +%u) out of range (A = %llu)",
+                  (unsigned long long)first, count, (unsigned long long)e->A);
+        return GFE_ERR_ARG;
+    }
+    if (count == 0) return GFE_OK;
+    for (uint32_t i = 0; i < n; ++i)
+        if ((path_steps[i] >> 1) >= e->n_nodes) {
+            set_error(e, "gfe_trace_pairs: step %u names node %u >= n_nodes %u", i,
+                      path_steps[i] >> 1, e->n_nodes);
+            return GFE_ERR_ARG;
+        }
+    cudaStream_t st = e->stream;
+    // total ops bytes of the request = steps in range + count * n
+    uint32_t range[2];
+    CUDA_TRY(e, cudaMemcpyAsync(&range[0], e->d_off + first, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(e, cudaMemcpyAsync(&range[1], e->d_off + first + count, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(e, cudaStreamSynchronize(st));
+    const uint64_t need = (uint64_t)(range[1] - range[0]) + (uint64_t)count * n;
+    if (ops_capacity < need) {
+        set_error(e, "gfe_trace_pairs: ops buffer holds %llu bytes, %llu needed",
+                  (unsigned long long)ops_capacity, (unsigned long long)need);
+        return GFE_ERR_ARG;
+    }
+    TRY(ensure_dev(e, e->d_tr_path, n));
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_tr_path.ptr, path_steps, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    e->h2d_bytes += (uint64_t)n * 4;
+    const size_t budget_words = (size_t)1 << 28;   // 1 GiB of decision words per sub-batch
+    uint32_t done = 0;
+    uint64_t ops_done = 0;   // bytes of ops regions before the current sub-batch
+    while (done < count) {
+        // sub-batch size: start from what fits with W = 1, shrink once the real max m is known
+        uint32_t sub = (uint32_t)std::min<uint64_t>(count - done, std::max<size_t>(budget_words / n, 1));
+        uint32_t max_m = 0, W = 1;
+        for (;;) {
+            TRY(ensure_dev(e, e->d_tr_misc, 4));
+            CUDA_TRY(e, cudaMemsetAsync(e->d_tr_misc.ptr, 0, 4, st));
+            launch_max_len(e->d_off, first + done, sub, e->d_tr_misc.ptr, st);
+            e->kernel_launches += 1;
+            CUDA_TRY(e, cudaMemcpyAsync(&max_m, e->d_tr_misc.ptr, 4, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(e, cudaStreamSynchronize(st));
+            W = std::max<uint32_t>((max_m + 15) / 16, 1);
+            const size_t per_pair = (size_t)n * W + (max_m > 32 ? (size_t)max_m * 2 : 0);
+            const uint32_t fit = (uint32_t)std::max<size_t>(budget_words / per_pair, 1);
+            if (fit >= sub) break;
+            sub = fit;
+        }
+        const uint64_t f0 = first + done;
+        uint32_t sr[2];
+        CUDA_TRY(e, cudaMemcpyAsync(&sr[0], e->d_off + f0, 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(e, cudaMemcpyAsync(&sr[1], e->d_off + f0 + sub, 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(e, cudaStreamSynchronize(st));
+        const uint64_t sub_ops = (uint64_t)(sr[1] - sr[0]) + (uint64_t)sub * n;
+        TRY(ensure_dev(e, e->d_tr_dirs, (size_t)n * sub * W));
+        TRY(ensure_dev(e, e->d_tr_base, sub));
+        TRY(ensure_dev(e, e->d_tr_first, sub));
+        TRY(ensure_dev(e, e->d_tr_len, sub));
+        TRY(ensure_dev(e, e->d_tr_score, sub));
+        TRY(ensure_dev(e, e->d_tr_ops, sub_ops));
+        TRY(ensure_dev(e, e->d_tr_rc, sub));
+        if (max_m > 32) {
+            TRY(ensure_dev(e, e->d_tr_longb, (size_t)sub * max_m));
+            TRY(ensure_dev(e, e->d_tr_longrows, (size_t)sub * (max_m + 1)));
+        }
+        if (use_rc) {
+            CUDA_TRY(e, cudaMemcpyAsync(e->d_tr_rc.ptr, use_rc + done, sub, cudaMemcpyHostToDevice, st));
+            e->h2d_bytes += sub;
+        }
+        launch_trace_bases(e->d_off, f0, sub, n, e->d_tr_base.ptr, st);
+        TraceArgs a;
+        a.off = e->d_off;
+        a.steps = e->d_steps;
+        a.path = e->d_tr_path.ptr;
+        a.n = n;
+        a.first = f0;
+        a.count = sub;
+        a.use_rc = use_rc ? e->d_tr_rc.ptr : nullptr;
+        a.W = W;
+        a.dirs = e->d_tr_dirs.ptr;
+        a.long_b = e->d_tr_longb.ptr;
+        a.long_rows = e->d_tr_longrows.ptr;
+        a.long_stride = max_m;
+        a.ops_start_base = e->d_tr_base.ptr;
+        a.ops = e->d_tr_ops.ptr;
+        a.ops_first = e->d_tr_first.ptr;
+        a.ops_len = e->d_tr_len.ptr;
+        a.score = e->d_tr_score.ptr;
+        if (e->timing) {
+            TRY(next_event_pair(e));
+            CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+        }
+        launch_pair_trace(a, st);
+        if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
+        e->kernel_launches += 2;
+        CUDA_TRY(e, cudaGetLastError());
+        CUDA_TRY(e, cudaMemcpyAsync(ops + ops_done, e->d_tr_ops.ptr, sub_ops, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(e, cudaMemcpyAsync(ops_first + done, e->d_tr_first.ptr, (size_t)sub * 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(e, cudaMemcpyAsync(ops_len + done, e->d_tr_len.ptr, (size_t)sub * 4, cudaMemcpyDeviceToHost, st));
+        if (score)
+            CUDA_TRY(e, cudaMemcpyAsync(score + done, e->d_tr_score.ptr, (size_t)sub * 4, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(e, cudaStreamSynchronize(st));
+        if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
+        e->d2h_bytes += sub_ops + (uint64_t)sub * (score ? 16 : 12);
+        for (uint32_t k = 0; k < sub; ++k) ops_first[done + k] += ops_done;   // sub-batch -> request
+        done += sub;
+        ops_done += sub_ops;
+    }
+    return GFE_OK;
+}
+
+// ---- filter mode: membership of every alignment in a node set ------------------------------------
+
+int gfe_filter_alignments(gfe_engine *e, const uint32_t *nodes, uint32_t n, int32_t min_nodes,
+                          uint8_t *keep) {
+    if (!e || (!nodes && n) || !keep) return GFE_ERR_ARG;
+    if (!e->have_alignments) {
+        set_error(e, "gfe_filter_alignments: call gfe_set_alignments first");
+        return GFE_ERR_STATE;
+    }
+    if (e->A == 0) return GFE_OK;
+    const size_t words = ((size_t)e->n_nodes + 31) / 32 + 1;
+    std::vector<uint32_t> bits(words, 0);
+    for (uint32_t i = 0; i < n; ++i) {
+        if (nodes[i] >= e->n_nodes) {
+            set_error(e, "gfe_filter_alignments: node %u >= n_nodes %u", nodes[i], e->n_nodes);
+            return GFE_ERR_ARG;
+        }
+        bits[nodes[i] >> 5] |= 1u << (nodes[i] & 31);
+    }
+    cudaStream_t st = e->stream;
+    TRY(ensure_dev(e, e->d_tr_misc, words));
+    TRY(ensure_dev(e, e->d_tr_rc, e->A));
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_tr_misc.ptr, bits.data(), words * 4, cudaMemcpyHostToDevice, st));
+    FilterArgs a;
+    a.off = e->d_off;
+    a.steps = e->d_steps;
+    a.A = e->A;
+    a.node_bits = e->d_tr_misc.ptr;
+    a.n_nodes = e->n_nodes;
+    a.min_nodes = min_nodes;
+    a.keep = e->d_tr_rc.ptr;
+    if (e->timing) {
+        TRY(next_event_pair(e));
+        CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    }
+    launch_filter_rows(a, st);
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
+    e->kernel_launches += 1;
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaMemcpyAsync(keep, e->d_tr_rc.ptr, e->A, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(e, cudaStreamSynchronize(st));
+    if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
+    e->h2d_bytes += words * 4;
+    e->d2h_bytes += e->A;
+    return GFE_OK;
+}
+
+
 }  // extern "C"

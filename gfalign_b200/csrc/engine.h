@@ -74,6 +74,13 @@ struct gfe_engine {
     // evalPath outputs
     DevBuf<int32_t> d_tfw, d_trc;
 
+    // evalPath traceback / filter scratch
+    DevBuf<uint32_t> d_tr_path, d_tr_misc, d_tr_dirs, d_tr_len, d_tr_longb;
+    DevBuf<uint64_t> d_tr_base, d_tr_first;
+    DevBuf<int32_t> d_tr_score;
+    DevBuf<int16_t> d_tr_longrows;
+    DevBuf<uint8_t> d_tr_ops, d_tr_rc;
+
     // edge support
     DevBuf<uint32_t> d_row_off, d_edge_counts;
     DevBuf<uint2> d_row_ent;
@@ -91,6 +98,9 @@ struct gfe_engine {
         fd(d_row_off.ptr); fd(d_edge_counts.ptr); fd(d_row_ent.ptr);
         fd(d_pair_keys.ptr); fd(d_pair_ids.ptr); fd(d_pair_ctr.ptr); fd(d_masks.ptr);
         fd(d_unit_ctr.ptr); fd(d_slow.ptr);
+        fd(d_tr_path.ptr); fd(d_tr_misc.ptr); fd(d_tr_dirs.ptr); fd(d_tr_len.ptr); fd(d_tr_longb.ptr);
+        fd(d_tr_base.ptr); fd(d_tr_first.ptr); fd(d_tr_score.ptr); fd(d_tr_longrows.ptr);
+        fd(d_tr_ops.ptr); fd(d_tr_rc.ptr);
         fh(h_stage.ptr); fh(h_counts.ptr);
     }
 };

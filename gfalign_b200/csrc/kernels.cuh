@@ -146,6 +146,36 @@ struct EdgeArgs {
     uint32_t n_slots;
 };
 
+struct TraceArgs {            // evalPath detail: traceback columns of one path vs a batch of alignments
+    const uint32_t *off;      // original CSR (global node ids)
+    const uint32_t *steps;
+    const uint32_t *path;     // n oriented steps, global ids
+    uint32_t n;
+    uint64_t first;           // first alignment of the batch
+    uint32_t count;
+    const uint8_t *use_rc;    // per pair: align against the reverse complement (may be null)
+    uint32_t W;               // decision words per DP row = ceil(max m of the batch / 16)
+    uint32_t *dirs;           // n * count * W words
+    uint32_t *long_b;         // count * long_stride (only when the batch has m > 32)
+    int16_t *long_rows;       // count * (long_stride + 1)
+    uint32_t long_stride;
+    const uint64_t *ops_start_base;   // per pair: start of its (n + m)-byte region in ops
+    uint8_t *ops;
+    uint64_t *ops_first;      // out: index of the pair's first column in ops
+    uint32_t *ops_len;        // out: columns
+    int32_t *score;           // out (may be null): traceback score
+};
+
+struct FilterArgs {           // filter mode: rows whose nodes all lie in a set, with at least min_nodes steps
+    const uint32_t *off;
+    const uint32_t *steps;
+    uint64_t A;
+    const uint32_t *node_bits;   // bitmap over n_nodes
+    uint32_t n_nodes;
+    int32_t min_nodes;
+    uint8_t *keep;
+};
+
 // hist: kNumBuckets counters, [kNumBuckets] = max length, [kNumBuckets+1] = steps of long rows
 void launch_length_histogram(const uint32_t *off, uint64_t A, uint32_t *hist, cudaStream_t st);
 // cursors: kNumBuckets row cursors + [kNumBuckets] long-step cursor (zeroed by the caller)
@@ -177,6 +207,12 @@ void launch_pair_classify(const PairArgs &a, int sm_count, cudaStream_t st);
 void launch_pair_exact(const PairArgs &a, cudaStream_t st);
 void launch_pair_exact_long(const PairArgs &a, uint32_t max_m, cudaStream_t st);
 void launch_edge_support(const EdgeArgs &a, int sm_count, cudaStream_t st);
+void launch_max_len(const uint32_t *off, uint64_t first, uint32_t count, uint32_t *out,
+                    cudaStream_t st);
+void launch_trace_bases(const uint32_t *off, uint64_t first, uint32_t count, uint32_t n,
+                        uint64_t *base, cudaStream_t st);
+void launch_pair_trace(const TraceArgs &a, cudaStream_t st);
+void launch_filter_rows(const FilterArgs &a, cudaStream_t st);
 int configure_kernels();   // cudaFuncSetAttribute for the large-shared-memory kernels
 
 }  // namespace gfe

@@ -97,6 +97,29 @@ int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
 int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int filter,
                     int32_t *t_fw, int32_t *t_rc, uint32_t *bad, uint32_t *good);
 
+/* ---- evalPath detail: the gapped alignment strings ------------------------------------------------
+ * Replaces get_optimal_alignment's SA/SB (reference src/alignments.cpp:511-554) as printed by
+ * PairwisePathAlignment::getAlignment (include/alignments.h:98-122) from evaluatePath
+ * (src/eval.cpp:100-105): for ONE path and the alignments [first, first + count), the traceback of
+ * alignPaths(path, B) where B is the alignment (use_rc[k] == 0 or use_rc == NULL) or its reverse
+ * complement (use_rc[k] != 0; the reference prints the rc alignment unless T_fw > T_rc).
+ * Output: one op byte per alignment column, columns in path order:
+ *     0  path step == alignment step          1  both present, different
+ *     2  path step against a gap              3  alignment step against a gap in the path
+ * Pair k's columns are ops[ops_first[k] .. ops_first[k] + ops_len[k]); the caller sizes ops to
+ * (offsets[first+count] - offsets[first]) + count * n bytes.  score (may be NULL) receives the
+ * traceback score of the chosen direction (== t_fw / t_rc of gfe_score_pairs). */
+int gfe_trace_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, uint64_t first,
+                    uint32_t count, const uint8_t *use_rc, uint8_t *ops, uint64_t ops_capacity,
+                    uint64_t *ops_first, uint32_t *ops_len, int32_t *score);
+
+/* ---- filter mode --------------------------------------------------------------------------------
+ * Replaces InAlignments::filterAlignmentByNodelist (reference src/alignments.cpp:459-472 with
+ * isContained :96-114 and pathNodesCount :116-135): keep[a] = 1 iff every step of alignment a names
+ * a node of `nodes` and the alignment has at least min_nodes steps. */
+int gfe_filter_alignments(gfe_engine *e, const uint32_t *nodes, uint32_t n, int32_t min_nodes,
+                          uint8_t *keep /* A */);
+
 /* ---- evalGFA: per-edge read support -------------------------------------------------------------
  * Replaces InAlignments::buildEdgeGraph (reference src/alignments.cpp:353-403) + the per-edge
  * lookup of evalGFA (src/eval.cpp:42-60).  edges are the graph's L lines in file order as
@@ -171,6 +194,30 @@ typedef int (*gfe_score_fn)(void *score_user, const uint32_t *path_offsets,
 int gfe_search_with_scorer(gfe_score_fn score, void *score_user, const gfe_graph *g,
                            const gfe_search_params *p, gfe_row_fn emit, void *user,
                            gfe_search_stats *stats);
+
+/* ---- text packers (host only, no GPU needed) ------------------------------------------------------
+ * GFA1 / GAF text -> the packed arrays the entry points above take.  Replaces, for this path,
+ * gfalibs' readGFA (reference gfalibs/src/input-gfa.cpp:497-641: S and L records, name -> id),
+ * InSequences::buildEdgeGraph (gfalibs/src/gfa.cpp:1076-1097), InAlignments::load +
+ * InAlignment::GAFpathToPath (reference src/alignments.cpp:143-235, 75-94).  Nodes get dense ids in
+ * order of first appearance (S records, then names first seen on L records); a walk name the
+ * graph does not know becomes node 0, as the reference's headersToIds[...] default-inserts 0
+ * (src/alignments.cpp:86).  The GAF is parsed by `threads` host threads (<= 0: all cores). */
+typedef struct gfe_text gfe_text;
+typedef struct gfe_text_view {
+    uint32_t n_nodes, n_links;
+    const uint32_t *edge_from, *edge_to;   /* L records in file order, oriented steps */
+    gfe_graph graph;                       /* adjacency for gfe_search */
+    uint64_t A;                            /* alignments (0 when no GAF was given) */
+    const uint32_t *offsets, *steps;       /* CSR for gfe_set_alignments */
+} gfe_text_view;
+int gfe_text_open(const char *gfa_path, const char *gaf_path /* may be NULL */, int threads,
+                  gfe_text **out, char *err, size_t err_len);
+void gfe_text_close(gfe_text *t);
+int gfe_text_get(const gfe_text *t, gfe_text_view *out);
+const char *gfe_text_node_name(const gfe_text *t, uint32_t node);
+int64_t gfe_text_node_id(const gfe_text *t, const char *name);   /* -1: unknown */
+const char *gfe_text_qname(const gfe_text *t, uint64_t a, uint32_t *len);   /* not NUL-terminated */
 
 /* ---- introspection (bench / tests) --------------------------------------------------------------*/
 typedef struct gfe_counters {

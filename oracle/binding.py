@@ -62,6 +62,15 @@ class Oracle:
         A, B = _u32(A), _u32(B)
         return int(self.lib.orc_pair_score(_p(A), A.size, _p(B), B.size))
 
+    def pair_alignment(self, A, B):
+        """-> (SA, SB, score): gapped sequences in path order, 0xFFFFFFFF = gap."""
+        A, B = _u32(A), _u32(B)
+        SA = np.zeros(A.size + B.size + 1, dtype=np.uint32)
+        SB = np.zeros(A.size + B.size + 1, dtype=np.uint32)
+        sc = C.c_int32()
+        n = self.lib.orc_pair_alignment(_p(A), A.size, _p(B), B.size, _p(SA), _p(SB), C.byref(sc))
+        return SA[:n], SB[:n], sc.value
+
     def evaluate_path(self, path, offsets, steps, filter: bool, scores: bool = False):
         path, offsets, steps = _u32(path), _u32(offsets), _u32(steps)
         A = offsets.size - 1

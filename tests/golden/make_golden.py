@@ -69,7 +69,8 @@ def make_pairs(shim):
 
 
 def run_ref(binary, args, cwd):
-    p = subprocess.run([binary] + args, cwd=cwd, capture_output=True, text=True)
+    # always bounded: the reference can hang on its error paths (thread pool never joined)
+    p = subprocess.run([binary] + args, cwd=cwd, capture_output=True, text=True, timeout=120)
     return p.stdout, p.returncode
 
 
@@ -83,7 +84,9 @@ def cli_case(binary, name, files, args, outfile=None):
         case = {"name": name, "files": files, "args": args, "stdout": out, "rc": rc}
         if outfile:
             with open(os.path.join(wd, outfile)) as f:
-                case["out_L_lines"] = [l.rstrip("\n") for l in f if l.startswith("L\t")]
+                text = f.read()
+            case["out_L_lines"] = [l for l in text.split("\n") if l.startswith("L\t")]
+            case["out_text"] = text
         return case
 
 
@@ -128,6 +131,19 @@ def make_cli(binary):
     cases.append(cli_case(binary, "hairpin_evalgfa", hp,
                           ["evalGFA", "-j", "1", "-g", "h.gaf", "-f", "h.gfa", "-o", "dec.gfa"],
                           outfile="dec.gfa"))
+    # filter mode (reference testFiles + a ':'-bearing tag, a numeric column with leading zeros)
+    r3f = dict(r3)
+    r3f["random3.filter_nodelist.ls"] = rd("random3.filter_nodelist.ls")
+    fb = ["filter", "-j", "1", "-g", "random3.gaf", "-n", "random3.filter_nodelist.ls"]
+    cases.append(cli_case(binary, "random3_filter", r3f, fb + ["-o", "out.gaf"], outfile="out.gaf"))
+    cases.append(cli_case(binary, "random3_filter_min3", r3f, fb + ["--min-nodes", "3", "-o", "out.gaf"],
+                          outfile="out.gaf"))
+    odd = {"n.ls": "a\nb\nc\n",
+           "a.gaf": "r1\t010\t0\t10\t+\t>a<b\t10\t0\t10\t10\t10\t60\ttp:A:P\tzz:Z:x:y\n"
+                    "r2\t12\t1\t9\t-\t>a>d\t10\t0\t10\t9\t10\t0\n"
+                    "r3\t7\t0\t7\t+\t<c\t7\t0\t7\t7\t7\t30\n"}
+    cases.append(cli_case(binary, "odd_filter", odd, ["filter", "-j", "1", "-g", "a.gaf", "-n", "n.ls",
+                                                      "-o", "out.gaf"], outfile="out.gaf"))
     # seeded synthetic tangles: search (driver order + scoring), evalPath (per-pair scores), evalGFA
     for k, (n_nodes, extra, A, c2, m_steps) in enumerate([(12, 14, 300, 0.3, 400), (30, 40, 1500, 0.1, 300),
                                                          (60, 70, 4000, 0.05, 150), (8, 16, 200, 0.5, 500)]):
@@ -145,6 +161,12 @@ def make_cli(binary):
             p = ",".join(synth.step_str(t.names, int(s)) for s in ps[po[i]:po[i + 1]])
             cases.append(cli_case(binary, f"tangle{k}_evalpath_{i}", files,
                                   ["evalPath", "-j", "1", "-f", "g.gfa", "-g", "a.gaf", "-p", p]))
+        keep = "".join(nm + "\n" for nm in t.names[: max(3, (2 * n_nodes) // 3)])
+        ff = dict(files)
+        ff["keep.ls"] = keep
+        cases.append(cli_case(binary, f"tangle{k}_filter", ff,
+                              ["filter", "-j", "1", "-g", "a.gaf", "-n", "keep.ls", "--min-nodes", "2",
+                               "-o", "out.gaf"], outfile="out.gaf"))
         cases.append(cli_case(binary, f"tangle{k}_evalgfa", files,
                               ["evalGFA", "-j", "1", "-g", "a.gaf", "-f", "g.gfa", "-o", "dec.gfa"],
                               outfile="dec.gfa"))

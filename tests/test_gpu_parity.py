@@ -238,3 +238,91 @@ def test_repeated_nodes_stress(engine, oracle, seed):
         got = engine.score_paths(po, ps, filter=filt)
         want = oracle.evaluate_paths(po, ps, off, steps, filt, 8)
         assert np.array_equal(got, want), (seed, alpha, filt)
+
+
+# ---- evalPath detail (traceback columns) and filter mode ------------------------------------------
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("alpha,n_hi,m_hi,seed", [(3, 12, 8, 1), (6, 40, 17, 2), (4, 30, 60, 3),
+                                                  (12, 200, 10, 4)])
+def test_trace_pairs_matches_oracle(engine, oracle, alpha, n_hi, m_hi, seed):
+    from evalpath_text import ops_from_gapped
+    rng = np.random.default_rng(seed)
+    lens = rng.integers(0, m_hi + 1, 400)
+    off, st = _rand_csr(rng, 400, alpha, lens)
+    engine.set_alignments(off, st, alpha)
+    n = int(rng.integers(1, n_hi + 1))
+    path = (rng.integers(0, alpha, n) * 2 + rng.integers(0, 2, n)).astype(np.uint32)
+    use_rc = rng.integers(0, 2, 400).astype(np.uint8)
+    for first, count in ((0, 400), (37, 101), (399, 1), (5, 0)):
+        cols, score = engine.trace_pairs(path, first, count, use_rc[first:first + count], off)
+        for k in range(count):
+            B = st[off[first + k]:off[first + k + 1]]
+            if use_rc[first + k]:
+                B = (B[::-1] ^ 1).astype(np.uint32)
+            SA, SB, sc = oracle.pair_alignment(path, B)
+            assert cols[k].tolist() == ops_from_gapped(SA, SB), (first, k)
+            assert int(score[k]) == sc == oracle.pair_score(path, B)
+
+
+@pytest.mark.gpu
+def test_golden_evalpath_stdout_through_engine(engine):
+    """Full evalPath stdout (gapped strings, scores, totals) of the golden cases from
+    gfe_score_pairs + gfe_trace_pairs."""
+    from gfalign_b200 import textio
+    from evalpath_text import evalpath_stdout
+    seen = 0
+    for c in _cases():
+        if "_evalpath_" not in c["name"]:
+            continue
+        gfa = next(v for k, v in c["files"].items() if k.endswith(".gfa"))
+        gaf = next(v for k, v in c["files"].items() if k.endswith(".gaf"))
+        names, _, _ = textio.parse_gfa(gfa)
+        qn, off, st = textio.parse_gaf(gaf, names)
+        path = textio.parse_path(c["args"][c["args"].index("-p") + 1], names)
+        engine.set_alignments(off, st, len(names))
+        tf, tr, _, _ = engine.score_pairs(path, filter=False)
+        use_rc = (~(tf > tr)).astype(np.uint8)
+        cols, score = engine.trace_pairs(path, 0, len(qn), use_rc, off)
+        assert np.array_equal(score, np.where(use_rc == 1, tr, tf))
+        it = iter(cols)
+        text = evalpath_stdout(names, path, qn, off, st, tf, tr, lambda p, B: next(it).tolist())
+        assert text == c["stdout"], c["name"]
+        seen += 1
+    assert seen >= 18
+
+
+@pytest.mark.gpu
+def test_trace_pairs_max_sizes(engine, oracle):
+    """n = 1000 path against alignments up to 1000 steps (long-row scratch, several decision words)."""
+    from evalpath_text import ops_from_gapped
+    rng = np.random.default_rng(9)
+    lens = np.array([0, 1, 16, 17, 32, 33, 200, 1000, 5, 999])
+    off = np.zeros(lens.size + 1, dtype=np.uint32)
+    off[1:] = np.cumsum(lens)
+    st = (rng.integers(0, 5, int(off[-1])) * 2 + rng.integers(0, 2, int(off[-1]))).astype(np.uint32)
+    path = (rng.integers(0, 5, 1000) * 2 + rng.integers(0, 2, 1000)).astype(np.uint32)
+    st2 = st.copy()
+    st2[off[7]:off[7] + 400] = path[300:700]          # a long exact sub-walk
+    engine.set_alignments(off, st2, 5)
+    cols, score = engine.trace_pairs(path, 0, lens.size, np.zeros(lens.size, np.uint8), off)
+    for k in range(lens.size):
+        SA, SB, sc = oracle.pair_alignment(path, st2[off[k]:off[k + 1]])
+        assert cols[k].tolist() == ops_from_gapped(SA, SB), k
+        assert int(score[k]) == sc
+
+
+@pytest.mark.gpu
+def test_filter_alignments(engine):
+    rng = np.random.default_rng(11)
+    lens = rng.choice([0, 1, 2, 3, 5, 9, 300], 5000, p=[.02, .1, .2, .3, .2, .17, .01])
+    off, st = _rand_csr(rng, 5000, 50, lens)
+    engine.set_alignments(off, st, 50)
+    for nodes, mn in ((np.arange(0, 50, 2), 0), (np.arange(50), 3), (np.array([], dtype=np.uint32), 0),
+                      (rng.permutation(50)[:45], 2), (np.arange(50), -1)):
+        keep = engine.filter_alignments(nodes, mn)
+        inset = np.zeros(50, dtype=bool)
+        inset[np.asarray(nodes, dtype=np.int64)] = True
+        want = np.array([bool(inset[st[off[a]:off[a + 1]] >> 1].all()) and (off[a + 1] - off[a]) >= mn
+                         for a in range(5000)])
+        assert np.array_equal(keep, want), (nodes.size, mn)

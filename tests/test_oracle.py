@@ -138,3 +138,28 @@ def test_oracle_threads_agree(oracle):
     one = oracle.evaluate_paths(po, ps, w.offsets, w.steps, True, 1)
     many = oracle.evaluate_paths(po, ps, w.offsets, w.steps, True, 5)
     assert np.array_equal(one, many) and one.sum() > 0
+
+
+def test_golden_evalpath_gapped_strings(oracle, cli_cases):
+    """Pins the oracle's traceback (orc_pair_alignment) to the reference: the full evalPath stdout —
+    every gapped alignment string, score and the totals — of the 18 golden CLI cases."""
+    from gfalign_b200 import textio
+    from evalpath_text import evalpath_stdout, ops_from_gapped
+    seen = 0
+    for c in cli_cases.values():
+        if "_evalpath_" not in c["name"]:
+            continue
+        gfa = next(v for k, v in c["files"].items() if k.endswith(".gfa"))
+        gaf = next(v for k, v in c["files"].items() if k.endswith(".gaf"))
+        names, _, _ = textio.parse_gfa(gfa)
+        qn, off, st = textio.parse_gaf(gaf, names)
+        path = textio.parse_path(c["args"][c["args"].index("-p") + 1], names)
+        _, _, tf, tr = oracle.evaluate_path(path, off, st, False, scores=True)
+
+        def trace(p, B):
+            SA, SB, _ = oracle.pair_alignment(p, B)
+            return ops_from_gapped(SA, SB)
+
+        assert evalpath_stdout(names, path, qn, off, st, tf, tr, trace) == c["stdout"], c["name"]
+        seen += 1
+    assert seen >= 18
