@@ -284,6 +284,7 @@ int gfe_set_alignments(gfe_engine *e, const uint32_t *offsets, const uint32_t *s
     e->n_nodes = n_nodes;
     e->max_m = mx;
     e->have_alignments = true;
+    e->have_rowstart = false;
     e->have_universe = false;
     return build_bucket_geometry(e);
 }
@@ -301,6 +302,7 @@ int gfe_set_alignments_device(gfe_engine *e, const uint32_t *d_offsets, const ui
     e->S = total_steps;
     e->n_nodes = n_nodes;
     e->have_alignments = true;
+    e->have_rowstart = false;
     e->have_universe = false;
     CUDA_TRY(e, cudaSetDevice(e->device));
     return build_bucket_geometry(e);   // also finds the longest alignment
@@ -758,7 +760,8 @@ struct PairKeyHash {
 inline uint64_t pair_key(uint32_t from, uint32_t to) { return ((uint64_t)from << 32) | to; }
 
 // representative slot of every directed pair: the first slot (2i = edge i, 2i+1 = its reverse
-// complement) that carries the pair.
+// complement) that carries the pair.  Host side of the sharded flow only
+// (gfe_edge_weights_from_counts); the single-GPU path keeps everything on the device.
 void build_rep(const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
                std::unordered_map<uint64_t, uint32_t, PairKeyHash> &rep) {
     rep.reserve((size_t)E * 2 + 1);
@@ -766,6 +769,59 @@ void build_rep(const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
         rep.emplace(pair_key(edge_from[i], edge_to[i]), 2 * i);
         rep.emplace(pair_key(edge_to[i] ^ 1u, edge_from[i] ^ 1u), 2 * i + 1);
     }
+}
+
+// bitmap over the step array, bit s = step s starts an alignment; built lazily once per table
+int ensure_rowstart(gfe_engine *e, cudaStream_t st) {
+    if (e->have_rowstart) return GFE_OK;
+    const size_t words = (size_t)(e->S >> 5) + 2;
+    TRY(ensure_dev(e, e->d_rowstart, words));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_rowstart.ptr, 0, words * 4, st));
+    launch_rowstart(e->d_off, e->A, e->d_rowstart.ptr, st);
+    e->kernel_launches += e->A ? 1 : 0;
+    CUDA_TRY(e, cudaGetLastError());
+    e->have_rowstart = true;
+    return GFE_OK;
+}
+
+// uploads the link records, builds the device pair table and streams the alignments through it
+int edge_count_on_device(gfe_engine *e, const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
+                         cudaStream_t st) {
+    if (E >= 0x7FFFFFFFu / 3) {
+        set_error(e, "gfe_edge_support: %u link records exceed the table limit", E);
+        return GFE_ERR_LIMIT;
+    }
+    const uint32_t space = 2 * e->n_nodes;
+    for (uint32_t i = 0; i < E; ++i)
+        if (edge_from[i] >= space || edge_to[i] >= space) {
+            set_error(e, "edge %u names a node >= n_nodes %u", i, e->n_nodes);
+            return GFE_ERR_ARG;
+        }
+    e->edge_cap = edge_table_capacity(E);
+    TRY(ensure_dev(e, e->d_edge_ft, std::max<size_t>((size_t)E * 2, 1)));
+    TRY(ensure_dev(e, e->d_edge_table, e->edge_cap));
+    if (E) {
+        CUDA_TRY(e, cudaMemcpyAsync(e->d_edge_ft.ptr, edge_from, (size_t)E * 4, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(e, cudaMemcpyAsync(e->d_edge_ft.ptr + E, edge_to, (size_t)E * 4, cudaMemcpyHostToDevice, st));
+    }
+    launch_edge_build(e->d_edge_ft.ptr, e->d_edge_ft.ptr + E, E, e->d_edge_table.ptr, e->edge_cap, st);
+    EdgeStreamArgs a;
+    TRY(ensure_rowstart(e, st));
+    a.steps = e->d_steps;
+    a.rowstart = e->d_rowstart.ptr;
+    a.S = e->S;
+    a.table = e->d_edge_table.ptr;
+    a.cap = e->edge_cap;
+    if (e->timing) {
+        TRY(next_event_pair(e));
+        CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    }
+    if (E) launch_edge_stream(a, e->sm_count, st);
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
+    e->kernel_launches += (E ? 1 : 0) + ((E && e->A) ? 1 : 0) + 1;
+    e->h2d_bytes += (uint64_t)E * 8;
+    CUDA_TRY(e, cudaGetLastError());
+    return GFE_OK;
 }
 }  // namespace
 
@@ -776,57 +832,15 @@ int gfe_edge_traversals_device(gfe_engine *e, const uint32_t *edge_from, const u
         set_error(e, "gfe_edge_support: call gfe_set_alignments first");
         return GFE_ERR_STATE;
     }
-    if (E >= 0x7FFFFFFFu) return GFE_ERR_LIMIT;
     CUDA_TRY(e, cudaSetDevice(e->device));
     cudaStream_t st = (cudaStream_t)cuda_stream;   // NULL = the CUDA default stream
-    const uint32_t space = 2 * e->n_nodes;
-    for (uint32_t i = 0; i < E; ++i)
-        if (edge_from[i] >= space || edge_to[i] >= space) {
-            set_error(e, "edge %u names a node >= n_nodes %u", i, e->n_nodes);
-            return GFE_ERR_ARG;
-        }
-    // adjacency rows by oriented from-step, entries (to, representative slot), deduplicated
-    std::unordered_map<uint64_t, uint32_t, PairKeyHash> rep;
-    build_rep(edge_from, edge_to, E, rep);
-    std::vector<uint32_t> row_off((size_t)space + 1, 0);
-    for (auto &kv : rep) row_off[(kv.first >> 32) + 1]++;
-    for (uint32_t i = 0; i < space; ++i) row_off[i + 1] += row_off[i];
-    std::vector<uint2> ent(rep.size());
-    {
-        std::vector<uint32_t> fill(row_off.begin(), row_off.end() - 1);
-        for (auto &kv : rep) {
-            const uint32_t from = (uint32_t)(kv.first >> 32);
-            ent[fill[from]++] = make_uint2((uint32_t)kv.first, kv.second);
-        }
-    }
-    TRY(ensure_dev(e, e->d_row_off, row_off.size()));
-    TRY(ensure_dev(e, e->d_row_ent, std::max<size_t>(ent.size(), 1)));
-    CUDA_TRY(e, cudaMemcpyAsync(e->d_row_off.ptr, row_off.data(), row_off.size() * 4,
-                                cudaMemcpyHostToDevice, st));
-    if (!ent.empty())
-        CUDA_TRY(e, cudaMemcpyAsync(e->d_row_ent.ptr, ent.data(), ent.size() * sizeof(uint2),
-                                    cudaMemcpyHostToDevice, st));
+    TRY(edge_count_on_device(e, edge_from, edge_to, E, st));
     CUDA_TRY(e, cudaMemsetAsync(d_counts, 0, (size_t)E * 2 * sizeof(uint32_t), st));
-    EdgeArgs a;
-    a.off = e->d_off;
-    a.steps = e->d_steps;
-    a.A = e->A;
-    a.row_off = e->d_row_off.ptr;
-    a.row_ent = e->d_row_ent.ptr;
-    a.n_steps_space = space;
-    a.counts = d_counts;
-    a.n_slots = 2 * E;
-    if (e->timing) {
-        TRY(next_event_pair(e));
-        CUDA_TRY(e, cudaEventRecord(e->ev0, st));
-    }
-    if (E) launch_edge_support(a, e->sm_count, st);
-    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
-    e->kernel_launches += (E && e->A) ? 1 : 0;
+    launch_edge_scatter(e->d_edge_table.ptr, e->edge_cap, d_counts, st);
+    e->kernel_launches += 1;
     CUDA_TRY(e, cudaGetLastError());
-    // the host vectors above must outlive the async copies
+    // the caller's host arrays may go away after the call
     CUDA_TRY(e, cudaStreamSynchronize(st));
-    e->h2d_bytes += row_off.size() * 4 + ent.size() * sizeof(uint2);
     return GFE_OK;
 }
 
@@ -849,18 +863,26 @@ int gfe_edge_weights_from_counts(const uint32_t *edge_from, const uint32_t *edge
 
 int gfe_edge_support(gfe_engine *e, const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
                      uint32_t *weights) {
-    if (!e || (E && !weights)) return GFE_ERR_ARG;
-    TRY(ensure_dev(e, e->d_edge_counts, std::max<size_t>((size_t)E * 2, 1)));
-    TRY(gfe_edge_traversals_device(e, edge_from, edge_to, E, e->d_edge_counts.ptr, (void *)e->stream));
-    std::vector<uint32_t> counts((size_t)E * 2);
-    if (E) {
-        CUDA_TRY(e, cudaMemcpyAsync(counts.data(), e->d_edge_counts.ptr, counts.size() * 4,
-                                    cudaMemcpyDeviceToHost, e->stream));
-        CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    if (!e || (E && (!weights || !edge_from || !edge_to))) return GFE_ERR_ARG;
+    if (!e->have_alignments) {
+        set_error(e, "gfe_edge_support: call gfe_set_alignments first");
+        return GFE_ERR_STATE;
     }
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    cudaStream_t st = e->stream;
+    TRY(edge_count_on_device(e, edge_from, edge_to, E, st));
+    if (E) {
+        TRY(ensure_dev(e, e->d_edge_counts, E));
+        launch_edge_weights(e->d_edge_ft.ptr, e->d_edge_ft.ptr + E, E, e->d_edge_table.ptr, e->edge_cap,
+                            e->d_edge_counts.ptr, st);
+        e->kernel_launches += 1;
+        CUDA_TRY(e, cudaGetLastError());
+        CUDA_TRY(e, cudaMemcpyAsync(weights, e->d_edge_counts.ptr, (size_t)E * 4, cudaMemcpyDeviceToHost, st));
+    }
+    CUDA_TRY(e, cudaStreamSynchronize(st));
     if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
-    e->d2h_bytes += counts.size() * 4;
-    return gfe_edge_weights_from_counts(edge_from, edge_to, E, counts.data(), weights);
+    e->d2h_bytes += (uint64_t)E * 4;
+    return GFE_OK;
 }
 
 // ---- evalPath detail: traceback columns ----------------------------------------------------------
@@ -1018,13 +1040,16 @@ int gfe_filter_alignments(gfe_engine *e, const uint32_t *nodes, uint32_t n, int3
     a.n_nodes = e->n_nodes;
     a.min_nodes = min_nodes;
     a.keep = e->d_tr_rc.ptr;
+    a.S = e->S;
+    TRY(ensure_dev(e, e->d_tr_dirs, (size_t)((e->S + 31) / 32) + 1));
+    a.bad_bits = e->d_tr_dirs.ptr;
     if (e->timing) {
         TRY(next_event_pair(e));
         CUDA_TRY(e, cudaEventRecord(e->ev0, st));
     }
-    launch_filter_rows(a, st);
+    launch_filter_rows(a, e->sm_count, st);
     if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
-    e->kernel_launches += 1;
+    e->kernel_launches += 2;
     CUDA_TRY(e, cudaGetLastError());
     CUDA_TRY(e, cudaMemcpyAsync(keep, e->d_tr_rc.ptr, e->A, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(e, cudaStreamSynchronize(st));

@@ -82,8 +82,11 @@ struct gfe_engine {
     DevBuf<uint8_t> d_tr_ops, d_tr_rc;
 
     // edge support
-    DevBuf<uint32_t> d_row_off, d_edge_counts;
-    DevBuf<uint2> d_row_ent;
+    DevBuf<uint32_t> d_edge_ft, d_edge_counts;     // link records (from | to), per-record weights
+    DevBuf<gfe::EdgeSlot> d_edge_table;
+    uint32_t edge_cap = 0;
+    DevBuf<uint32_t> d_rowstart;                   // bit s: step s starts an alignment
+    bool have_rowstart = false;
 
     // counters
     uint64_t kernel_launches = 0, exact_pairs = 0, slow_pairs = 0, h2d_bytes = 0, d2h_bytes = 0;
@@ -95,7 +98,7 @@ struct gfe_engine {
         fd(d_ldesc.ptr); fd(d_perm.ptr); fd(d_hist.ptr); fd(d_cursors.ptr);
         fd(d_stage.ptr); fd(d_ptab.ptr); fd(d_plocal.ptr); fd(d_pnext.ptr); fd(d_counts.ptr); fd(d_err.ptr);
         fd(d_work.ptr); fd(d_work_count.ptr); fd(d_pair_work.ptr); fd(d_tfw.ptr); fd(d_trc.ptr);
-        fd(d_row_off.ptr); fd(d_edge_counts.ptr); fd(d_row_ent.ptr);
+        fd(d_edge_ft.ptr); fd(d_edge_counts.ptr); fd(d_edge_table.ptr); fd(d_rowstart.ptr);
         fd(d_pair_keys.ptr); fd(d_pair_ids.ptr); fd(d_pair_ctr.ptr); fd(d_masks.ptr);
         fd(d_unit_ctr.ptr); fd(d_slow.ptr);
         fd(d_tr_path.ptr); fd(d_tr_misc.ptr); fd(d_tr_dirs.ptr); fd(d_tr_len.ptr); fd(d_tr_longb.ptr);

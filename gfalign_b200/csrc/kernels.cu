@@ -917,50 +917,7 @@ pair_exact_long_kernel(const PairArgs a) {
     }
 }
 
-// ------------------------------------------------------------------------------------------------
-// K3: edge_support — scatter-add of every consecutive oriented step pair of every alignment into
-// the counter of the matching adjacency entry (reference src/alignments.cpp:371-396).  Adjacency
-// rows are keyed by the oriented from-step.  When the counter array fits (kSmem) it is privatised
-// in shared memory per CTA and flushed once with global atomics.
-// ------------------------------------------------------------------------------------------------
-template <bool kSmem>
-__global__ void __launch_bounds__(kBlock)
-edge_support_kernel(const EdgeArgs a) {
-    extern __shared__ uint32_t s_counts[];
-    if (kSmem) {
-        for (uint32_t i = threadIdx.x; i < a.n_slots; i += blockDim.x) s_counts[i] = 0;
-        __syncthreads();
-    }
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t ai = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; ai < a.A; ai += stride) {
-        const uint32_t o0 = __ldg(a.off + ai), o1 = __ldg(a.off + ai + 1);
-        if (o1 - o0 < 2) continue;
-        uint32_t x = __ldg(a.steps + o0);
-        for (uint32_t k = o0 + 1; k < o1; ++k) {
-            const uint32_t y = __ldg(a.steps + k);
-            if (x < a.n_steps_space) {
-                const uint32_t r0 = __ldg(a.row_off + x), r1 = __ldg(a.row_off + x + 1);
-                for (uint32_t r = r0; r < r1; ++r) {
-                    const uint2 ent = __ldg(a.row_ent + r);
-                    if (ent.x == y) {
-                        if (kSmem) atomicAdd(&s_counts[ent.y], 1u);
-                        else atomicAdd(&a.counts[ent.y], 1u);
-                        break;
-                    }
-                }
-            }
-            x = y;
-        }
-    }
-    if (kSmem) {
-        __syncthreads();
-        for (uint32_t i = threadIdx.x; i < a.n_slots; i += blockDim.x)
-            if (s_counts[i]) atomicAdd(&a.counts[i], s_counts[i]);
-    }
-}
-
 constexpr size_t kMaxDynSmem = 200 * 1024;
-constexpr uint32_t kEdgeSmemSlots = 40 * 1024;   // 160 KB of privatised counters
 
 size_t score_smem_bytes(const ScoreArgs &a) {
     return (size_t)a.chunk * a.tab_stride * 2 + (size_t)a.chunk * 3 * sizeof(uint32_t);
@@ -982,10 +939,7 @@ int configure_kernels() {
     e = cudaFuncSetAttribute(pair_classify_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)kMaxDynSmem);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(edge_support_kernel<true>,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
-    if (e != cudaSuccess) return (int)e;
-    return 0;
+    return configure_edge_kernels();
 }
 
 void launch_length_histogram(const uint32_t *off, uint64_t A, uint32_t *hist, cudaStream_t st) {
@@ -1085,18 +1039,5 @@ void launch_pair_exact_long(const PairArgs &a, uint32_t max_m, cudaStream_t st) 
     pair_exact_long_kernel<<<148 * 8, 32, (size_t)(max_m + 1) * 8 * sizeof(int), st>>>(a);
 }
 
-void launch_edge_support(const EdgeArgs &a, int sm_count, cudaStream_t st) {
-    if (a.A == 0) return;
-    uint64_t blocks = (a.A + kBlock - 1) / kBlock;
-    if (a.n_slots <= kEdgeSmemSlots) {
-        const uint64_t cap = (uint64_t)sm_count * 2;
-        if (blocks > cap) blocks = cap;
-        edge_support_kernel<true><<<(unsigned)blocks, kBlock, (size_t)a.n_slots * 4, st>>>(a);
-    } else {
-        const uint64_t cap = (uint64_t)sm_count * 8;
-        if (blocks > cap) blocks = cap;
-        edge_support_kernel<false><<<(unsigned)blocks, kBlock, 0, st>>>(a);
-    }
-}
 
 }  // namespace gfe

@@ -135,15 +135,18 @@ struct PairArgs {             // evalPath: one path against every alignment
     uint32_t work_cap;
 };
 
-struct EdgeArgs {
-    const uint32_t *off;
+struct __align__(16) EdgeSlot {   // evalGFA: one directed link pair of the graph (edges.cu)
+    unsigned long long key;       // from_step << 32 | to_step; ~0 = empty
+    uint32_t count;               // traversal events equal to this pair
+    uint32_t rep;                 // lowest slot (2i = record i, 2i+1 = its reverse complement) carrying it
+};
+
+struct EdgeStreamArgs {
     const uint32_t *steps;
-    uint64_t A;
-    const uint32_t *row_off;  // 2*n_nodes+1, adjacency rows by oriented from-step
-    const uint2 *row_ent;     // (to step, counter slot)
-    uint32_t n_steps_space;   // 2*n_nodes
-    uint32_t *counts;         // n_slots
-    uint32_t n_slots;
+    const uint32_t *rowstart;     // bitmap over steps: bit s = step s starts an alignment
+    uint64_t S;                   // total steps
+    EdgeSlot *table;
+    uint32_t cap;
 };
 
 struct TraceArgs {            // evalPath detail: traceback columns of one path vs a batch of alignments
@@ -174,6 +177,8 @@ struct FilterArgs {           // filter mode: rows whose nodes all lie in a set,
     uint32_t n_nodes;
     int32_t min_nodes;
     uint8_t *keep;
+    uint64_t S;                  // total steps
+    uint32_t *bad_bits;          // scratch, (S + 31) / 32 words: step names a node outside the set
 };
 
 // hist: kNumBuckets counters, [kNumBuckets] = max length, [kNumBuckets+1] = steps of long rows
@@ -206,13 +211,21 @@ void launch_exact_worklist_long(const ScoreArgs &a, uint32_t max_m, cudaStream_t
 void launch_pair_classify(const PairArgs &a, int sm_count, cudaStream_t st);
 void launch_pair_exact(const PairArgs &a, cudaStream_t st);
 void launch_pair_exact_long(const PairArgs &a, uint32_t max_m, cudaStream_t st);
-void launch_edge_support(const EdgeArgs &a, int sm_count, cudaStream_t st);
+uint32_t edge_table_capacity(uint32_t E);
+void launch_rowstart(const uint32_t *off, uint64_t A, uint32_t *rowstart, cudaStream_t st);
+void launch_edge_build(const uint32_t *d_ef, const uint32_t *d_et, uint32_t E, EdgeSlot *table,
+                       uint32_t cap, cudaStream_t st);
+void launch_edge_stream(const EdgeStreamArgs &a, int sm_count, cudaStream_t st);
+void launch_edge_scatter(const EdgeSlot *table, uint32_t cap, uint32_t *counts, cudaStream_t st);
+void launch_edge_weights(const uint32_t *d_ef, const uint32_t *d_et, uint32_t E, const EdgeSlot *table,
+                         uint32_t cap, uint32_t *weights, cudaStream_t st);
+int configure_edge_kernels();
 void launch_max_len(const uint32_t *off, uint64_t first, uint32_t count, uint32_t *out,
                     cudaStream_t st);
 void launch_trace_bases(const uint32_t *off, uint64_t first, uint32_t count, uint32_t n,
                         uint64_t *base, cudaStream_t st);
 void launch_pair_trace(const TraceArgs &a, cudaStream_t st);
-void launch_filter_rows(const FilterArgs &a, cudaStream_t st);
+void launch_filter_rows(const FilterArgs &a, int sm_count, cudaStream_t st);
 int configure_kernels();   // cudaFuncSetAttribute for the large-shared-memory kernels
 
 }  // namespace gfe

@@ -8,10 +8,10 @@
 //   decision words: dirs[((i-1) * count + k) * W + w], 16 cells per u32 — consecutive threads write
 //   consecutive words, so the n*W stores per pair are coalesced.
 //
-// filter_rows_kernel: filter mode (InAlignment::isContained + pathNodesCount,
-// src/alignments.cpp:96-135, 459-472): keep[a] = every step's node is in the set && m >= min.
-// A CTA owns 256 rows; their steps are one contiguous CSR range, streamed with coalesced loads;
-// a step outside the set finds its row by binary search in the CTA's offsets (shared memory).
+// filter mode (InAlignment::isContained + pathNodesCount, src/alignments.cpp:96-135, 459-472):
+// keep[a] = every step's node is in the set && m >= min.  Two flat, fully coalesced passes:
+// filter_mark_kernel streams the step array once and writes one "outside the set" bit per step
+// (S/8 bytes); filter_rows_kernel reads the offsets and tests each row's bit range.
 #include "kernels.cuh"
 
 namespace gfe {
@@ -132,34 +132,41 @@ __global__ void trace_bases_kernel(const uint32_t *off, uint64_t first, uint32_t
     if (k < count) base[k] = (uint64_t)(off[first + k] - off[first]) + (uint64_t)k * n;
 }
 
-constexpr int kFilterRows = 256;
+// pass 1, flat over the step array: one step per thread and iteration, the warp's ballot is the
+// word of the "outside the set" bitmap for its 32 consecutive steps
+__global__ void __launch_bounds__(256) filter_mark_kernel(FilterArgs a) {
+    const uint64_t n_words = (a.S + 31) / 32;
+    const uint64_t warp = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
+    const uint64_t n_warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    const uint32_t lane = threadIdx.x & 31;
+    for (uint64_t w = warp; w < n_words; w += n_warps) {
+        const uint64_t s = w * 32 + lane;
+        bool bad = false;
+        if (s < a.S) {
+            const uint32_t node = __ldg(a.steps + s) >> 1;
+            bad = !(node < a.n_nodes && ((__ldg(a.node_bits + (node >> 5)) >> (node & 31)) & 1u));
+        }
+        const uint32_t word = __ballot_sync(0xFFFFFFFFu, bad);
+        if (lane == 0) a.bad_bits[w] = word;
+    }
+}
 
-__global__ void __launch_bounds__(kFilterRows) filter_rows_kernel(FilterArgs a) {
-    __shared__ uint32_t s_off[kFilterRows + 1];
-    __shared__ uint32_t s_drop[kFilterRows];
-    const uint64_t r0 = (uint64_t)blockIdx.x * kFilterRows;
-    const uint32_t rows = (uint32_t)((a.A - r0) < (uint64_t)kFilterRows ? (a.A - r0) : kFilterRows);
-    for (uint32_t t = threadIdx.x; t <= rows; t += blockDim.x) s_off[t] = a.off[r0 + t];
-    s_drop[threadIdx.x] = 0;
-    __syncthreads();
-    const uint32_t lo = s_off[0], hi = s_off[rows];
-    for (uint32_t s = lo + threadIdx.x; s < hi; s += blockDim.x) {
-        const uint32_t node = a.steps[s] >> 1;
-        const bool in = node < a.n_nodes && ((a.node_bits[node >> 5] >> (node & 31)) & 1u);
-        if (!in) {
-            uint32_t l = 0, h = rows;   // largest r with s_off[r] <= s
-            while (h - l > 1) {
-                const uint32_t mid = (l + h) >> 1;
-                if (s_off[mid] <= s) l = mid; else h = mid;
-            }
-            s_drop[l] = 1;
+// pass 2: one thread per alignment, any marked step in [off[a], off[a+1])?
+__global__ void __launch_bounds__(256) filter_rows_kernel(FilterArgs a) {
+    const uint64_t r = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+    if (r >= a.A) return;
+    const uint32_t o0 = __ldg(a.off + r), o1 = __ldg(a.off + r + 1);
+    bool any = false;
+    if (o1 > o0) {
+        const uint32_t w0 = o0 >> 5, w1 = (o1 - 1) >> 5;
+        for (uint32_t w = w0; w <= w1 && !any; ++w) {
+            uint32_t bits = __ldg(a.bad_bits + w);
+            if (w == w0) bits &= 0xFFFFFFFFu << (o0 & 31);
+            if (w == w1) bits &= 0xFFFFFFFFu >> (31 - ((o1 - 1) & 31));
+            any = bits != 0;
         }
     }
-    __syncthreads();
-    if (threadIdx.x < rows) {
-        const uint32_t m = s_off[threadIdx.x + 1] - s_off[threadIdx.x];
-        a.keep[r0 + threadIdx.x] = (!s_drop[threadIdx.x] && (int64_t)m >= (int64_t)a.min_nodes) ? 1 : 0;
-    }
+    a.keep[r] = (!any && (int64_t)(o1 - o0) >= (int64_t)a.min_nodes) ? 1 : 0;
 }
 
 }  // namespace
@@ -183,9 +190,16 @@ void launch_pair_trace(const TraceArgs &a, cudaStream_t st) {
                         a.n * sizeof(uint32_t), st>>>(a);
 }
 
-void launch_filter_rows(const FilterArgs &a, cudaStream_t st) {
+void launch_filter_rows(const FilterArgs &a, int sm_count, cudaStream_t st) {
     if (!a.A) return;
-    filter_rows_kernel<<<(unsigned)((a.A + kFilterRows - 1) / kFilterRows), kFilterRows, 0, st>>>(a);
+    const uint64_t n_words = (a.S + 31) / 32;
+    if (n_words) {
+        uint64_t blocks = (n_words + 7) / 8;           // 8 warps per CTA
+        const uint64_t cap = (uint64_t)sm_count * 32;
+        if (blocks > cap) blocks = cap;
+        filter_mark_kernel<<<(unsigned)blocks, 256, 0, st>>>(a);
+    }
+    filter_rows_kernel<<<(unsigned)((a.A + 255) / 256), 256, 0, st>>>(a);
 }
 
 }  // namespace gfe

@@ -128,10 +128,12 @@ int gfe_filter_alignments(gfe_engine *e, const uint32_t *nodes, uint32_t n, int3
 int gfe_edge_support(gfe_engine *e, const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
                      uint32_t *weights);
 
-/* Device-side half of the above for sharded alignments: raw traversal counters per DIRECTED
- * adjacency entry, to be summed across shards (all-reduce) before gfe_edge_weights_from_counts.
- * d_counts has 2*E uint32 slots (slot 2i = events equal to edge i, 2i+1 = events equal to its
- * reverse complement). */
+/* Device-side half of the above for sharded alignments: raw traversal counters, to be summed across
+ * shards (all-reduce) before gfe_edge_weights_from_counts.  d_counts has 2*E uint32 slots (slot 2i =
+ * record i as written, 2i+1 = its reverse complement).  A pair and its reverse complement are
+ * counted together: their events are reported at the lowest slot carrying the canonical
+ * orientation and the other slots stay 0, so only sums over both orientations of a record are
+ * defined — which is all gfe_edge_weights_from_counts uses. */
 int gfe_edge_traversals_device(gfe_engine *e, const uint32_t *edge_from, const uint32_t *edge_to,
                                uint32_t E, uint32_t *d_counts, void *cuda_stream);
 int gfe_edge_weights_from_counts(const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,

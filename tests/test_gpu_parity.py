@@ -95,6 +95,19 @@ def test_edge_support_hairpins_random(engine, oracle):
     got = engine.edge_support(ef, et)
     want = oracle.edge_support(off, steps, 4, ef, et)
     assert np.array_equal(got, want)
+    # the sharded flow: raw device counters of two alignment shards, summed, then the host rule
+    import torch
+    from gfalign_b200 import sharded
+    total = torch.zeros(2 * ef.size, dtype=torch.int64)
+    for lo, hi in ((0, 2000), (2000, 5000)):
+        so, ss = sharded.take_shard(off, steps, lo, hi)
+        engine.set_alignments(so, ss, 4)
+        d = torch.zeros(2 * ef.size, dtype=torch.int32, device="cuda")
+        engine.edge_traversals_device(ef, et, d.data_ptr())
+        torch.cuda.synchronize()
+        total += d.cpu().to(torch.int64)
+    w = engine.edge_weights_from_counts(ef, et, total.numpy().astype(np.uint32))
+    assert np.array_equal(w, want)
 
 
 # ---- against the golden fixtures generated from the compiled reference --------------------------
