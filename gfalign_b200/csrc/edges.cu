@@ -11,8 +11,7 @@
 //                          a pair and its reverse complement are one entry, since only their sum
 //                          is ever used; 16-byte entries {key, count, representative slot}: the
 //                          probe and the atomic of one event touch the same 32-byte sector;
-//                          cap = 1.5 E keeps the table of a 700 k-link graph at 17 MB (L2-resident
-//                          on either die; a 56 MB table of directed keys was not)
+//                          cap = 3 E (34 MB for a 700 k-link graph, L2-resident)
 //   counts u32[2E]         slot 2i = record i as written, 2i+1 = its reverse complement; the events
 //                          of both orientations are reported at the lowest slot that carries the
 //                          canonical orientation, every other slot stays 0
@@ -190,7 +189,7 @@ __global__ void edge_weights_kernel(const uint32_t *ef, const uint32_t *et, uint
 }  // namespace
 
 uint32_t edge_table_capacity(uint32_t E) {
-    uint64_t cap = (uint64_t)E * 3 / 2 + 64;    // <= E canonical keys, load <= 2/3
+    uint64_t cap = (uint64_t)E * 3 + 64;        // <= E canonical keys, load <= 1/3: short probe runs
     if (cap > 0xFFFFFFF0ull) cap = 0xFFFFFFF0ull;
     return (uint32_t)cap;
 }
