@@ -98,12 +98,12 @@ def time_reference_cli(binary: str, gfa: str, gaf: str, nl: str, t, m_steps: int
     base = [binary, "search", "-j", "1", "-f", gfa, "-g", gaf, "-n", nl, "-s", t.names[t.source],
             "-d", t.names[t.destination]]
     t0 = time.perf_counter()
-    subprocess.run(base + ["-m", "0"], capture_output=True, check=True)
+    subprocess.run(base + ["-m", "0"], capture_output=True, check=True, timeout=600)
     load = time.perf_counter() - t0
     t0 = time.perf_counter()
-    subprocess.run(base + ["-m", str(m_steps)], capture_output=True, check=True)
+    subprocess.run(base + ["-m", str(m_steps)], capture_output=True, check=True, timeout=600)
     full = time.perf_counter() - t0
-    v = subprocess.run(base + ["-m", str(m_steps), "--verbose"], capture_output=True, text=True)
+    v = subprocess.run(base + ["-m", str(m_steps), "--verbose"], capture_output=True, text=True, timeout=600)
     calls = v.stderr.count("We can visit this node")
     return max(full - load, 1e-9), calls, load
 
@@ -321,8 +321,8 @@ def main():
     achieved = alg_bytes / (k1_ms * 1e-3) / 1e9
     legacy = os.environ.get("GFE_FORCE_LEGACY") == "1"
     # dram__bytes_read+write of ONE launch from the committed ncu --set full capture of this command
-    # (profiles/r01_score_bitset_ncu_full_summary.csv; cfg3, P = 1024): 19.3 MB
-    traffic = 19.3e6 if (args.workload == "cfg3" and P == 1024 and A == 1_000_000 and not legacy) else None
+    # (profiles/r01_score_bitset_ncu_full_summary.csv; cfg3, P = 1024): 20.45 MB read + 5 KB written
+    traffic = 20.45e6 if (args.workload == "cfg3" and P == 1024 and A == 1_000_000 and not legacy) else None
     # the limiter of the bitset kernel is the SM (issue slots + shared-memory reads), not HBM:
     # warp instructions per launch from the same capture (1.1-1.5e8) vs 4 issue slots/clk/SM
     sm_clock = 1.965e9

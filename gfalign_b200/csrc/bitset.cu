@@ -193,18 +193,20 @@ __device__ __noinline__ void push_slow8(uint2 *__restrict__ slow, uint32_t *work
 //    B's last step, the pair (b_j, b_j+1) taken by the path; mirrored for rc(B).
 // What is still open after this goes to the (path, row) list of kernels.cu.
 template <int W>
-__device__ __noinline__ uint4 refine_row(const uint4 *__restrict__ nt, const uint32_t *__restrict__ tab,
+__device__ __noinline__ uint4 refine_row(const uint2 *__restrict__ nt, const uint32_t *__restrict__ tab,
                                          const uint16_t *__restrict__ rp, int m, uint32_t pair_base,
-                                         uint32_t bt_base, uint32_t lm, int filter) {
+                                         uint32_t bt_base, uint32_t lm, int filter, uint32_t lm_base) {
+    const uint2 *nf = nt + (size_t)(lm_base / 4) * W;   // second node plane: half of the node block
     const uint32_t *mt = tab + (size_t)pair_base * W;
     const uint32_t *bt = tab + (size_t)bt_base * W;
     uint32_t pass = 0xFFFFFFFFu, fw = 0xFFFFFFFFu, rc = 0xFFFFFFFFu, bfw = 0, brc = 0, over = 0;
     uint32_t prev_pid = 0, prev_mr = 0;
     for (int j = 0; j < m; ++j) {
         const uint32_t v = __ldg(rp + j);
-        const uint4 e = nt[(v >> 1) * W];
-        const uint32_t ff = (v & 1u) ? e.w : e.z;   // path[0] == b_j
-        const uint32_t fr = (v & 1u) ? e.z : e.w;   // path[0] == rc of b_j
+        const uint2 e = nt[(v >> 1) * W];           // {N, F+|F-}
+        const uint2 f = nf[(v >> 1) * W];           // {F+, F-}
+        const uint32_t ff = (v & 1u) ? f.y : f.x;   // path[0] == b_j
+        const uint32_t fr = (v & 1u) ? f.x : f.y;   // path[0] == rc of b_j
         pass &= e.x;
         uint32_t mf = 0xFFFFFFFFu, mr = 0xFFFFFFFFu, pid = 0;
         if (j < m - 1) {
@@ -236,25 +238,26 @@ __device__ __noinline__ uint4 refine_row(const uint4 *__restrict__ nt, const uin
 }
 
 // One row of length M (its u16 elements packed two per register in q) against this lane's word.
-// nt / tab = shared-memory table at this lane's word (node quads / plain entries).
+// nt / tab = shared-memory table at this lane's word (first node plane / plain entries).
 template <int M, int W>
-__device__ __forceinline__ void eval_row(const uint4 *__restrict__ nt, const uint32_t *__restrict__ mt,
+__device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const uint32_t *__restrict__ mt,
                                          const uint32_t *__restrict__ bt,
                                          const uint32_t (&q)[row_stride(M) / 2], uint32_t lm,
                                          bool filter, uint32_t &good, uint32_t &bad, uint32_t &slow,
                                          uint32_t &over_open) {
     auto elem = [&](int i) -> uint32_t { return (i & 1) ? (q[i >> 1] >> 16) : (q[i >> 1] & 0xFFFFu); };
-    // node block: one LDS.128 per step -> {N, T, F+, F-} of this lane's 32 paths.  A node visited
+    // node block: one LDS.64 per step -> {N, F+|F-} of this lane's 32 paths ({F+, F-} live in a
+    // second plane only refine_row reads: a 16-lane row group then moves 128 B = one wavefront per
+    // step instead of the two of a 16-byte quad).  A node visited
     // twice can only break the pair test when it is an INTERIOR step of B (it then joins two pairs
     // that may sit at different visits); at either end of B it joins one pair, whose other end
     // pins the visit.
-    uint32_t pass = 0xFFFFFFFFu, tacc = 0, over = 0;
+    uint32_t pass = 0xFFFFFFFFu, over = 0;
 #pragma unroll
     for (int j = 0; j < M; ++j) {
-        const uint4 e = nt[(elem(j) >> 1) * W];
+        const uint2 e = nt[(elem(j) >> 1) * W];     // LDS.64: {N, F+|F-}
         pass &= e.x;
-        if (j >= 1 && j <= M - 2) tacc |= e.y;
-        over |= e.z | e.w;
+        over |= e.y;
     }
     const uint32_t in = filter ? pass : 0xFFFFFFFFu;
     if (M == 1) {
@@ -281,7 +284,6 @@ __device__ __forceinline__ void eval_row(const uint4 *__restrict__ nt, const uin
         bfw |= bt[slot * W];
         brc |= bt[(slot ^ 1u) * W];
     }
-    (void)tacc;
     const uint32_t sure = (fw & ~bfw) | (rc & ~brc);
     const uint32_t amb = (fw & bfw) | (rc & brc);
     const uint32_t open = in & ~lm & ~sure;
@@ -297,7 +299,7 @@ __device__ __forceinline__ void eval_row(const uint4 *__restrict__ nt, const uin
 // vote decides whether any of them needs the second look at the start overhang.  The loop is kept
 // rolled and short so that the body stays in the instruction cache.
 template <int M, int W>
-__device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint4 *__restrict__ nt,
+__device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__restrict__ nt,
                                            const uint32_t *__restrict__ tab, uint32_t unit,
                                            uint32_t word_base, Planes &G, Planes &B, int lane) {
     constexpr int R = 32 / W;                       // rows per warp step
@@ -345,7 +347,7 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint4 *__r
                 if (!__any_sync(0xFFFFFFFFu, ov[k] != 0)) continue;
                 const uint32_t r = it + k * R + sub;
                 const uint4 x = refine_row<W>(nt, tab, base + (size_t)(valid[k] ? r : 0u) * RS, M,
-                                              a.mg.pair_base, a.mg.bt_base, lm, a.filter);
+                                              a.mg.pair_base, a.mg.bt_base, lm, a.filter, a.mg.lm_base);
                 gm[k] = valid[k] ? x.x : 0u;
                 bm[k] = valid[k] ? x.y : 0u;
                 sm[k] = valid[k] ? x.z : 0u;
@@ -390,9 +392,9 @@ score_bitset_kernel(const BitsetArgs a) {
     mbar_wait(s_bar, 0);
 
     const uint32_t w = (uint32_t)lane % W;
-    // node block: 4 words per (node, w) -> this lane's quad starts at 4*w; the plain entries
+    // node block: two planes of 2 words per (node, w), {N, F+|F-} then {F+, F-}; the plain entries
     // (LM, pairs) live behind it at (entry * W + w)
-    const uint4 *nt = reinterpret_cast<const uint4 *>(s_tab) + w;
+    const uint2 *nt = reinterpret_cast<const uint2 *>(s_tab) + w;
     const uint32_t *tab = s_tab + w;
     const uint32_t word_base = p_base + 32u * w;
     Planes G, B;

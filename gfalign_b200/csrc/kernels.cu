@@ -280,14 +280,16 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
     uint32_t *tab0 = masks + (size_t)(p / per_chunk) * mg.entries * mg.W;
     uint32_t *tabw = tab0 + (q >> 5);
     const uint32_t bit = 1u << (q & 31u);
-    // node block: for node i and word w four consecutive words {N, T, F+, F-}
+    // node block, two planes of 2 words per (node i, word w): {N, F+|F-} and {F+, F-}
     for (uint32_t i = threadIdx.x; i < L; i += blockDim.x) {
         const uint32_t v = row[i];
         if (v == 0xFFFFFFFFu) continue;
-        uint32_t *e = tab0 + ((size_t)i * mg.W + (q >> 5)) * 4;
+        uint32_t *e = tab0 + ((size_t)i * mg.W + (q >> 5)) * 2;
         atomicOr(e, bit);                                                  // N: on the path
-        if (v >> 31) atomicOr(e + 1, bit);                                 // T: visited twice
-        if (((v & 0x7FFFFFFFu) >> 1) == 0) atomicOr(e + 2 + (s[0] & 1u), bit);   // F+/F-: path[0]
+        if (((v & 0x7FFFFFFFu) >> 1) == 0) {                               // path[0] is this node
+            atomicOr(e + 1, bit);
+            atomicOr(e + (size_t)(mg.lm_base / 2) * mg.W + (s[0] & 1u), bit);   // F+ / F-
+        }
     }
     for (uint32_t m = threadIdx.x; m <= (uint32_t)kMaxBucket; m += blockDim.x)
         if (n < m) atomicOr(tabw + (size_t)(mg.lm_base + m) * mg.W, bit);           // LM: n < m

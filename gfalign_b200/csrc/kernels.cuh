@@ -98,7 +98,7 @@ struct PairDict {
 // mask-table geometry of one batch (entries are W words each)
 struct MaskGeom {
     uint32_t W;               // words per entry = chunk paths / 32 (power of two <= 32)
-    uint32_t L;               // universe size; node v, word w: 4 words {N, T, F, 0} at (v*W + w)*4
+    uint32_t L;               // universe size; node v, word w: {N, F+|F-} at (v*W + w)*2, {F+, F-} at (lm_base/2)*W + (v*W + w)*2
     uint32_t lm_base;         // LM[m] at lm_base + m, m = 0..kMaxBucket
     uint32_t pair_base;       // M[pid] at pair_base + pid, pid <= 2C+1 (2C, 2C+1: always zero)
     uint32_t bt_base;         // BT[h] at bt_base + h, h < 2*kBloom: paths with a broken triple hashing to h
