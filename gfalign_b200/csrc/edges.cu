@@ -37,9 +37,12 @@ constexpr uint64_t kEmptyKey = ~0ull;
 constexpr uint32_t kEdgeSmemCap = 4096;   // table entries that fit the shared-memory variant (64 KB)
 
 __device__ __forceinline__ uint32_t edge_hash(uint64_t key, uint32_t cap) {
+    // the HIGH half of the product depends on every key bit (the low half sees only the to-step);
+    // a second multiply breaks up the runs a chain graph's consecutive ids would leave
     uint64_t h = key * 0x9E3779B97F4A7C15ull;
-    h ^= h >> 29;
-    return (uint32_t)(((h & 0xFFFFFFFFull) * cap) >> 32);
+    h ^= h >> 32;
+    h *= 0xFF51AFD7ED558CCDull;
+    return (uint32_t)(((h >> 32) * cap) >> 32);
 }
 
 // a directed pair and its reverse complement (y^1, x^1) share one table entry: the smaller key
