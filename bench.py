@@ -229,6 +229,12 @@ def main():
     if world > 1:
         import torch.distributed as dist_mod
         dist = dist_mod
+        # stdout carries exactly one JSON line: NCCL's printf banner goes to stderr (fd 1 -> fd 2 for
+        # the C level, Python keeps a private copy of the real stdout)
+        sys.stdout.flush()
+        _real = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+        sys.stdout = _real
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     # workload: every rank builds the same tangle and its own alignment shard (seed + rank)

@@ -1,0 +1,45 @@
+"""Two GPUs, one process each (torchrun, NCCL): `gfalign_b200.multigpu` prints the reference's rows /
+writes the reference's RC:i tags with the alignment table sharded over the ranks."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+from test_gpu_parity import _cases
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.gpu
+
+
+def _torchrun(n, args, cwd, port):
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), "-m", "gfalign_b200.multigpu"] + args
+    return subprocess.run(cmd, cwd=cwd, env=env, capture_output=True, text=True, timeout=600)
+
+
+def test_two_gpu_search_and_evalgfa_match_reference(tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    port = 29610
+    seen = 0
+    for c in _cases():
+        if c["name"] not in ("random3_search", "tangle1_search_all", "tangle2_search", "tangle2_evalgfa",
+                             "hairpin_evalgfa"):
+            continue
+        d = os.path.join(str(tmp_path), c["name"])
+        os.makedirs(d)
+        for fn, txt in c["files"].items():
+            with open(os.path.join(d, fn), "w") as f:
+                f.write(txt)
+        p = _torchrun(2, list(c["args"]), d, port)
+        port += 1
+        assert p.returncode == 0, p.stderr[-2000:]
+        assert p.stdout == c["stdout"], c["name"]
+        if "-o" in c["args"]:
+            out = open(os.path.join(d, c["args"][c["args"].index("-o") + 1])).read()
+            assert out == c["out_text"], c["name"]
+        seen += 1
+    assert seen == 5
