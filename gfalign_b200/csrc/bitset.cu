@@ -195,8 +195,8 @@ __device__ __noinline__ void push_slow8(uint2 *__restrict__ slow, uint32_t *work
 template <int W>
 __device__ __noinline__ uint4 refine_row(const uint2 *__restrict__ nt, const uint32_t *__restrict__ tab,
                                          const uint16_t *__restrict__ rp, int m, uint32_t pair_base,
-                                         uint32_t bt_base, uint32_t lm, int filter, uint32_t lm_base) {
-    const uint2 *nf = nt + (size_t)(lm_base / 4) * W;   // second node plane: half of the node block
+                                         uint32_t bt_base, uint32_t lm, int filter,
+                                         const uint2 *__restrict__ nf) {   // nf: global {F+, F-} plane at this lane's word
     const uint32_t *mt = tab + (size_t)pair_base * W;
     const uint32_t *bt = tab + (size_t)bt_base * W;
     uint32_t pass = 0xFFFFFFFFu, fw = 0xFFFFFFFFu, rc = 0xFFFFFFFFu, bfw = 0, brc = 0, over = 0;
@@ -204,7 +204,7 @@ __device__ __noinline__ uint4 refine_row(const uint2 *__restrict__ nt, const uin
     for (int j = 0; j < m; ++j) {
         const uint32_t v = __ldg(rp + j);
         const uint2 e = nt[(v >> 1) * W];           // {N, F+|F-}
-        const uint2 f = nf[(v >> 1) * W];           // {F+, F-}
+        const uint2 f = __ldg(nf + (v >> 1) * W);   // {F+, F-}
         const uint32_t ff = (v & 1u) ? f.y : f.x;   // path[0] == b_j
         const uint32_t fr = (v & 1u) ? f.x : f.y;   // path[0] == rc of b_j
         pass &= e.x;
@@ -300,6 +300,7 @@ __device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const uin
 // rolled and short so that the body stays in the instruction cache.
 template <int M, int W>
 __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__restrict__ nt,
+                                           const uint2 *__restrict__ nf,
                                            const uint32_t *__restrict__ tab, uint32_t unit,
                                            uint32_t word_base, Planes &G, Planes &B, int lane) {
     constexpr int R = 32 / W;                       // rows per warp step
@@ -347,7 +348,7 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__r
                 if (!__any_sync(0xFFFFFFFFu, ov[k] != 0)) continue;
                 const uint32_t r = it + k * R + sub;
                 const uint4 x = refine_row<W>(nt, tab, base + (size_t)(valid[k] ? r : 0u) * RS, M,
-                                              a.mg.pair_base, a.mg.bt_base, lm, a.filter, a.mg.lm_base);
+                                              a.mg.pair_base, a.mg.bt_base, lm, a.filter, nf);
                 gm[k] = valid[k] ? x.x : 0u;
                 bm[k] = valid[k] ? x.y : 0u;
                 sm[k] = valid[k] ? x.z : 0u;
@@ -392,9 +393,10 @@ score_bitset_kernel(const BitsetArgs a) {
     mbar_wait(s_bar, 0);
 
     const uint32_t w = (uint32_t)lane % W;
-    // node block: two planes of 2 words per (node, w), {N, F+|F-} then {F+, F-}; the plain entries
+    // node block: 2 words per (node, w), {N, F+|F-} ({F+, F-} stays in global memory); the plain entries
     // (LM, pairs) live behind it at (entry * W + w)
     const uint2 *nt = reinterpret_cast<const uint2 *>(s_tab) + w;
+    const uint2 *nf = reinterpret_cast<const uint2 *>(a.fplane) + (size_t)chunk * (a.mg.L + 1) * W + w;
     const uint32_t *tab = s_tab + w;
     const uint32_t word_base = p_base + 32u * w;
     Planes G, B;
@@ -431,7 +433,7 @@ score_bitset_kernel(const BitsetArgs a) {
         prefetch_unit(a, next, lane);
         const int b = unit_bucket(a, unit);
         switch (b) {
-#define GFE_CASE(M_) case M_: score_unit<M_, W>(a, nt, tab, unit, word_base, G, B, lane); break;
+#define GFE_CASE(M_) case M_: score_unit<M_, W>(a, nt, nf, tab, unit, word_base, G, B, lane); break;
             GFE_CASE(1) GFE_CASE(2) GFE_CASE(3) GFE_CASE(4) GFE_CASE(5) GFE_CASE(6) GFE_CASE(7)
             GFE_CASE(8) GFE_CASE(9) GFE_CASE(10) GFE_CASE(11) GFE_CASE(12) GFE_CASE(13)
             GFE_CASE(14) GFE_CASE(15) GFE_CASE(16)

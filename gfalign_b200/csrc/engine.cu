@@ -352,7 +352,7 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) 
     e->n_pairs = 0;
     {
         const int64_t word_budget = (int64_t)(kBitsetSmemBudget / 4) - 64 - 8;
-        int64_t max_pairs = (word_budget - 4 * ((int64_t)e->L + 1) - (kMaxBucket + 1) - 2 - 3 - 2 * (int64_t)kBloom) / 2;
+        int64_t max_pairs = (word_budget - 2 * ((int64_t)e->L + 1) - (kMaxBucket + 1) - 2 - 3 - 2 * (int64_t)kBloom) / 2;
         max_pairs = std::min<int64_t>(max_pairs, 32766);
         if (max_pairs >= 1 && !e->force_legacy) {
             TRY(ensure_dev(e, e->d_pair_keys, kPairHashCap));
@@ -435,7 +435,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         // ---- bitset kernel: 32*W paths per CTA pass, mask table in shared memory ----------------
         MaskGeom mg;
         mg.L = e->L;
-        mg.lm_base = 4 * (e->L + 1);
+        mg.lm_base = 2 * (e->L + 1);   // node plane {N, F+|F-}: 2 words per (node, w); {F+, F-} is outside the table
         mg.pair_base = mg.lm_base + kMaxBucket + 1;
         mg.n_pairs = e->n_pairs;
         mg.bt_base = mg.pair_base + 2 * e->n_pairs + 2;
@@ -445,7 +445,9 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         while (W > 1 && (size_t)mg.entries * W * 4 + 64 * W * 4 + 16 > kBitsetSmemBudget) W >>= 1;
         mg.W = W;
         const uint32_t chunks = (P + 32 * W - 1) / (32 * W);
-        const size_t mask_words = (size_t)chunks * mg.entries * W;
+        const size_t table_words = (size_t)chunks * mg.entries * W;
+        const size_t fplane_words = (size_t)chunks * 2 * (e->L + 1) * W;   // {F+, F-}, second look only
+        const size_t mask_words = table_words + fplane_words;
         {
             const uint64_t want = std::min<uint64_t>(
                 std::max<uint64_t>((uint64_t)P * e->A / 64, 1u << 20), 1ull << 28);
@@ -460,11 +462,12 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         CUDA_TRY(e, cudaMemsetAsync(e->d_masks.ptr, 0, mask_words * 4, st));
         CUDA_TRY(e, cudaMemsetAsync(e->d_unit_ctr.ptr, 0, (size_t)chunks * 4, st));
         launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr,
-                            e->d_masks.ptr, mg, pd, st);
+                            e->d_masks.ptr, e->d_masks.ptr + table_words, mg, pd, st);
         BitsetArgs b;
         b.bk = e->bk;
         b.mg = mg;
         b.masks = e->d_masks.ptr;
+        b.fplane = e->d_masks.ptr + table_words;
         b.P = P;
         b.filter = filter;
         b.counts = d_counts;
@@ -508,7 +511,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     } else {
         MaskGeom mg{};
         launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr,
-                            nullptr, mg, pd, st);
+                            nullptr, nullptr, mg, pd, st);
         if (e->timing) {
             TRY(next_event_pair(e));
             CUDA_TRY(e, cudaEventRecord(e->ev0, st));
@@ -700,7 +703,7 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
         MaskGeom mg{};
         PairDict pd{nullptr, nullptr, nullptr};
         launch_build_tables(d_poff, d_pstep, 1, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr,
-                            nullptr, mg, pd, st);
+                            nullptr, nullptr, mg, pd, st);
     }
     PairArgs a;
     a.bk = e->bk;

@@ -237,8 +237,8 @@ __device__ __forceinline__ RowRef locate_row(const Buckets &bk, uint32_t sorted)
 __global__ void __launch_bounds__(kBlock)
 build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restrict__ pstep,
                     uint32_t L, uint32_t stride, uint16_t *__restrict__ ptab,
-                    uint16_t *__restrict__ pnext, uint32_t *__restrict__ masks, const MaskGeom mg,
-                    const PairDict pd) {
+                    uint16_t *__restrict__ pnext, uint32_t *__restrict__ masks,
+                    uint32_t *__restrict__ fplane, const MaskGeom mg, const PairDict pd) {
     extern __shared__ uint32_t row[];
     const uint32_t p = blockIdx.x;
     const uint32_t o0 = poff[p], n = poff[p + 1] - o0;
@@ -280,7 +280,7 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
     uint32_t *tab0 = masks + (size_t)(p / per_chunk) * mg.entries * mg.W;
     uint32_t *tabw = tab0 + (q >> 5);
     const uint32_t bit = 1u << (q & 31u);
-    // node block, two planes of 2 words per (node i, word w): {N, F+|F-} and {F+, F-}
+    // node block: {N, F+|F-} per (node i, word w) in the table, {F+, F-} in the global fplane
     for (uint32_t i = threadIdx.x; i < L; i += blockDim.x) {
         const uint32_t v = row[i];
         if (v == 0xFFFFFFFFu) continue;
@@ -288,7 +288,8 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
         atomicOr(e, bit);                                                  // N: on the path
         if (((v & 0x7FFFFFFFu) >> 1) == 0) {                               // path[0] is this node
             atomicOr(e + 1, bit);
-            atomicOr(e + (size_t)(mg.lm_base / 2) * mg.W + (s[0] & 1u), bit);   // F+ / F-
+            atomicOr(fplane + ((size_t)(p / per_chunk) * (L + 1) * mg.W + (size_t)i * mg.W + (q >> 5)) * 2 +
+                         (s[0] & 1u), bit);                                // F+ / F-
         }
     }
     for (uint32_t m = threadIdx.x; m <= (uint32_t)kMaxBucket; m += blockDim.x)
@@ -985,10 +986,10 @@ void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, u
 
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
                          uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, uint32_t *masks,
-                         const MaskGeom &mg, const PairDict &pd, cudaStream_t st) {
+                         uint32_t *fplane, const MaskGeom &mg, const PairDict &pd, cudaStream_t st) {
     if (P == 0) return;
     build_tables_kernel<<<P, kBlock, (size_t)(L + 1) * sizeof(uint32_t), st>>>(
-        poff, pstep, L, tab_stride, ptab, pnext, masks, mg, pd);
+        poff, pstep, L, tab_stride, ptab, pnext, masks, fplane, mg, pd);
 }
 
 void launch_score_paths(const ScoreArgs &a, int sm_count, uint32_t tile_lo, uint32_t tile_hi,

@@ -98,7 +98,7 @@ struct PairDict {
 // mask-table geometry of one batch (entries are W words each)
 struct MaskGeom {
     uint32_t W;               // words per entry = chunk paths / 32 (power of two <= 32)
-    uint32_t L;               // universe size; node v, word w: {N, F+|F-} at (v*W + w)*2, {F+, F-} at (lm_base/2)*W + (v*W + w)*2
+    uint32_t L;               // universe size; node v, word w: {N, F+|F-} at (v*W + w)*2, {F+, F-} in BitsetArgs::fplane (global memory)
     uint32_t lm_base;         // LM[m] at lm_base + m, m = 0..kMaxBucket
     uint32_t pair_base;       // M[pid] at pair_base + pid, pid <= 2C+1 (2C, 2C+1: always zero)
     uint32_t bt_base;         // BT[h] at bt_base + h, h < 2*kBloom: paths with a broken triple hashing to h
@@ -110,6 +110,7 @@ struct BitsetArgs {
     Buckets bk;
     MaskGeom mg;
     const uint32_t *masks;    // [chunks][E][W]
+    const uint32_t *fplane;   // [chunks][L+1][W] x {F+, F-}: path[0] is this node in that orientation (second look)
     uint32_t P;
     int filter;
     uint32_t *counts;         // P x {bad, good}
@@ -199,7 +200,7 @@ void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, u
 // masks == nullptr: tables only (legacy kernel); else also ORs path p into the batch's bitsets
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
                          uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, uint32_t *masks,
-                         const MaskGeom &mg, const PairDict &pd, cudaStream_t st);
+                         uint32_t *fplane, const MaskGeom &mg, const PairDict &pd, cudaStream_t st);
 // tiles [tile_lo, tile_hi) of the bucket geometry; add_empty: count the step-less rows as good
 void launch_score_paths(const ScoreArgs &a, int sm_count, uint32_t tile_lo, uint32_t tile_hi,
                         bool add_empty, cudaStream_t st);
