@@ -327,8 +327,8 @@ def main():
     achieved = alg_bytes / (k1_ms * 1e-3) / 1e9
     legacy = os.environ.get("GFE_FORCE_LEGACY") == "1"
     # dram__bytes_read+write of ONE launch from the committed ncu --set full capture of this command
-    # (profiles/r01_score_bitset_ncu_full_summary.csv; cfg3, P = 1024): 20.45 MB read + 5 KB written
-    traffic = 20.45e6 if (args.workload == "cfg3" and P == 1024 and A == 1_000_000 and not legacy) else None
+    # (profiles/r01_score_bitset_ncu_full_summary.csv; cfg3, P = 1024): 20.41 MB read
+    traffic = 20.41e6 if (args.workload == "cfg3" and P == 1024 and A == 1_000_000 and not legacy) else None
     # the limiter of the bitset kernel is the SM (issue slots + shared-memory reads), not HBM:
     # warp instructions per launch from the same capture (1.1-1.5e8) vs 4 issue slots/clk/SM
     sm_clock = 1.965e9
