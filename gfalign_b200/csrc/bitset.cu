@@ -197,7 +197,7 @@ __device__ __noinline__ uint4 refine_row(const uint2 *__restrict__ nt, const uin
                                          const uint16_t *__restrict__ rp, int m, uint32_t pair_base,
                                          uint32_t bt_base, uint32_t lm, int filter,
                                          const uint2 *__restrict__ nf) {   // nf: global {F+, F-} plane at this lane's word
-    const uint32_t *mt = tab + (size_t)pair_base * W;
+    const uint32_t *mt = tab;                       // the rows hold absolute entries (pair_base + id)
     const uint32_t *bt = tab + (size_t)bt_base * W;
     uint32_t pass = 0xFFFFFFFFu, fw = 0xFFFFFFFFu, rc = 0xFFFFFFFFu, bfw = 0, brc = 0, over = 0;
     uint32_t prev_pid = 0, prev_mr = 0;
@@ -221,7 +221,7 @@ __device__ __noinline__ uint4 refine_row(const uint2 *__restrict__ nt, const uin
         if (j == 0) over |= fr;                     // rc, k = 1
         else if (j <= m - 2) over |= fr & prev_mr;  // rc, pair (b_j-1, b_j) reversed
         if (j >= 1 && j <= m - 2) {
-            const uint32_t slot = triple_slot(prev_pid, pid);
+            const uint32_t slot = triple_slot(prev_pid - pair_base, pid - pair_base);
             bfw |= bt[slot * W];
             brc |= bt[(slot ^ 1u) * W];
         }
@@ -240,8 +240,8 @@ __device__ __noinline__ uint4 refine_row(const uint2 *__restrict__ nt, const uin
 // One row of length M (its u16 elements packed two per register in q) against this lane's word.
 // nt / tab = shared-memory table at this lane's word (first node plane / plain entries).
 template <int M, int W>
-__device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const uint32_t *__restrict__ mt,
-                                         const uint32_t *__restrict__ bt,
+__device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const unsigned char *__restrict__ mt,
+                                         const unsigned char *__restrict__ bt, uint32_t lane_off,
                                          const uint32_t (&q)[row_stride(M) / 2], uint32_t lm,
                                          bool filter, uint32_t &good, uint32_t &bad, uint32_t &slow,
                                          uint32_t &over_open) {
@@ -271,9 +271,11 @@ __device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const uin
     uint32_t fw = 0xFFFFFFFFu, rc = 0xFFFFFFFFu;
 #pragma unroll
     for (int j = 0; j < M - 1; ++j) {
-        const uint32_t pid = elem(M + j);
-        fw &= mt[pid * W];
-        rc &= mt[(pid ^ 1u) * W];
+        // byte offset of entry pid at this lane's word: pid * (4W) has its low bits clear, so the
+        // lane offset is OR-ed in and the warp-uniform region base stays out of the address math
+        const uint32_t o = (elem(M + j) * (4u * W)) | lane_off;
+        fw &= *reinterpret_cast<const uint32_t *>(mt + o);
+        rc &= *reinterpret_cast<const uint32_t *>(mt + (o ^ (4u * W)));
     }
     // broken triples of the path among B's triples (one slot byte per interior step)
     uint32_t bfw = 0, brc = 0;
@@ -281,8 +283,9 @@ __device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const uin
     for (int j = 0; j < M - 2; ++j) {
         constexpr int kByte0 = 2 * (2 * M - 1);
         const uint32_t slot = (q[(kByte0 + j) >> 2] >> (8 * ((kByte0 + j) & 3))) & 0xFFu;
-        bfw |= bt[slot * W];
-        brc |= bt[(slot ^ 1u) * W];
+        const uint32_t o = (slot * (4u * W)) | lane_off;
+        bfw |= *reinterpret_cast<const uint32_t *>(bt + o);
+        brc |= *reinterpret_cast<const uint32_t *>(bt + (o ^ (4u * W)));
     }
     const uint32_t sure = (fw & ~bfw) | (rc & ~brc);
     const uint32_t amb = (fw & bfw) | (rc & brc);
@@ -300,7 +303,7 @@ __device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const uin
 // rolled and short so that the body stays in the instruction cache.
 template <int M, int W>
 __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__restrict__ nt,
-                                           const uint2 *__restrict__ nf,
+                                           const uint2 *__restrict__ nf, const uint32_t *__restrict__ s_tab,
                                            const uint32_t *__restrict__ tab, uint32_t unit,
                                            uint32_t word_base, Planes &G, Planes &B, int lane) {
     constexpr int R = 32 / W;                       // rows per warp step
@@ -311,8 +314,11 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__r
     const uint16_t *base = a.bk.bstep + a.bk.step_base[M] + (size_t)row0 * RS;
     const uint32_t sorted0 = a.bk.row_start[M] + row0;
     const uint32_t lm = tab[(a.mg.lm_base + M) * W];
-    const uint32_t *mt = tab + (size_t)a.mg.pair_base * W;
-    const uint32_t *bt = tab + (size_t)a.mg.bt_base * W;
+    // warp-uniform region bases (the lane's word offset is OR-ed into each entry offset)
+    const uint32_t lane_off = 4u * ((uint32_t)lane % W);
+    // the rows hold absolute pair entries and BT sits at entry 0: both offsets are relative to the table
+    const unsigned char *mt = reinterpret_cast<const unsigned char *>(s_tab);
+    const unsigned char *bt = mt;
     const uint32_t sub = (uint32_t)lane / W;
     const bool filter = a.filter != 0;
 #pragma unroll 1
@@ -334,7 +340,7 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__r
         uint32_t gm[UB], bm[UB], sm[UB], sb[UB], ov[UB], any_over = 0, any_slow = 0;
 #pragma unroll
         for (int k = 0; k < UB; ++k) {
-            eval_row<M, W>(nt, mt, bt, q[k], lm, filter, gm[k], bm[k], sm[k], ov[k]);
+            eval_row<M, W>(nt, mt, bt, lane_off, q[k], lm, filter, gm[k], bm[k], sm[k], ov[k]);
             gm[k] = valid[k] ? gm[k] : 0u;
             bm[k] = valid[k] ? bm[k] : 0u;
             sm[k] = valid[k] ? sm[k] : 0u;
@@ -395,7 +401,7 @@ score_bitset_kernel(const BitsetArgs a) {
     const uint32_t w = (uint32_t)lane % W;
     // node block: 2 words per (node, w), {N, F+|F-} ({F+, F-} stays in global memory); the plain entries
     // (LM, pairs) live behind it at (entry * W + w)
-    const uint2 *nt = reinterpret_cast<const uint2 *>(s_tab) + w;
+    const uint2 *nt = reinterpret_cast<const uint2 *>(s_tab + (size_t)geom_node_base() * W) + w;
     const uint2 *nf = reinterpret_cast<const uint2 *>(a.fplane) + (size_t)chunk * (a.mg.L + 1) * W + w;
     const uint32_t *tab = s_tab + w;
     const uint32_t word_base = p_base + 32u * w;
@@ -433,7 +439,7 @@ score_bitset_kernel(const BitsetArgs a) {
         prefetch_unit(a, next, lane);
         const int b = unit_bucket(a, unit);
         switch (b) {
-#define GFE_CASE(M_) case M_: score_unit<M_, W>(a, nt, nf, tab, unit, word_base, G, B, lane); break;
+#define GFE_CASE(M_) case M_: score_unit<M_, W>(a, nt, nf, s_tab, tab, unit, word_base, G, B, lane); break;
             GFE_CASE(1) GFE_CASE(2) GFE_CASE(3) GFE_CASE(4) GFE_CASE(5) GFE_CASE(6) GFE_CASE(7)
             GFE_CASE(8) GFE_CASE(9) GFE_CASE(10) GFE_CASE(11) GFE_CASE(12) GFE_CASE(13)
             GFE_CASE(14) GFE_CASE(15) GFE_CASE(16)

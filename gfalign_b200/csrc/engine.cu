@@ -352,7 +352,7 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) 
     e->n_pairs = 0;
     {
         const int64_t word_budget = (int64_t)(kBitsetSmemBudget / 4) - 64 - 8;
-        int64_t max_pairs = (word_budget - 2 * ((int64_t)e->L + 1) - (kMaxBucket + 1) - 2 - 3 - 2 * (int64_t)kBloom) / 2;
+        int64_t max_pairs = (word_budget - 2 * ((int64_t)e->L + 1) - (kMaxBucket + 2) - 2 - 3 - 2 * (int64_t)kBloom) / 2;
         max_pairs = std::min<int64_t>(max_pairs, 32766);
         if (max_pairs >= 1 && !e->force_legacy) {
             TRY(ensure_dev(e, e->d_pair_keys, kPairHashCap));
@@ -377,7 +377,8 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) 
     }
     launch_bucket_scatter(e->d_off, e->d_steps, e->d_node2local.ptr, e->A, e->bk, e->d_bstep.ptr,
                           e->d_ldesc.ptr, e->d_perm.ptr, e->d_cursors.ptr, pd,
-                          e->have_dict ? e->n_pairs : 0xFFFFFFFFu, e->stream);
+                          e->have_dict ? e->n_pairs : 0xFFFFFFFFu,
+                          e->have_dict ? geom_pair_base(e->L) : 0u, e->stream);
     e->kernel_launches += e->A ? 1 : 0;
     CUDA_TRY(e, cudaGetLastError());
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
@@ -435,11 +436,13 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         // ---- bitset kernel: 32*W paths per CTA pass, mask table in shared memory ----------------
         MaskGeom mg;
         mg.L = e->L;
-        mg.lm_base = 2 * (e->L + 1);   // node plane {N, F+|F-}: 2 words per (node, w); {F+, F-} is outside the table
-        mg.pair_base = mg.lm_base + kMaxBucket + 1;
+        // BT | node plane {N, F+|F-} (2 words per (node, w); {F+, F-} is outside the table) | LM | pairs
+        mg.bt_base = 0;
+        mg.node_base = geom_node_base();
+        mg.lm_base = geom_lm_base(e->L);
+        mg.pair_base = geom_pair_base(e->L);   // == the bias bucket_scatter added to the rows' pair ids
         mg.n_pairs = e->n_pairs;
-        mg.bt_base = mg.pair_base + 2 * e->n_pairs + 2;
-        mg.entries = (mg.bt_base + 2 * kBloom + 3) & ~3u;
+        mg.entries = (mg.pair_base + 2 * e->n_pairs + 2 + 3) & ~3u;
         uint32_t W = 1;
         while (W < 32 && 32 * W < P) W <<= 1;
         while (W > 1 && (size_t)mg.entries * W * 4 + 64 * W * 4 + 16 > kBitsetSmemBudget) W >>= 1;

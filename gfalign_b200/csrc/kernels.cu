@@ -110,7 +110,7 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
                       const uint32_t *__restrict__ map, uint64_t A, const Buckets bk,
                       uint16_t *__restrict__ bstep, uint2 *__restrict__ ldesc,
                       uint32_t *__restrict__ perm, uint32_t *__restrict__ cursors,
-                      const PairDict pd, uint32_t n_pairs) {
+                      const PairDict pd, uint32_t n_pairs, uint32_t pair_bias) {
     __shared__ uint32_t s_cnt[kNumBuckets + 1], s_base[kNumBuckets + 1];
     const uint64_t n_tiles = (A + kBlock - 1) / kBlock;
     for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -154,7 +154,7 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
                         const uint32_t h = pair_find(pd, key);
                         if (h != kPairEmpty) pid = 2u * pd.ids[h] + flip;
                     }
-                    bstep[dst + m + j - 1] = (uint16_t)pid;
+                    bstep[dst + m + j - 1] = (uint16_t)(pid + pair_bias);   // absolute table entry
                     if (j >= 2) slots[j - 2] = (unsigned char)triple_slot(prev_pid, pid);
                     prev_pid = pid;
                 }
@@ -284,7 +284,7 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
     for (uint32_t i = threadIdx.x; i < L; i += blockDim.x) {
         const uint32_t v = row[i];
         if (v == 0xFFFFFFFFu) continue;
-        uint32_t *e = tab0 + ((size_t)i * mg.W + (q >> 5)) * 2;
+        uint32_t *e = tab0 + (size_t)mg.node_base * mg.W + ((size_t)i * mg.W + (q >> 5)) * 2;
         atomicOr(e, bit);                                                  // N: on the path
         if (((v & 0x7FFFFFFFu) >> 1) == 0) {                               // path[0] is this node
             atomicOr(e + 1, bit);
@@ -968,12 +968,12 @@ void launch_pair_assign(const PairDict &pd, cudaStream_t st) {
 void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local,
                            uint64_t A, const Buckets &bk, uint16_t *bstep, uint2 *ldesc,
                            uint32_t *perm, uint32_t *cursors, const PairDict &pd, uint32_t n_pairs,
-                           cudaStream_t st) {
+                           uint32_t pair_bias, cudaStream_t st) {
     if (A == 0) return;
     uint64_t blocks = (A + kBlock - 1) / kBlock;
     if (blocks > 148 * 8) blocks = 148 * 8;
     bucket_scatter_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(off, steps, node2local, A, bk, bstep,
-                                                               ldesc, perm, cursors, pd, n_pairs);
+                                                               ldesc, perm, cursors, pd, n_pairs, pair_bias);
 }
 
 void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, uint32_t n_nodes,

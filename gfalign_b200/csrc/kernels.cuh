@@ -99,6 +99,7 @@ struct PairDict {
 struct MaskGeom {
     uint32_t W;               // words per entry = chunk paths / 32 (power of two <= 32)
     uint32_t L;               // universe size; node v, word w: {N, F+|F-} at (v*W + w)*2, {F+, F-} in BitsetArgs::fplane (global memory)
+    uint32_t node_base;       // node plane starts at entry node_base (= 2*kBloom: BT comes first, at entry 0)
     uint32_t lm_base;         // LM[m] at lm_base + m, m = 0..kMaxBucket
     uint32_t pair_base;       // M[pid] at pair_base + pid, pid <= 2C+1 (2C, 2C+1: always zero)
     uint32_t bt_base;         // BT[h] at bt_base + h, h < 2*kBloom: paths with a broken triple hashing to h
@@ -190,10 +191,17 @@ void launch_pair_collect(const uint32_t *off, const uint32_t *steps, const uint3
                          cudaStream_t st);
 void launch_pair_assign(const PairDict &pd, cudaStream_t st);
 // n_pairs = 0xFFFFFFFF: no dictionary (pair ids are not written)
+// pair_bias is added to every stored pair id, so a row holds ABSOLUTE table entries (MaskGeom::pair_base + id)
 void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local,
                            uint64_t A, const Buckets &bk, uint16_t *bstep, uint2 *ldesc,
                            uint32_t *perm, uint32_t *cursors, const PairDict &pd, uint32_t n_pairs,
-                           cudaStream_t st);
+                           uint32_t pair_bias, cudaStream_t st);
+
+// mask-table geometry as a function of the universe size L (entries of W words): BT first (so its
+// byte offsets need no base), then the node plane, LM, and the pair masks on an even entry
+__host__ __device__ constexpr uint32_t geom_node_base() { return 2u * kBloom; }
+__host__ __device__ constexpr uint32_t geom_lm_base(uint32_t L) { return geom_node_base() + 2u * (L + 1u); }
+__host__ __device__ constexpr uint32_t geom_pair_base(uint32_t L) { return (geom_lm_base(L) + kMaxBucket + 2u) & ~1u; }
 void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, uint32_t n_nodes,
                            uint32_t L, uint16_t *out, uint32_t total, uint32_t *err,
                            cudaStream_t st);
