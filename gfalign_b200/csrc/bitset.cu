@@ -321,21 +321,39 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__r
     const unsigned char *bt = mt;
     const uint32_t sub = (uint32_t)lane / W;
     const bool filter = a.filter != 0;
+    // rows of trip `it0` into registers (independent LDG.64s in flight together)
+    auto load_rows = [&](uint32_t it0, uint32_t (&qq)[UB][RS / 2]) {
+#pragma unroll
+        for (int k = 0; k < UB; ++k) {
+            const uint32_t r = it0 + k * R + sub;
+            const uint2 *src = reinterpret_cast<const uint2 *>(base + (size_t)(r < nrows ? r : 0u) * RS);
+#pragma unroll
+            for (int c = 0; c < RS / 4; ++c) {
+                const uint2 t = __ldg(src + c);
+                qq[k][2 * c] = t.x;
+                qq[k][2 * c + 1] = t.y;
+            }
+        }
+    };
+    // short rows (most of them): the next trip's rows are loaded before this trip is scored, so
+    // the global-load latency hides behind ~4 rows of table work
+    constexpr bool kPrefetch = M <= 5;
+    uint32_t qn[kPrefetch ? UB : 1][RS / 2];
+    if (kPrefetch) load_rows(0, reinterpret_cast<uint32_t (&)[UB][RS / 2]>(qn));
 #pragma unroll 1
     for (uint32_t it = 0; it < nrows; it += UB * R) {
         uint32_t q[UB][RS / 2];
         bool valid[UB];
 #pragma unroll
-        for (int k = 0; k < UB; ++k) {
-            const uint32_t r = it + k * R + sub;
-            valid[k] = r < nrows;
-            const uint2 *src = reinterpret_cast<const uint2 *>(base + (size_t)(valid[k] ? r : 0u) * RS);
+        for (int k = 0; k < UB; ++k) valid[k] = it + k * R + sub < nrows;
+        if (kPrefetch) {
 #pragma unroll
-            for (int c = 0; c < RS / 4; ++c) {
-                const uint2 t = __ldg(src + c);
-                q[k][2 * c] = t.x;
-                q[k][2 * c + 1] = t.y;
-            }
+            for (int k = 0; k < UB; ++k)
+#pragma unroll
+                for (int c = 0; c < RS / 2; ++c) q[k][c] = qn[kPrefetch ? k : 0][c];
+            if (it + UB * R < nrows) load_rows(it + UB * R, reinterpret_cast<uint32_t (&)[UB][RS / 2]>(qn));
+        } else {
+            load_rows(it, q);
         }
         uint32_t gm[UB], bm[UB], sm[UB], sb[UB], ov[UB], any_over = 0, any_slow = 0;
 #pragma unroll
