@@ -243,7 +243,7 @@ template <int M, int W>
 __device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const unsigned char *__restrict__ mt,
                                          const unsigned char *__restrict__ bt, uint32_t lane_off,
                                          const uint32_t (&q)[row_stride(M) / 2], uint32_t lm,
-                                         bool filter, uint32_t &good, uint32_t &bad, uint32_t &slow,
+                                         uint32_t vmask, bool filter, uint32_t &good, uint32_t &bad, uint32_t &slow,
                                          uint32_t &over_open) {
     auto elem = [&](int i) -> uint32_t { return (i & 1) ? (q[i >> 1] >> 16) : (q[i >> 1] & 0xFFFFu); };
     // node block: one LDS.64 per step -> {N, F+|F-} of this lane's 32 paths ({F+, F-} live in a
@@ -259,7 +259,7 @@ __device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const uns
         pass &= e.x;
         over |= e.y;
     }
-    const uint32_t in = filter ? pass : 0xFFFFFFFFu;
+    const uint32_t in = (filter ? pass : 0xFFFFFFFFu) & vmask;   // vmask: 0 for the rows past the unit's end
     if (M == 1) {
         // a single step occurs (forward or reverse-complemented) iff its node is on the path
         good = in & (lm | pass);
@@ -358,11 +358,8 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__r
         uint32_t gm[UB], bm[UB], sm[UB], sb[UB], ov[UB], any_over = 0, any_slow = 0;
 #pragma unroll
         for (int k = 0; k < UB; ++k) {
-            eval_row<M, W>(nt, mt, bt, lane_off, q[k], lm, filter, gm[k], bm[k], sm[k], ov[k]);
-            gm[k] = valid[k] ? gm[k] : 0u;
-            bm[k] = valid[k] ? bm[k] : 0u;
-            sm[k] = valid[k] ? sm[k] : 0u;
-            ov[k] = valid[k] ? ov[k] : 0u;
+            eval_row<M, W>(nt, mt, bt, lane_off, q[k], lm, valid[k] ? 0xFFFFFFFFu : 0u, filter, gm[k], bm[k],
+                           sm[k], ov[k]);
             sb[k] = 0;
             any_over |= ov[k];
         }
