@@ -399,8 +399,10 @@ static uint32_t pick_chunk(const gfe_engine *e, uint32_t P) {
 }
 
 // Enqueue table build + scoring (+ exact fallbacks) for paths already on the device in local ids.
+// d_raw_steps != nullptr: d_pstep is the engine's scratch the prologue fills from the raw steps.
 static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *d_pstep, uint32_t P,
-                         uint32_t total_steps, int filter, uint32_t *d_counts, cudaStream_t st) {
+                         uint32_t total_steps, int filter, uint32_t *d_counts, uint32_t *d_work_count,
+                         const uint32_t *d_raw_steps, cudaStream_t st) {
     TRY(ensure_dev(e, e->d_ptab, (size_t)P * e->tab_stride));
     TRY(ensure_dev(e, e->d_pnext, (size_t)total_steps + 8));
     // exact-DP worklist: sized for 1 ambiguous pair in 128 checks (cfg3 measures ~1 in 2500)
@@ -412,10 +414,20 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
             CUDA_TRY(e, cudaStreamSynchronize(st));
             TRY(ensure_dev(e, e->d_work, e->work_cap));
         }
-        TRY(ensure_dev(e, e->d_work_count, 4));
     }
-    CUDA_TRY(e, cudaMemsetAsync(d_counts, 0, (size_t)P * 2 * sizeof(uint32_t), st));
-    CUDA_TRY(e, cudaMemsetAsync(e->d_work_count.ptr, 0, 4 * sizeof(uint32_t), st));
+    // one prologue launch clears every accumulator of the batch (and localizes raw device paths)
+    PrologueArgs pro{};
+    pro.zero[0] = d_counts;
+    pro.zero_words[0] = P * 2;
+    pro.zero[1] = d_work_count;
+    pro.zero_words[1] = 4;
+    pro.psteps = d_raw_steps;
+    pro.map = e->d_node2local.ptr;
+    pro.n_nodes = e->n_nodes;
+    pro.L = e->L;
+    pro.out = const_cast<uint16_t *>(d_pstep);
+    pro.total = total_steps;
+    pro.err = e->d_err.ptr;
     ScoreArgs a;
     a.bk = e->bk;
     a.poff = d_poff;
@@ -428,7 +440,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     a.filter = filter;
     a.counts = d_counts;
     a.work = e->d_work.ptr;
-    a.work_count = e->d_work_count.ptr;
+    a.work_count = d_work_count;
     a.work_cap = (uint32_t)std::min<size_t>(e->d_work.cap, 0xFFFFFFFFu);
     const PairDict pd{e->d_pair_keys.ptr, e->d_pair_ids.ptr, e->d_pair_ctr.ptr};
     const uint32_t long_lo = e->bk.tile_start[kLongBucket], long_hi = e->bk.tile_start[kNumBuckets];
@@ -462,8 +474,15 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
             TRY(ensure_dev(e, e->d_masks, mask_words));
             TRY(ensure_dev(e, e->d_unit_ctr, chunks));
         }
-        CUDA_TRY(e, cudaMemsetAsync(e->d_masks.ptr, 0, mask_words * 4, st));
-        CUDA_TRY(e, cudaMemsetAsync(e->d_unit_ctr.ptr, 0, (size_t)chunks * 4, st));
+        pro.zero[2] = e->d_masks.ptr;
+        if (mask_words > 0xFFFFFFFFull) {   // beyond the prologue's 32-bit word counts
+            CUDA_TRY(e, cudaMemsetAsync(e->d_masks.ptr, 0, mask_words * 4, st));
+            pro.zero[2] = nullptr;
+        }
+        pro.zero_words[2] = pro.zero[2] ? (uint32_t)mask_words : 0;
+        pro.zero[3] = e->d_unit_ctr.ptr;
+        pro.zero_words[3] = chunks;
+        launch_prologue(pro, e->sm_count, st);
         launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr,
                             e->d_masks.ptr, e->d_masks.ptr + table_words, mg, pd, st);
         BitsetArgs b;
@@ -476,7 +495,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         b.counts = d_counts;
         b.unit_ctr = e->d_unit_ctr.ptr;
         b.slow = e->d_slow.ptr;
-        b.work_count = e->d_work_count.ptr;
+        b.work_count = d_work_count;
         b.slow_cap = (uint32_t)std::min<size_t>(e->d_slow.cap, 0xFFFFFFFFu);
         // scheduling units: eight warp steps of 32/W rows, at least 16 rows (short tail)
         // scheduling units: a multiple of four warp steps (32/W rows each); small enough that every
@@ -502,17 +521,18 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         }
         launch_score_bitset(b, e->sm_count, st);
         if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
-        e->kernel_launches += 2;
+        e->kernel_launches += 3;   // prologue, tables, bitset scoring
         if (long_hi > long_lo) {   // alignments longer than kMaxBucket steps: position-table kernel
             launch_score_paths(a, e->sm_count, long_lo, long_hi, false, st);
             e->kernel_launches += 1;
         }
         if (e->A) {
-            launch_slow_worklist(a, e->d_slow.ptr, e->d_work_count.ptr + 2, b.slow_cap, st);
+            launch_slow_worklist(a, e->d_slow.ptr, d_work_count + 2, b.slow_cap, st);
             e->kernel_launches += 1;
         }
     } else {
         MaskGeom mg{};
+        launch_prologue(pro, e->sm_count, st);
         launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr,
                             nullptr, nullptr, mg, pd, st);
         if (e->timing) {
@@ -521,7 +541,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         }
         launch_score_paths(a, e->sm_count, 0, long_hi, true, st);
         if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
-        e->kernel_launches += 2;
+        e->kernel_launches += 3;
     }
     if (e->A) {
         launch_exact_worklist(a, st);
@@ -565,8 +585,9 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
     const size_t bytes = off_bytes + (size_t)total * 2;
     TRY(ensure_pinned(e, e->h_stage, bytes));
     TRY(ensure_dev(e, e->d_stage, bytes));
-    TRY(ensure_pinned(e, e->h_counts, (size_t)P * 2));
-    TRY(ensure_dev(e, e->d_counts, (size_t)P * 2));
+    // the four work counters ride behind the count records: one device->host copy per batch
+    TRY(ensure_pinned(e, e->h_counts, (size_t)P * 2 + 4));
+    TRY(ensure_dev(e, e->d_counts, (size_t)P * 2 + 4));
     memcpy(e->h_stage.ptr, path_offsets, (size_t)(P + 1) * 4);
     uint16_t *ls = reinterpret_cast<uint16_t *>(e->h_stage.ptr + off_bytes);
     for (uint32_t i = 0; i < total; ++i) {
@@ -582,14 +603,13 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
                                 e->stream));
     const uint32_t *d_poff = reinterpret_cast<const uint32_t *>(e->d_stage.ptr);
     const uint16_t *d_pstep = reinterpret_cast<const uint16_t *>(e->d_stage.ptr + off_bytes);
-    TRY(enqueue_score(e, d_poff, d_pstep, P, total, filter, e->d_counts.ptr, e->stream));
-    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, (size_t)P * 2 * sizeof(uint32_t),
+    TRY(enqueue_score(e, d_poff, d_pstep, P, total, filter, e->d_counts.ptr,
+                      e->d_counts.ptr + (size_t)P * 2, nullptr, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, ((size_t)P * 2 + 4) * sizeof(uint32_t),
                                 cudaMemcpyDeviceToHost, e->stream));
     uint32_t wc[4] = {0, 0, 0, 0};
-    CUDA_TRY(e, cudaMemcpyAsync(e->h_wc, e->d_work_count.ptr, 4 * sizeof(uint32_t),
-                                cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-    for (int i = 0; i < 4; ++i) wc[i] = e->h_wc[i];
+    for (int i = 0; i < 4; ++i) wc[i] = e->h_counts.ptr[(size_t)P * 2 + i];
     if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
     e->h2d_bytes += bytes;
     e->d2h_bytes += (size_t)P * 2 * sizeof(uint32_t) + 16;
@@ -640,10 +660,9 @@ int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
         TRY(ensure_dev(e, e->d_err, 4));
         CUDA_TRY(e, cudaMemsetAsync(e->d_err.ptr, 0, 4 * sizeof(uint32_t), st));
     }
-    launch_localize_paths(d_path_steps, e->d_node2local.ptr, e->n_nodes, e->L, e->d_plocal.ptr,
-                          total_path_steps, e->d_err.ptr, st);
-    e->kernel_launches += 1;
-    return enqueue_score(e, d_path_offsets, e->d_plocal.ptr, P, total_path_steps, filter, d_counts, st);
+    TRY(ensure_dev(e, e->d_work_count, 4));
+    return enqueue_score(e, d_path_offsets, e->d_plocal.ptr, P, total_path_steps, filter, d_counts,
+                         e->d_work_count.ptr, d_path_steps, st);
 }
 
 // ---- evalPath scoring ---------------------------------------------------------------------------

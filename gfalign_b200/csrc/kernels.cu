@@ -168,17 +168,29 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
     }
 }
 
-// K0b': candidate paths (global ids) -> local ids; a node outside the universe raises *err.
-__global__ void localize_paths_kernel(const uint32_t *__restrict__ psteps,
-                                      const uint32_t *__restrict__ map, uint32_t n_nodes,
-                                      uint32_t L, uint16_t *__restrict__ out, uint32_t total,
-                                      uint32_t *err) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= total) return;
-    uint32_t s = psteps[i], node = s >> 1;
-    uint32_t l = node < n_nodes ? map[node] : L;
-    if (l >= L) { atomicOr(err, 1u); l = L; }
-    out[i] = (uint16_t)((l << 1) | (s & 1u));
+// K0b': batch prologue: clears the accumulators; candidate paths (global ids) -> local ids, a node
+// outside the universe raises *err.
+__global__ void __launch_bounds__(256) prologue_kernel(PrologueArgs a) {
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        uint32_t *z = a.zero[r];
+        const uint32_t n = a.zero_words[r];
+        if ((n & 3u) == 0 && (reinterpret_cast<uintptr_t>(z) & 15u) == 0) {
+            uint4 *z4 = reinterpret_cast<uint4 *>(z);
+            for (uint32_t i = tid; i < n / 4; i += nthr) z4[i] = make_uint4(0, 0, 0, 0);
+        } else {
+            for (uint32_t i = tid; i < n; i += nthr) z[i] = 0;
+        }
+    }
+    if (a.psteps) {
+        for (uint32_t i = tid; i < a.total; i += nthr) {
+            const uint32_t s = a.psteps[i], node = s >> 1;
+            uint32_t l = node < a.n_nodes ? a.map[node] : a.L;
+            if (l >= a.L) { atomicOr(a.err, 1u); l = a.L; }
+            a.out[i] = (uint16_t)((l << 1) | (s & 1u));
+        }
+    }
 }
 
 // Which bucket a kBlock-row tile belongs to, and this thread's row in it.
@@ -976,12 +988,11 @@ void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uin
                                                                ldesc, perm, cursors, pd, n_pairs, pair_bias);
 }
 
-void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, uint32_t n_nodes,
-                           uint32_t L, uint16_t *out, uint32_t total, uint32_t *err,
-                           cudaStream_t st) {
-    if (total == 0) return;
-    localize_paths_kernel<<<(total + 255) / 256, 256, 0, st>>>(psteps, node2local, n_nodes, L, out,
-                                                                total, err);
+void launch_prologue(const PrologueArgs &a, int sm_count, cudaStream_t st) {
+    uint64_t most = a.psteps ? a.total : 0;
+    for (int r = 0; r < 4; ++r) most = std::max<uint64_t>(most, a.zero_words[r] / 4 + 1);
+    const uint64_t blocks = std::min<uint64_t>((most + 255) / 256, (uint64_t)sm_count * 8);
+    prologue_kernel<<<(unsigned)std::max<uint64_t>(blocks, 1), 256, 0, st>>>(a);
 }
 
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,

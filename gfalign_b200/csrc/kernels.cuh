@@ -202,9 +202,20 @@ void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uin
 __host__ __device__ constexpr uint32_t geom_node_base() { return 2u * kBloom; }
 __host__ __device__ constexpr uint32_t geom_lm_base(uint32_t L) { return geom_node_base() + 2u * (L + 1u); }
 __host__ __device__ constexpr uint32_t geom_pair_base(uint32_t L) { return (geom_lm_base(L) + kMaxBucket + 2u) & ~1u; }
-void launch_localize_paths(const uint32_t *psteps, const uint32_t *node2local, uint32_t n_nodes,
-                           uint32_t L, uint16_t *out, uint32_t total, uint32_t *err,
-                           cudaStream_t st);
+// One launch in front of every scoring batch: clears the batch's accumulators (count records, work
+// counters, mask tables, unit counters) and, for paths given as raw device steps, maps them to
+// universe-local 16-bit steps (psteps == nullptr: the host already did).
+struct PrologueArgs {
+    uint32_t *zero[4];
+    uint32_t zero_words[4];
+    const uint32_t *psteps;
+    const uint32_t *map;
+    uint32_t n_nodes, L;
+    uint16_t *out;
+    uint32_t total;
+    uint32_t *err;
+};
+void launch_prologue(const PrologueArgs &a, int sm_count, cudaStream_t st);
 // masks == nullptr: tables only (legacy kernel); else also ORs path p into the batch's bitsets
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
                          uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, uint32_t *masks,
