@@ -78,23 +78,6 @@ struct Planes {
 #pragma unroll
         for (int k = 0; k < kPlanes; ++k) p[k] = 0;
     }
-    // add eight 1-bit-per-column masks
-    __device__ __forceinline__ void add8(const uint32_t (&x)[8]) {
-        uint32_t c0, c1, c2, c3, d0, d1, e0;
-        csa(p[0], c0, p[0], x[0], x[1]);
-        csa(p[0], c1, p[0], x[2], x[3]);
-        csa(p[0], c2, p[0], x[4], x[5]);
-        csa(p[0], c3, p[0], x[6], x[7]);
-        csa(p[1], d0, p[1], c0, c1);
-        csa(p[1], d1, p[1], c2, c3);
-        csa(p[2], e0, p[2], d0, d1);
-#pragma unroll
-        for (int k = 3; k < kPlanes; ++k) {   // ripple the weight-8 carry
-            const uint32_t t = p[k] & e0;
-            p[k] ^= e0;
-            e0 = t;
-        }
-    }
     // add four / two masks (3:2 compressors first, then ripple the carry of weight 4 / 2)
     __device__ __forceinline__ void add(const uint32_t (&x)[4]) {
         uint32_t c0, c1, d0;
@@ -118,26 +101,27 @@ struct Planes {
             c0 = t;
         }
     }
-    // column c of the counter
-    __device__ __forceinline__ uint32_t value(int c) const {
-        uint32_t v = 0;
+    // columns c, c+8, c+16, c+24 of the counter at once: planes 0-7 land in the four bytes of `lo`,
+    // the planes above in the bytes of `hi` (three instructions per plane for four columns)
+    __device__ __forceinline__ void value4(int c, uint32_t &lo, uint32_t &hi) const {
+        static_assert(kPlanes > 8 && kPlanes <= 16, "two bytes per column");
+        lo = hi = 0;
 #pragma unroll
-        for (int k = 0; k < kPlanes; ++k) v |= ((p[k] >> c) & 1u) << k;
-        return v;
+        for (int k = 0; k < 8; ++k) lo += ((p[k] >> c) & 0x01010101u) << k;
+#pragma unroll
+        for (int k = 8; k < kPlanes; ++k) hi += ((p[k] >> c) & 0x01010101u) << (k - 8);
     }
 };
 
-__device__ __forceinline__ int unit_bucket(const BitsetArgs &a, uint32_t unit) {
-    int b = 1;
-#pragma unroll
-    for (int k = 2; k <= kMaxBucket; ++k) b += (unit >= a.unit_start[k]) ? 1 : 0;
-    return b;
+// Bucket (row length) of a unit: lane k compares with the first unit of bucket k (s_ustart: a
+// shared copy of unit_start, 0xFFFFFFFF beyond kMaxBucket), one vote counts the buckets passed.
+__device__ __forceinline__ int unit_bucket(const uint32_t *s_ustart, uint32_t unit, int lane) {
+    return __popc(__ballot_sync(0xFFFFFFFFu, unit >= s_ustart[lane])) - 1;   // entries 0 and 1 are 0
 }
 
 // first row / row count / bytes of a unit; used to prefetch the next unit's rows into L1
-__device__ __forceinline__ void prefetch_unit(const BitsetArgs &a, uint32_t unit, int lane) {
+__device__ __forceinline__ void prefetch_unit(const BitsetArgs &a, uint32_t unit, int b, int lane) {
     if (unit >= a.unit_start[kMaxBucket + 1]) return;
-    const int b = unit_bucket(a, unit);
     const uint32_t row0 = (unit - a.unit_start[b]) * a.unit_rows;
     const uint32_t nrows = min(a.unit_rows, a.bk.count[b] - row0);
     const uint32_t rs = row_stride(b);
@@ -255,7 +239,9 @@ __device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const uns
     uint32_t pass = 0xFFFFFFFFu, over = 0;
 #pragma unroll
     for (int j = 0; j < M; ++j) {
-        const uint2 e = nt[(elem(j) >> 1) * W];     // LDS.64: {N, F+|F-}
+        // byte offset like the pair entries below: shift, one and-or LOP3, LDS.64 [R + UR + imm]
+        const uint32_t o = ((elem(j) >> 1) * (8u * W)) | (2u * lane_off);
+        const uint2 e = *reinterpret_cast<const uint2 *>(mt + geom_node_base() * (4u * W) + o);   // {N, F+|F-}
         pass &= e.x;
         over |= e.y;
     }
@@ -399,7 +385,9 @@ score_bitset_kernel(const BitsetArgs a) {
     const uint32_t chunk = blockIdx.y;
     const uint32_t p_base = chunk * 32u * W;
     const int lane = threadIdx.x & 31;
+    __shared__ uint32_t s_ustart[32];
     if (threadIdx.x == 0) mbar_init(s_bar, 1);
+    if (threadIdx.x < 32) s_ustart[threadIdx.x] = threadIdx.x <= kMaxBucket ? a.unit_start[threadIdx.x] : 0xFFFFFFFFu;
     for (uint32_t i = threadIdx.x; i < 64u * W; i += blockDim.x) s_cnt[i] = 0;
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -427,11 +415,19 @@ score_bitset_kernel(const BitsetArgs a) {
     const uint32_t n_units = a.unit_start[kMaxBucket + 1];
 
     auto flush = [&]() {
-#pragma unroll 4
-        for (int c = 0; c < 32; ++c) {
-            const uint32_t g = G.value(c), b = B.value(c);
-            if (b) atomicAdd(&s_cnt[2 * (32 * w + c)], b);
-            if (g) atomicAdd(&s_cnt[2 * (32 * w + c) + 1], g);
+#pragma unroll 2
+        for (int c = 0; c < 8; ++c) {
+            uint32_t gl, gh, bl, bh;
+            G.value4(c, gl, gh);
+            B.value4(c, bl, bh);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t g = ((gl >> (8 * j)) & 0xFFu) | (((gh >> (8 * j)) & 0xFFu) << 8);
+                const uint32_t b = ((bl >> (8 * j)) & 0xFFu) | (((bh >> (8 * j)) & 0xFFu) << 8);
+                const uint32_t col = 32 * w + c + 8 * j;
+                if (b) atomicAdd(&s_cnt[2 * col], b);
+                if (g) atomicAdd(&s_cnt[2 * col + 1], g);
+            }
         }
         G.clear();
         B.clear();
@@ -446,13 +442,15 @@ score_bitset_kernel(const BitsetArgs a) {
         pending = atomicAdd(a.unit_ctr + chunk, 1u);
     }
     next = __shfl_sync(0xFFFFFFFFu, next, 0);
+    int next_b = unit_bucket(s_ustart, next, lane);
     for (;;) {
         const uint32_t unit = next;
         if (unit >= n_units) break;
+        const int b = next_b;
         next = __shfl_sync(0xFFFFFFFFu, pending, 0);
         if (lane == 0) pending = atomicAdd(a.unit_ctr + chunk, 1u);
-        prefetch_unit(a, next, lane);
-        const int b = unit_bucket(a, unit);
+        next_b = unit_bucket(s_ustart, next, lane);
+        prefetch_unit(a, next, next_b, lane);
         switch (b) {
 #define GFE_CASE(M_) case M_: score_unit<M_, W>(a, nt, nf, s_tab, tab, unit, word_base, G, B, lane); break;
             GFE_CASE(1) GFE_CASE(2) GFE_CASE(3) GFE_CASE(4) GFE_CASE(5) GFE_CASE(6) GFE_CASE(7)
