@@ -455,6 +455,7 @@ __device__ __forceinline__ void exact_both(const uint16_t *__restrict__ A, int n
                                            const uint16_t *__restrict__ b, int m, bool need_both,
                                            int *tf, int *tr) {
     if (m <= 8) exact_both_regs<8>(A, n, b, m, need_both, tf, tr);
+    else if (m <= 16) exact_both_regs<16>(A, n, b, m, need_both, tf, tr);
     else exact_both_regs<kExactRegSteps>(A, n, b, m, need_both, tf, tr);
 }
 
