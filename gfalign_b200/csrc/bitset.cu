@@ -132,13 +132,24 @@ __device__ __forceinline__ void prefetch_unit(const BitsetArgs &a, uint32_t unit
 }
 
 // Push the set bits of the eight masks of one warp step (paths word_base .. word_base+31, rows
-// row_first + u*row_step) as (path, row) work items.  Called by the whole warp: ONE atomic on the
-// list counter per call (a per-lane atomic serialises on a single L2 address).
-__device__ __noinline__ void push_slow8(uint2 *__restrict__ slow, uint32_t *work_count,
-                                        uint32_t slow_cap, uint32_t s0, uint32_t s1, uint32_t s2,
-                                        uint32_t s3, uint32_t s4, uint32_t s5, uint32_t s6,
-                                        uint32_t s7, uint32_t word_base, uint32_t row_first,
-                                        uint32_t row_step, int lane) {
+// row_first + u*row_step) as (path, row) work items.  Called by the whole warp.  The warp owns a
+// window [win.x, win.y) of the list, reserved kSlowChunk slots at a time with ONE atomic on the
+// list counter -- the round trip to L2 is paid once per chunk, not once per call; what a warp
+// leaves unused of its last window is filled with kSlowHole entries the second-look kernel skips.
+constexpr uint32_t kSlowChunk = 64;
+
+__device__ __forceinline__ void fill_slow_holes(uint2 *__restrict__ slow, uint32_t *work_count,
+                                                uint32_t slow_cap, uint2 win, int lane) {
+    if (lane == 0 && win.y > win.x) atomicAdd(work_count + 4, win.y - win.x);   // holes; no return value used
+    for (uint32_t i = win.x + (uint32_t)lane; i < win.y; i += 32u)
+        if (i < slow_cap) slow[i] = make_uint2(kSlowHole, kSlowHole);
+}
+
+__device__ __noinline__ uint2 push_slow8(uint2 *__restrict__ slow, uint32_t *work_count,
+                                         uint32_t slow_cap, uint2 win, uint32_t s0, uint32_t s1, uint32_t s2,
+                                         uint32_t s3, uint32_t s4, uint32_t s5, uint32_t s6,
+                                         uint32_t s7, uint32_t word_base, uint32_t row_first,
+                                         uint32_t row_step, int lane) {
     const uint32_t sm[8] = {s0, s1, s2, s3, s4, s5, s6, s7};
     uint32_t n = 0;
 #pragma unroll
@@ -149,10 +160,19 @@ __device__ __noinline__ void push_slow8(uint2 *__restrict__ slow, uint32_t *work
         const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
         if (lane >= o) incl += t;
     }
-    uint32_t base = 0;
-    if (lane == 31) base = atomicAdd(work_count + 2, incl);
-    base = __shfl_sync(0xFFFFFFFFu, base, 31);
-    uint32_t idx = base + incl - n;
+    const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    if (win.x + total > win.y) {      // warp-uniform: the window is used up
+        fill_slow_holes(slow, work_count, slow_cap, win, lane);
+        const uint32_t need = total > kSlowChunk ? total : kSlowChunk;
+        uint32_t base = 0;
+        if (lane == 0) {
+            base = atomicAdd(work_count + 2, need);
+        }
+        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+        win.x = base;
+        win.y = base + need;
+    }
+    uint32_t idx = win.x + incl - n;
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
         uint32_t mask = sm[u];
@@ -167,6 +187,8 @@ __device__ __noinline__ void push_slow8(uint2 *__restrict__ slow, uint32_t *work
             ++idx;
         }
     }
+    win.x += total;
+    return win;
 }
 
 // Second, exact look at one row (runtime length m) for this lane's 32 paths; the warp calls it
@@ -291,7 +313,8 @@ template <int M, int W>
 __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__restrict__ nt,
                                            const uint2 *__restrict__ nf, const uint32_t *__restrict__ s_tab,
                                            const uint32_t *__restrict__ tab, uint32_t unit,
-                                           uint32_t word_base, Planes &G, Planes &B, int lane) {
+                                           uint32_t word_base, Planes &G, Planes &B, uint2 &slow_win,
+                                           int lane) {
     constexpr int R = 32 / W;                       // rows per warp step
     constexpr int RS = (int)row_stride(M);
     constexpr int UB = M <= 8 ? 4 : 2;   // rows scored per loop trip (their data is loaded first)
@@ -366,10 +389,12 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__r
         B.add(bm);
 #pragma unroll
         for (int k = 0; k < UB; ++k) any_slow |= sm[k] | sb[k];
-        if (__any_sync(0xFFFFFFFFu, any_slow != 0))
-            push_slow8(a.slow, a.work_count, a.slow_cap, sm[0], sm[1], UB > 2 ? sm[UB > 2 ? 2 : 0] : 0u,
-                       UB > 2 ? sm[UB > 2 ? 3 : 0] : 0u, sb[0], sb[1], UB > 2 ? sb[UB > 2 ? 2 : 0] : 0u,
-                       UB > 2 ? sb[UB > 2 ? 3 : 0] : 0u, word_base, sorted0 + it + sub, (uint32_t)R, lane);
+        if (__any_sync(0xFFFFFFFFu, any_slow != 0)) {
+            slow_win = push_slow8(a.slow, a.work_count, a.slow_cap, slow_win, sm[0], sm[1],
+                                  UB > 2 ? sm[UB > 2 ? 2 : 0] : 0u, UB > 2 ? sm[UB > 2 ? 3 : 0] : 0u, sb[0], sb[1],
+                                  UB > 2 ? sb[UB > 2 ? 2 : 0] : 0u, UB > 2 ? sb[UB > 2 ? 3 : 0] : 0u, word_base,
+                                  sorted0 + it + sub, (uint32_t)R, lane);
+        }
     }
 }
 
@@ -412,6 +437,7 @@ score_bitset_kernel(const BitsetArgs a) {
     G.clear();
     B.clear();
     uint32_t rows_acc = 0;
+    uint2 slow_win = make_uint2(0u, 0u);   // this warp's reserved window of the second-look list
     const uint32_t n_units = a.unit_start[kMaxBucket + 1];
 
     auto flush = [&]() {
@@ -435,24 +461,28 @@ score_bitset_kernel(const BitsetArgs a) {
     };
 
     // Dynamic scheduling, two units ahead: `unit` is being scored, `next` is known to the warp and
-    // its rows are being prefetched into L1, `pending` is lane 0's atomic still in flight.
+    // its rows are being prefetched into L1, `pending` is lane 0's atomic still in flight.  Units
+    // are claimed from the longest rows down to the shortest (the counter counts claims; unit =
+    // n_units - 1 - claim), so the last units a CTA waits for at the end are the cheapest ones.
     uint32_t next = 0, pending = 0;
     if (lane == 0) {
         next = atomicAdd(a.unit_ctr + chunk, 1u);
         pending = atomicAdd(a.unit_ctr + chunk, 1u);
     }
     next = __shfl_sync(0xFFFFFFFFu, next, 0);
-    int next_b = unit_bucket(s_ustart, next, lane);
+    int next_b = unit_bucket(s_ustart, n_units - 1u - min(next, n_units - 1u), lane);
     for (;;) {
-        const uint32_t unit = next;
-        if (unit >= n_units) break;
+        if (next >= n_units) break;
+        const uint32_t unit = n_units - 1u - next;
         const int b = next_b;
         next = __shfl_sync(0xFFFFFFFFu, pending, 0);
         if (lane == 0) pending = atomicAdd(a.unit_ctr + chunk, 1u);
-        next_b = unit_bucket(s_ustart, next, lane);
-        prefetch_unit(a, next, next_b, lane);
+        if (next < n_units) {
+            next_b = unit_bucket(s_ustart, n_units - 1u - next, lane);
+            prefetch_unit(a, n_units - 1u - next, next_b, lane);
+        }
         switch (b) {
-#define GFE_CASE(M_) case M_: score_unit<M_, W>(a, nt, nf, s_tab, tab, unit, word_base, G, B, lane); break;
+#define GFE_CASE(M_) case M_: score_unit<M_, W>(a, nt, nf, s_tab, tab, unit, word_base, G, B, slow_win, lane); break;
             GFE_CASE(1) GFE_CASE(2) GFE_CASE(3) GFE_CASE(4) GFE_CASE(5) GFE_CASE(6) GFE_CASE(7)
             GFE_CASE(8) GFE_CASE(9) GFE_CASE(10) GFE_CASE(11) GFE_CASE(12) GFE_CASE(13)
             GFE_CASE(14) GFE_CASE(15) GFE_CASE(16)
@@ -463,6 +493,7 @@ score_bitset_kernel(const BitsetArgs a) {
         if (rows_acc > (1u << kPlanes) - 2u * a.unit_rows) flush();
     }
     flush();
+    fill_slow_holes(a.slow, a.work_count, a.slow_cap, slow_win, lane);
     __syncthreads();
     // alignments without steps pass the filter and score 0 against every path: good
     const uint32_t empty_rows = blockIdx.x == 0 ? a.bk.count[0] : 0u;

@@ -420,7 +420,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     pro.zero[0] = d_counts;
     pro.zero_words[0] = P * 2;
     pro.zero[1] = d_work_count;
-    pro.zero_words[1] = 4;
+    pro.zero_words[1] = kWorkCounters;
     pro.psteps = d_raw_steps;
     pro.map = e->d_node2local.ptr;
     pro.n_nodes = e->n_nodes;
@@ -585,9 +585,9 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
     const size_t bytes = off_bytes + (size_t)total * 2;
     TRY(ensure_pinned(e, e->h_stage, bytes));
     TRY(ensure_dev(e, e->d_stage, bytes));
-    // the four work counters ride behind the count records: one device->host copy per batch
-    TRY(ensure_pinned(e, e->h_counts, (size_t)P * 2 + 4));
-    TRY(ensure_dev(e, e->d_counts, (size_t)P * 2 + 4));
+    // the work counters ride behind the count records: one device->host copy per batch
+    TRY(ensure_pinned(e, e->h_counts, (size_t)P * 2 + kWorkCounters));
+    TRY(ensure_dev(e, e->d_counts, (size_t)P * 2 + kWorkCounters));
     memcpy(e->h_stage.ptr, path_offsets, (size_t)(P + 1) * 4);
     uint16_t *ls = reinterpret_cast<uint16_t *>(e->h_stage.ptr + off_bytes);
     for (uint32_t i = 0; i < total; ++i) {
@@ -605,14 +605,15 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
     const uint16_t *d_pstep = reinterpret_cast<const uint16_t *>(e->d_stage.ptr + off_bytes);
     TRY(enqueue_score(e, d_poff, d_pstep, P, total, filter, e->d_counts.ptr,
                       e->d_counts.ptr + (size_t)P * 2, nullptr, e->stream));
-    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, ((size_t)P * 2 + 4) * sizeof(uint32_t),
-                                cudaMemcpyDeviceToHost, e->stream));
-    uint32_t wc[4] = {0, 0, 0, 0};
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr,
+                                ((size_t)P * 2 + kWorkCounters) * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+                                e->stream));
+    uint32_t wc[kWorkCounters] = {};
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-    for (int i = 0; i < 4; ++i) wc[i] = e->h_counts.ptr[(size_t)P * 2 + i];
+    for (int i = 0; i < kWorkCounters; ++i) wc[i] = e->h_counts.ptr[(size_t)P * 2 + i];
     if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
     e->h2d_bytes += bytes;
-    e->d2h_bytes += (size_t)P * 2 * sizeof(uint32_t) + 16;
+    e->d2h_bytes += ((size_t)P * 2 + kWorkCounters) * sizeof(uint32_t);
     if (wc[3]) {
         // the list of pairs the bitsets could not settle overflowed: grow it, or halve the batch
         if (e->d_slow.cap < (1ull << 28)) {
@@ -639,7 +640,7 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
         return gfe_score_paths(e, path_offsets, path_steps, P, filter, counts);
     }
     e->exact_pairs += wc[0];
-    e->slow_pairs += wc[2];
+    e->slow_pairs += wc[2] - wc[4];   // reserved slots minus the holes
     memcpy(counts, e->h_counts.ptr, (size_t)P * 2 * sizeof(uint32_t));
     return GFE_OK;
 }
@@ -660,7 +661,7 @@ int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
         TRY(ensure_dev(e, e->d_err, 4));
         CUDA_TRY(e, cudaMemsetAsync(e->d_err.ptr, 0, 4 * sizeof(uint32_t), st));
     }
-    TRY(ensure_dev(e, e->d_work_count, 4));
+    TRY(ensure_dev(e, e->d_work_count, kWorkCounters));
     return enqueue_score(e, d_path_offsets, e->d_plocal.ptr, P, total_path_steps, filter, d_counts,
                          e->d_work_count.ptr, d_path_steps, st);
 }
@@ -712,14 +713,14 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
     TRY(ensure_dev(e, e->d_counts, 2));
     TRY(ensure_pinned(e, e->h_counts, 2));
     TRY(ensure_dev(e, e->d_pair_work, std::max<uint64_t>(e->A, 1)));
-    TRY(ensure_dev(e, e->d_work_count, 4));
+    TRY(ensure_dev(e, e->d_work_count, kWorkCounters));
     const bool want_scores = t_fw || t_rc;
     if (want_scores) {
         TRY(ensure_dev(e, e->d_tfw, std::max<uint64_t>(e->A, 1)));
         TRY(ensure_dev(e, e->d_trc, std::max<uint64_t>(e->A, 1)));
     }
     CUDA_TRY(e, cudaMemsetAsync(e->d_counts.ptr, 0, 2 * sizeof(uint32_t), st));
-    CUDA_TRY(e, cudaMemsetAsync(e->d_work_count.ptr, 0, 4 * sizeof(uint32_t), st));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_work_count.ptr, 0, kWorkCounters * sizeof(uint32_t), st));
     TRY(ensure_dev(e, e->d_pnext, (size_t)n + 8));
     {
         MaskGeom mg{};

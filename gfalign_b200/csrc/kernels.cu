@@ -755,6 +755,7 @@ slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < cnt;
          idx += gridDim.x * blockDim.x) {
         uint2 w = slow[idx];
+        if (w.x == kSlowHole) continue;     // unused tail of a warp's reserved window
         const uint32_t guess = w.x >> 31;   // the bitset kernel already counted this pair good (1) / bad (0)
         w.x &= 0x7FFFFFFFu;
         const RowRef r = locate_row(a.bk, w.y);

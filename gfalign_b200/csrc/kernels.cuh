@@ -43,6 +43,8 @@ constexpr int kExactRegSteps = 32;    // widest alignment the register DP handle
 constexpr int kMaxChunk = 64;         // candidate paths per CTA pass (tables in shared memory)
 constexpr uint32_t kTabAbsent = 0;
 constexpr int kBitThreads = 512;      // threads per CTA of the bitset kernel (one CTA per SM)
+constexpr uint32_t kSlowHole = 0xFFFFFFFFu;   // unused slot of the second-look list (bitset.cu push_slow8)
+constexpr int kWorkCounters = 8;      // [0] exact entries [1] exact overflow [2] second-look slots [3] overflow [4] holes among [2]
 constexpr int kPlanes = 12;           // bit-sliced counter planes per lane (flush before 2^12 rows)
 constexpr uint32_t kPairHashCap = 1u << 16;   // slots of the pair dictionary
 constexpr uint32_t kPairEmpty = 0xFFFFFFFFu;
