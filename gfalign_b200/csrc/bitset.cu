@@ -415,6 +415,8 @@ score_bitset_kernel(const BitsetArgs a) {
     if (threadIdx.x < 32) s_ustart[threadIdx.x] = threadIdx.x <= kMaxBucket ? a.unit_start[threadIdx.x] : 0xFFFFFFFFu;
     for (uint32_t i = threadIdx.x; i < 64u * W; i += blockDim.x) s_cnt[i] = 0;
     __syncthreads();
+    pdl_wait();      // build_tables' mask tables (everything above only touched this CTA's shared memory)
+    pdl_trigger();
     if (threadIdx.x == 0) {
         // one TMA bulk copy per <= 64 KB slice of this chunk's table
         const uint32_t bytes = tab_words * 4u;
@@ -520,7 +522,7 @@ void launch_w(const BitsetArgs &a, int sm_count, cudaStream_t st) {
     const uint32_t n_units = a.unit_start[kMaxBucket + 1];
     const uint32_t max_gx = (n_units + (kBitThreads / 32) - 1) / (kBitThreads / 32);
     if (gx > max_gx) gx = max_gx ? max_gx : 1;
-    score_bitset_kernel<W><<<dim3(gx, chunks), kBitThreads, smem, st>>>(a);
+    launch_pdl(1, score_bitset_kernel<W>, dim3(gx, chunks), dim3(kBitThreads), smem, st, a);
 }
 
 }  // namespace

@@ -252,6 +252,7 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
                     uint16_t *__restrict__ pnext, uint32_t *__restrict__ masks,
                     uint32_t *__restrict__ fplane, const MaskGeom mg, const PairDict pd) {
     extern __shared__ uint32_t row[];
+    pdl_trigger();   // the scoring kernel may be scheduled now; it waits for this grid before its first read
     const uint32_t p = blockIdx.x;
     const uint32_t o0 = poff[p], n = poff[p + 1] - o0;
     const uint16_t *s = pstep + o0;
@@ -751,7 +752,10 @@ score_paths_kernel(const ScoreArgs a, const uint32_t tile_lo, const uint32_t til
 __global__ void __launch_bounds__(128)
 slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
                      const uint32_t *__restrict__ slow_count, const uint32_t slow_cap) {
-    const uint32_t cnt = min(slow_count[0], slow_cap);
+    pdl_wait();      // the scoring kernel's list and counts
+    pdl_trigger();
+    // volatile: a load through the read-only path may be hoisted above the wait
+    const uint32_t cnt = min(*reinterpret_cast<const volatile uint32_t *>(slow_count), slow_cap);
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < cnt;
          idx += gridDim.x * blockDim.x) {
         uint2 w = slow[idx];
@@ -781,7 +785,8 @@ slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
 // K1b: exact verdict for the worklist of ambiguous (path, alignment) pairs.
 __global__ void __launch_bounds__(128)
 exact_worklist_kernel(const ScoreArgs a) {
-    const uint32_t cnt = min(a.work_count[0], a.work_cap);
+    pdl_wait();      // the second-look kernel's worklist
+    const uint32_t cnt = min(*reinterpret_cast<const volatile uint32_t *>(a.work_count), a.work_cap);
     for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < cnt;
          idx += gridDim.x * blockDim.x) {
         const uint2 w = a.work[idx];
@@ -1001,6 +1006,7 @@ void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P
                          uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, uint32_t *masks,
                          uint32_t *fplane, const MaskGeom &mg, const PairDict &pd, cudaStream_t st) {
     if (P == 0) return;
+    // plain launch (full stream order behind the prologue); its trigger lets the scoring kernel in early
     build_tables_kernel<<<P, kBlock, (size_t)(L + 1) * sizeof(uint32_t), st>>>(
         poff, pstep, L, tab_stride, ptab, pnext, masks, fplane, mg, pd);
 }
@@ -1028,11 +1034,11 @@ void launch_score_paths(const ScoreArgs &a, int sm_count, uint32_t tile_lo, uint
 
 void launch_slow_worklist(const ScoreArgs &a, const uint2 *slow, const uint32_t *slow_count,
                           uint32_t slow_cap, cudaStream_t st) {
-    slow_worklist_kernel<<<148 * 16, 128, 0, st>>>(a, slow, slow_count, slow_cap);
+    launch_pdl(2, slow_worklist_kernel, dim3(148 * 16), dim3(128), 0, st, a, slow, slow_count, slow_cap);
 }
 
 void launch_exact_worklist(const ScoreArgs &a, cudaStream_t st) {
-    exact_worklist_kernel<<<148 * 4, 128, 0, st>>>(a);
+    launch_pdl(3, exact_worklist_kernel, dim3(148 * 4), dim3(128), 0, st, a);
 }
 
 void launch_exact_worklist_long(const ScoreArgs &a, uint32_t max_m, cudaStream_t st) {

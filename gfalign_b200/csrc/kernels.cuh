@@ -31,6 +31,7 @@
 //   edge support      src/alignments.cpp:353-403, src/eval.cpp:42-60
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdlib>
 #include <stdint.h>
 
 namespace gfe {
@@ -204,6 +205,37 @@ void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uin
 __host__ __device__ constexpr uint32_t geom_node_base() { return 2u * kBloom; }
 __host__ __device__ constexpr uint32_t geom_lm_base(uint32_t L) { return geom_node_base() + 2u * (L + 1u); }
 __host__ __device__ constexpr uint32_t geom_pair_base(uint32_t L) { return (geom_lm_base(L) + kMaxBucket + 2u) & ~1u; }
+// Programmatic dependent launch (the chain prologue -> tables -> bitset scoring -> second look ->
+// exact DP of one batch): a kernel launched with launch_pdl may be scheduled while its predecessor
+// in the stream drains; it must call pdl_wait() before it touches anything a predecessor wrote
+// (the wait returns when every earlier grid has completed and flushed).  pdl_trigger(), placed
+// AFTER the kernel's own wait, lets its successor be scheduled early -- so at most two kernels of
+// the chain overlap and a waiting kernel can only be early with respect to its direct predecessor.
+// The first value a kernel reads from that predecessor goes through a volatile load: a load on the
+// read-only path (const __restrict__ / __ldg) counts as invariant and may be hoisted above the
+// wait.  Without the launch attribute both calls are no-ops (plain <<<>>> launches stay correct).
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(int edge, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t st, Args &&...args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    static const int mask = getenv("GFE_PDL_MASK") ? atoi(getenv("GFE_PDL_MASK")) : 15;   // debugging aid
+    cfg.attrs = attr;
+    cfg.numAttrs = (mask >> edge) & 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 // One launch in front of every scoring batch: clears the batch's accumulators (count records, work
 // counters, mask tables, unit counters) and, for paths given as raw device steps, maps them to
 // universe-local 16-bit steps (psteps == nullptr: the host already did).
