@@ -3,6 +3,7 @@
 // one CUDA stream.  There is no CPU scoring path in this library: every entry point either runs
 // the kernels or fails with an error status.
 #include "engine.h"
+#include <chrono>
 
 #include <algorithm>
 #include <cstdarg>
@@ -105,15 +106,22 @@ int gfe_create(int cuda_device, gfe_engine **out) {
         const char *fl = getenv("GFE_FORCE_LEGACY");
         e->force_legacy = (fl && fl[0] == '1') ? 1 : 0;
     }
+    const bool dbg = getenv("GFE_DEBUG_TIMING") != nullptr;
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
     err = cudaSetDevice(cuda_device);
+    if (err == cudaSuccess) err = cudaFree(nullptr);   // creates the primary context here, not in the first real call
+    const double t1 = now();
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
-    cudaDeviceProp prop;
-    if (err == cudaSuccess) err = cudaGetDeviceProperties(&prop, cuda_device);
+    if (err == cudaSuccess) err = cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, cuda_device);
+    const double t2 = now();
     if (err == cudaSuccess) {
-        e->sm_count = prop.multiProcessorCount;
         int rc = configure_kernels();
         if (rc != 0) err = (cudaError_t)rc;
     }
+    if (dbg)
+        fprintf(stderr, "[gfe_create] context %.3f s, stream+attributes %.3f s, kernel configuration %.3f s\n",
+                t1 - t0, t2 - t1, now() - t2);
     if (err != cudaSuccess) {
         set_error(nullptr, "CUDA initialisation failed on device %d: %s", cuda_device,
                   cudaGetErrorString(err));

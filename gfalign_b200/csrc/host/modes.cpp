@@ -12,7 +12,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
+#include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "host.h"
@@ -21,22 +23,52 @@ namespace gfh {
 
 namespace {
 
+// CUDA start-up (driver initialisation + context: ~1 s on a B200 box) runs on its own thread while
+// the text inputs are parsed; the first engine call joins it.
+struct Engine;
+Engine *g_starting = nullptr;
+void finish_start();
+
 [[noreturn]] void die(const std::string &msg) {
+    finish_start();   // never exit() with the CUDA start-up still in flight
     fprintf(stderr, "%s\n", msg.c_str());
     exit(EXIT_FAILURE);
 }
 
 struct Engine {
     gfe_engine *e = nullptr;
+    int rc = GFE_OK;
+    std::string err;
+    std::thread th;
     explicit Engine(int device) {
-        if (gfe_create(device, &e) != GFE_OK)
-            die(std::string("gfalign-b200: ") + gfe_last_error(nullptr));
+        g_starting = this;
+        th = std::thread([this, device] {
+            rc = gfe_create(device, &e);
+            if (rc != GFE_OK) err = gfe_last_error(nullptr);   // thread-local message: read it here
+        });
     }
-    ~Engine() { gfe_destroy(e); }
-    void check(int rc) const {
-        if (rc != GFE_OK) die(std::string("gfalign-b200: ") + gfe_last_error(e));
+    void wait() {
+        if (th.joinable()) th.join();
+        if (g_starting == this) g_starting = nullptr;
+    }
+    // joins the start-up; dies the way the synchronous constructor did when there is no device
+    gfe_engine *get() {
+        wait();
+        if (rc != GFE_OK) die(std::string("gfalign-b200: ") + err);
+        return e;
+    }
+    ~Engine() {
+        wait();
+        if (e) gfe_destroy(e);
+    }
+    void check(int r) const {
+        if (r != GFE_OK) die(std::string("gfalign-b200: ") + gfe_last_error(e));
     }
 };
+
+void finish_start() {
+    if (g_starting) g_starting->wait();
+}
 
 double now_s() {
     using namespace std::chrono;
@@ -199,6 +231,7 @@ void emit_row(const gfe_search_row *r, void *user) {   // the row of src/eval.cp
 }  // namespace
 
 int run_search(const Options &o) {
+    Engine eng(o.device);   // CUDA start-up overlaps the parsing below
     const double t0 = now_s();
     Graph g;
     load_graph(o, g);
@@ -223,7 +256,7 @@ int run_search(const Options &o) {
         die(err);
     }
     const double t1 = now_s();
-    Engine eng(o.device);
+    eng.get();
     eng.check(gfe_set_alignments(eng.e, gaf.offsets.data(), gaf.steps.data(), gaf.A, g.names.size()));
     gfe_graph gv = g.view();
     gfe_search_params p;
@@ -263,6 +296,7 @@ int run_search(const Options &o) {
 // ---- evalPath (src/eval.cpp:196-242) ------------------------------------------------------------------
 
 int run_evalpath(const Options &o) {
+    Engine eng(o.device);   // CUDA start-up overlaps the parsing below
     Graph g;
     load_graph(o, g);
     // path string: components split at ';' / ',' (the separator stays on the component and is
@@ -297,7 +331,7 @@ int run_evalpath(const Options &o) {
     Gaf gaf;
     if (!o.gaf.empty()) load_gaf(o, g.names, 0, false, gaf);
     else gaf.offsets.assign(1, 0);
-    Engine eng(o.device);
+    eng.get();
     eng.check(gfe_set_alignments(eng.e, gaf.offsets.data(), gaf.steps.data(), gaf.A, g.names.size()));
     std::vector<int32_t> tfw(gaf.A), trc(gaf.A);
     uint32_t bad = 0, good = 0;
@@ -428,6 +462,9 @@ void mark_duplicates(const Gaf &gaf, const std::vector<uint64_t> &order, Alignme
 }  // namespace
 
 int run_evalgfa(const Options &o) {
+    // CUDA start-up overlaps the parsing and the alignment summary; not needed at all without -o
+    std::unique_ptr<Engine> engp;
+    if (!o.out_file.empty()) engp.reset(new Engine(o.device));
     Graph g;
     load_graph(o, g);
     if (o.gaf.empty()) return EXIT_SUCCESS;   // nothing to do without alignments (src/input-gfalign.cpp:83,92)
@@ -449,7 +486,8 @@ int run_evalgfa(const Options &o) {
         fflush(stdout);
     }
     if (o.out_file.empty()) return EXIT_SUCCESS;
-    Engine eng(o.device);
+    Engine &eng = *engp;
+    eng.get();
     eng.check(gfe_set_alignments(eng.e, gaf.offsets.data(), gaf.steps.data(), gaf.A, g.names.size()));
     const uint32_t E = (uint32_t)g.links.size();
     std::vector<uint32_t> w(E);
@@ -514,6 +552,7 @@ int run_evalgfa(const Options &o) {
 // ---- filter (Input::read case 4, src/input-gfalign.cpp:113-119) -----------------------------------
 
 int run_filter(const Options &o) {
+    Engine eng(o.device);   // CUDA start-up overlaps the parsing below
     if (o.gaf.empty()) return EXIT_SUCCESS;
     // readNodelist: every line of the node file is a name (no column split, src/input-gfalign.cpp:62-72)
     NameTable set;
@@ -532,7 +571,7 @@ int run_filter(const Options &o) {
     const uint32_t N = set.size();
     Gaf gaf;
     load_gaf(o, set, N, true, gaf);   // names outside the list share the id N
-    Engine eng(o.device);
+    eng.get();
     eng.check(gfe_set_alignments(eng.e, gaf.offsets.data(), gaf.steps.data(), gaf.A, N + 1));
     std::vector<uint32_t> nodes(N);
     std::iota(nodes.begin(), nodes.end(), 0);
