@@ -270,7 +270,26 @@ def main():
     torch.cuda.set_stream(tstream)
     stream = tstream.cuda_stream
 
+    # the exchange step of the sharded path: one peer-memory kernel per rank (csrc/peer.cu) reading
+    # every shard's record over NVLink; GFE_EXCHANGE=nccl selects a NCCL all-reduce instead
+    px = None
+    exchange = "none"
+    if dist is not None:
+        exchange = "nccl all-reduce"
+        if os.environ.get("GFE_EXCHANGE", "peer") == "peer":
+            try:
+                from gfalign_b200.sharded import PeerExchange
+                px = PeerExchange(P * 2, dev)
+                exchange = "peer-memory sum kernel (NVLink P2P loads)"
+            except Exception as ex:   # no peer access between the GPUs of this box
+                sys.stderr.write(f"[bench] peer exchange unavailable ({ex!r}); using NCCL\n")
+
     def step():
+        if px is not None:
+            eng.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), P, int(pst.size),
+                                   px.half_ptr(), filter=True, stream=stream)
+            px.sum_into(d_counts.data_ptr(), P * 2, stream)
+            return
         eng.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), P, int(pst.size),
                                d_counts.data_ptr(), filter=True, stream=stream)
         if dist is not None:
@@ -401,10 +420,10 @@ def main():
             "config": {"workload": desc, "alignments_per_gpu": A, "mean_steps": mbar,
                        "candidate_paths_per_step": P, "filter": True,
                        "l2": "flushed (512 MiB write) before every timed step",
-                       "parallelism": f"alignment shards x{world}, NCCL all-reduce of counts"
+                       "parallelism": f"alignment shards x{world}, counts summed by {exchange}"
                        if world > 1 else "single GPU"},
             "clocks": sampler.summary(), "e2e": e2e, "roofline": roofline,
-            "gpu_launches": int(c1["kernel_launches"] - c0["kernel_launches"]),
+            "gpu_launches": int(c1["kernel_launches"] - c0["kernel_launches"]) + (args.steps if px is not None else 0),
             "wall_ms_timed_region": wall * 1e3,
             "exact_dp_pairs_per_step": int(c1["exact_pairs"] - c0["exact_pairs"]) // args.steps}
 

@@ -79,10 +79,22 @@ EXPORTS = [
     "gfe_last_kernel_ms", "gfe_kernel_time_stats", "gfe_device_status",
     "gfe_trace_pairs", "gfe_filter_alignments",
     "gfe_text_open", "gfe_text_close", "gfe_text_get", "gfe_text_node_name", "gfe_text_node_id",
-    "gfe_text_qname",
+    "gfe_text_qname", "gfe_peer_sum_u32",
 ]
 
+PEER_MAX = 16      # GFE_PEER_MAX
+
 _lib = None
+
+
+def peer_sum_u32(peer_bases, rank: int, n_cap: int, n: int, epoch: int, d_out: int, stream: int = 0) -> None:
+    """gfe_peer_sum_u32: sum the n count slots of all ranks out of their peer-mapped exchange
+    buffers (peer_bases[q] = rank q's buffer as mapped here) into the device array at d_out."""
+    lib = load_library()
+    arr = (C.c_uint64 * len(peer_bases))(*[int(b) for b in peer_bases])
+    rc = lib.gfe_peer_sum_u32(arr, len(peer_bases), rank, n_cap, n, epoch, C.c_void_p(d_out), C.c_void_p(stream))
+    if rc != 0:
+        raise GfeError(rc, "gfe_peer_sum_u32: bad arguments or launch failure")
 
 
 def load_library() -> C.CDLL:
@@ -114,6 +126,8 @@ def load_library() -> C.CDLL:
     lib.gfe_edge_traversals_device.argtypes = [C.c_void_p, _u32p, _u32p, C.c_uint32, C.c_void_p,
                                                C.c_void_p]
     lib.gfe_edge_weights_from_counts.argtypes = [_u32p, _u32p, C.c_uint32, _u32p, _u32p]
+    lib.gfe_peer_sum_u32.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_int, C.c_uint32, C.c_uint32,
+                                     C.c_uint32, C.c_void_p, C.c_void_p]
     lib.gfe_search.argtypes = [C.c_void_p, C.POINTER(_Graph), C.POINTER(_SearchParams), _ROW_FN,
                                C.c_void_p, C.POINTER(_SearchStats)]
     lib.gfe_search_with_scorer.argtypes = [_SCORE_FN, C.c_void_p, C.POINTER(_Graph),

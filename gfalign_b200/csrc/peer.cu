@@ -1,0 +1,86 @@
+// gfalign_b200/csrc/peer.cu — the one exchange step of the sharded path: the
+// P x {bad, good} count records of the alignment shards are summed across the GPUs of a box by ONE
+// small kernel per rank that reads every peer's record straight out of its HBM over NVLink
+// (symmetric buffers mapped into every process), instead of a NCCL all-reduce (~45-60 us of launch
+// and protocol latency for 8 KB on 8 GPUs; this kernel: a flag round trip plus 8 KB per peer).
+//
+// Buffer layout (the same on every rank; `bases[p]` is rank p's buffer as mapped here):
+//   u32 data[2][n_cap]   two halves, used alternately: half (epoch & 1) carries this epoch's records
+//   u32 flags[kMaxPeers] flags[q] on rank p = the last epoch rank q announced to rank p
+// Protocol of epoch e (e = 1, 2, ...; all ranks call with the same e, stream-ordered behind the
+// kernels that produced data[e & 1]):
+//   1. block 0 publishes: fence, then flags[rank] := e on every peer (release, system scope);
+//   2. every block waits until its own flags[q] >= e for all q (acquire, system scope);
+//   3. out[i] = sum over q of peer q's data[e & 1][i].
+// A rank can run at most one epoch ahead of a peer (its next publish needs that peer's flag), and
+// then it writes the OTHER half, so no second barrier is needed; flags only grow, hence ">=".
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/gfalign_b200.h"
+
+namespace {
+
+constexpr int kMaxPeers = GFE_PEER_MAX;
+
+struct PeerArgs {
+    uint32_t *base[kMaxPeers];
+    int world, rank;
+    uint32_t n, n_cap, epoch;
+    uint32_t *out;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(512) peer_sum_kernel(PeerArgs a) {
+    const size_t flag0 = 2 * (size_t)a.n_cap;
+    if (blockIdx.x == 0 && threadIdx.x < a.world) {
+        __threadfence_system();   // this rank's records (written by earlier kernels of the stream)
+        st_release_sys(a.base[threadIdx.x] + flag0 + a.rank, a.epoch);
+    }
+    if (threadIdx.x < a.world) {
+        const uint32_t *f = a.base[a.rank] + flag0 + threadIdx.x;
+        while ((int32_t)(ld_acquire_sys(f) - a.epoch) < 0) __nanosleep(20);
+    }
+    __syncthreads();
+    const size_t half = (size_t)(a.epoch & 1u) * a.n_cap;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += gridDim.x * blockDim.x) {
+        uint32_t s = 0;
+        for (int q = 0; q < a.world; ++q) s += ld_relaxed_sys(a.base[q] + half + i);
+        a.out[i] = s;
+    }
+}
+
+}  // namespace
+
+extern "C" int gfe_peer_sum_u32(const uint64_t *peer_bases, int world, int rank, uint32_t n_cap, uint32_t n,
+                                uint32_t epoch, uint32_t *d_out, void *cuda_stream) {
+    if (!peer_bases || !d_out || world < 1 || world > kMaxPeers || rank < 0 || rank >= world || n > n_cap ||
+        epoch == 0)
+        return GFE_ERR_ARG;
+    PeerArgs a{};
+    for (int q = 0; q < world; ++q) a.base[q] = reinterpret_cast<uint32_t *>(peer_bases[q]);
+    a.world = world;
+    a.rank = rank;
+    a.n = n;
+    a.n_cap = n_cap;
+    a.epoch = epoch;
+    a.out = d_out;
+    unsigned blocks = (n + 2047) / 2048;
+    if (blocks < 1) blocks = 1;
+    if (blocks > 64) blocks = 64;
+    peer_sum_kernel<<<blocks, 512, 0, (cudaStream_t)cuda_stream>>>(a);
+    return cudaGetLastError() == cudaSuccess ? GFE_OK : GFE_ERR_CUDA;
+}

@@ -38,6 +38,45 @@ def take_shard(offsets: np.ndarray, steps: np.ndarray, lo: int, hi: int) -> Tupl
     return (o - o[0]).astype(np.uint32), np.ascontiguousarray(steps[int(o[0]):int(o[-1])], dtype=np.uint32)
 
 
+class PeerExchange:
+    """The exchange step over NVLink peer memory: a symmetric buffer (torch symmetric memory, one per
+    rank, mapped into every process of the box) holds two halves of n_cap count slots plus the
+    epoch flags; `half_ptr()` is where this rank's kernels accumulate the next batch's records and
+    `sum_into(out, n, stream)` launches gfe_peer_sum_u32 (csrc/peer.cu) behind them.  Every rank
+    must call both in the same order (they do: the search is replayed in lock step)."""
+
+    def __init__(self, n_cap: int, device, group=None):
+        import torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        self.torch = torch
+        self.n_cap = int(n_cap)
+        group = group if group is not None else dist.group.WORLD
+        words = 2 * self.n_cap + capi.PEER_MAX
+        self.buf = symm_mem.empty(words, dtype=torch.int32, device=device)
+        self.buf.zero_()
+        self.hdl = symm_mem.rendezvous(self.buf, group)
+        self.rank, self.world = int(self.hdl.rank), int(self.hdl.world_size)
+        if self.world > capi.PEER_MAX:
+            raise ValueError(f"PeerExchange: at most {capi.PEER_MAX} ranks")
+        self.bases = [int(p) for p in self.hdl.buffer_ptrs]
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)          # every rank's flags are zero before the first epoch
+        self.epoch = 0
+
+    def half_ptr(self) -> int:
+        """Device address of the half the NEXT sum_into() reads on this rank."""
+        return self.bases[self.rank] + 4 * self.n_cap * ((self.epoch + 1) & 1)
+
+    def half_tensor(self, n: int):
+        o = self.n_cap * ((self.epoch + 1) & 1)
+        return self.buf[o:o + n]
+
+    def sum_into(self, out_ptr: int, n: int, stream: int = 0) -> None:
+        self.epoch += 1
+        capi.peer_sum_u32(self.bases, self.rank, self.n_cap, n, self.epoch, out_ptr, stream)
+
+
 class ShardedScorer:
     """scorer(path_offsets, path_steps) -> summed (P, 2) counts over all ranks of `group`.
 

@@ -139,6 +139,19 @@ int gfe_edge_traversals_device(gfe_engine *e, const uint32_t *edge_from, const u
 int gfe_edge_weights_from_counts(const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
                                  const uint32_t *counts /* 2*E, host */, uint32_t *weights);
 
+/* ---- sharded alignments: the one exchange step ----------------------------------------------------
+ * The reference has no multi-process mode; this is the exchange SURVEY.md 8(e) adds for alignment
+ * shards (the sum the single evaluatePath loop of src/eval.cpp:14-28 forms in one address space).
+ * Sums the n uint32 count slots of `world` ranks (one process per GPU of a box) by reading every
+ * peer's record over NVLink peer memory, one small kernel per rank, stream-ordered.
+ * peer_bases[q] = rank q's exchange buffer as mapped into THIS process (e.g. torch symmetric memory
+ * buffer_ptrs), laid out as  u32 data[2][n_cap]; u32 flags[GFE_PEER_MAX]  and zero-filled once
+ * before the first call.  Epoch e = 1, 2, ... (the same on every rank): the caller has this rank's
+ * records written to data[e & 1] by earlier work on `cuda_stream`; d_out receives the sums. */
+#define GFE_PEER_MAX 16
+int gfe_peer_sum_u32(const uint64_t *peer_bases, int world, int rank, uint32_t n_cap, uint32_t n,
+                     uint32_t epoch, uint32_t *d_out, void *cuda_stream);
+
 /* ---- best-first search driver -------------------------------------------------------------------
  * Replaces dijkstra() (reference src/eval.cpp:110-193) on packed inputs: the bidirected adjacency
  * of InSequences::buildEdgeGraph (reference gfalibs/src/gfa.cpp:1076-1097) as CSR over nodes

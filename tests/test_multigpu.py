@@ -43,3 +43,18 @@ def test_two_gpu_search_and_evalgfa_match_reference(tmp_path):
             assert out == c["out_text"], c["name"]
         seen += 1
     assert seen == 5
+
+
+def test_peer_exchange_matches_nccl():
+    """gfe_peer_sum_u32 (NVLink peer-memory sum of the count records) == NCCL all-reduce."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    n = min(torch.cuda.device_count(), 8)
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+           "--master-addr", "127.0.0.1", "--master-port", "29650",
+           os.path.join(ROOT, "tests", "peer_exchange_worker.py")]
+    p = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-3000:]
+    assert "mismatching epochs 0" in p.stderr
