@@ -410,7 +410,7 @@ static uint32_t pick_chunk(const gfe_engine *e, uint32_t P) {
 // d_raw_steps != nullptr: d_pstep is the engine's scratch the prologue fills from the raw steps.
 static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *d_pstep, uint32_t P,
                          uint32_t total_steps, int filter, uint32_t *d_counts, uint32_t *d_work_count,
-                         const uint32_t *d_raw_steps, cudaStream_t st) {
+                         const uint32_t *d_raw_steps, uint32_t *d_bad_step, cudaStream_t st) {
     TRY(ensure_dev(e, e->d_ptab, (size_t)P * e->tab_stride));
     TRY(ensure_dev(e, e->d_pnext, (size_t)total_steps + 8));
     // exact-DP worklist: sized for 1 ambiguous pair in 128 checks (cfg3 measures ~1 in 2500)
@@ -435,7 +435,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     pro.L = e->L;
     pro.out = const_cast<uint16_t *>(d_pstep);
     pro.total = total_steps;
-    pro.err = e->d_err.ptr;
+    pro.err = d_bad_step;
     ScoreArgs a;
     a.bk = e->bk;
     a.poff = d_poff;
@@ -588,40 +588,54 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
         }
     }
     CUDA_TRY(e, cudaSetDevice(e->device));
-    // staging: [P+1 offsets u32][total local steps u16]
+    // staging: [P+1 offsets u32][total raw steps u32]; the batch prologue maps them to universe-local
+    // 16-bit steps on the device (a step outside the universe raises the flag word read back below)
     const size_t off_bytes = ((size_t)(P + 1) * 4 + 15) & ~(size_t)15;
-    const size_t bytes = off_bytes + (size_t)total * 2;
+    const size_t bytes = off_bytes + (size_t)total * 4;
+    // result block: [8 work counters][bad-step flag][pad to 16 words][P x {bad, good}]: ONE device->host
+    // copy per batch.  The flag word is zero between calls (cleared on allocation and after an error).
+    constexpr size_t kHdr = 16;
+    static_assert(kWorkCounters + 1 <= kHdr, "result header");
     TRY(ensure_pinned(e, e->h_stage, bytes));
     TRY(ensure_dev(e, e->d_stage, bytes));
-    // the work counters ride behind the count records: one device->host copy per batch
-    TRY(ensure_pinned(e, e->h_counts, (size_t)P * 2 + kWorkCounters));
-    TRY(ensure_dev(e, e->d_counts, (size_t)P * 2 + kWorkCounters));
-    memcpy(e->h_stage.ptr, path_offsets, (size_t)(P + 1) * 4);
-    uint16_t *ls = reinterpret_cast<uint16_t *>(e->h_stage.ptr + off_bytes);
-    for (uint32_t i = 0; i < total; ++i) {
-        const uint32_t node = path_steps[i] >> 1;
-        const uint32_t l = node < e->n_nodes ? e->node2local[node] : e->L;
-        if (l >= e->L) {
-            set_error(e, "gfe_score_paths: step %u names node %u outside the universe", i, node);
-            return GFE_ERR_ARG;
-        }
-        ls[i] = (uint16_t)((l << 1) | (path_steps[i] & 1u));
+    TRY(ensure_dev(e, e->d_plocal, (size_t)total + 8));
+    TRY(ensure_pinned(e, e->h_counts, (size_t)P * 2 + kHdr));
+    {
+        const uint32_t *before = e->d_counts.ptr;
+        TRY(ensure_dev(e, e->d_counts, (size_t)P * 2 + kHdr));
+        if (e->d_counts.ptr != before)
+            CUDA_TRY(e, cudaMemsetAsync(e->d_counts.ptr, 0, kHdr * sizeof(uint32_t), e->stream));
     }
+    memcpy(e->h_stage.ptr, path_offsets, (size_t)(P + 1) * 4);
+    memcpy(e->h_stage.ptr + off_bytes, path_steps, (size_t)total * 4);
     CUDA_TRY(e, cudaMemcpyAsync(e->d_stage.ptr, e->h_stage.ptr, bytes, cudaMemcpyHostToDevice,
                                 e->stream));
     const uint32_t *d_poff = reinterpret_cast<const uint32_t *>(e->d_stage.ptr);
-    const uint16_t *d_pstep = reinterpret_cast<const uint16_t *>(e->d_stage.ptr + off_bytes);
-    TRY(enqueue_score(e, d_poff, d_pstep, P, total, filter, e->d_counts.ptr,
-                      e->d_counts.ptr + (size_t)P * 2, nullptr, e->stream));
-    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr,
-                                ((size_t)P * 2 + kWorkCounters) * sizeof(uint32_t), cudaMemcpyDeviceToHost,
-                                e->stream));
+    const uint32_t *d_raw = reinterpret_cast<const uint32_t *>(e->d_stage.ptr + off_bytes);
+    uint32_t *d_hdr = e->d_counts.ptr, *d_cnt = e->d_counts.ptr + kHdr;
+    TRY(enqueue_score(e, d_poff, e->d_plocal.ptr, P, total, filter, d_cnt, d_hdr, d_raw, d_hdr + kWorkCounters,
+                      e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, ((size_t)P * 2 + kHdr) * sizeof(uint32_t),
+                                cudaMemcpyDeviceToHost, e->stream));
     uint32_t wc[kWorkCounters] = {};
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-    for (int i = 0; i < kWorkCounters; ++i) wc[i] = e->h_counts.ptr[(size_t)P * 2 + i];
+    for (int i = 0; i < kWorkCounters; ++i) wc[i] = e->h_counts.ptr[i];
     if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
     e->h2d_bytes += bytes;
-    e->d2h_bytes += ((size_t)P * 2 + kWorkCounters) * sizeof(uint32_t);
+    e->d2h_bytes += ((size_t)P * 2 + kHdr) * sizeof(uint32_t);
+    if (e->h_counts.ptr[kWorkCounters]) {
+        // a step outside the universe: name it the way the host check did, and clear the flag
+        CUDA_TRY(e, cudaMemset(e->d_counts.ptr + kWorkCounters, 0, sizeof(uint32_t)));
+        for (uint32_t i = 0; i < total; ++i) {
+            const uint32_t node = path_steps[i] >> 1;
+            if (node >= e->n_nodes || e->node2local[node] >= e->L) {
+                set_error(e, "gfe_score_paths: step %u names node %u outside the universe", i, node);
+                return GFE_ERR_ARG;
+            }
+        }
+        set_error(e, "gfe_score_paths: a step names a node outside the universe");
+        return GFE_ERR_ARG;
+    }
     if (wc[3]) {
         // the list of pairs the bitsets could not settle overflowed: grow it, or halve the batch
         if (e->d_slow.cap < (1ull << 28)) {
@@ -649,7 +663,7 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
     }
     e->exact_pairs += wc[0];
     e->slow_pairs += wc[2] - wc[4];   // reserved slots minus the holes
-    memcpy(counts, e->h_counts.ptr, (size_t)P * 2 * sizeof(uint32_t));
+    memcpy(counts, e->h_counts.ptr + 16, (size_t)P * 2 * sizeof(uint32_t));
     return GFE_OK;
 }
 
@@ -671,7 +685,7 @@ int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
     }
     TRY(ensure_dev(e, e->d_work_count, kWorkCounters));
     return enqueue_score(e, d_path_offsets, e->d_plocal.ptr, P, total_path_steps, filter, d_counts,
-                         e->d_work_count.ptr, d_path_steps, st);
+                         e->d_work_count.ptr, d_path_steps, e->d_err.ptr, st);
 }
 
 // ---- evalPath scoring ---------------------------------------------------------------------------
