@@ -782,23 +782,68 @@ slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
     }
 }
 
-// K1b: exact verdict for the worklist of ambiguous (path, alignment) pairs.
+// K1b: exact verdict for the worklist of ambiguous (path, alignment) pairs.  One thread runs one
+// pair's DP, so a warp costs its longest pair in every register tier its lanes touch.  The list
+// arrives in arbitrary order; each CTA therefore takes a tile of kExactTile pairs, counting-sorts
+// it in shared memory by (register tier of m, n / 32) and hands consecutive sorted pairs to
+// consecutive lanes: the lanes of a warp then run the same tier on paths of similar length.
+constexpr int kExactTile = 256;
+constexpr int kExactBins = 32;          // tier (0..2) * 8 + min(n / 32, 7); bin 31 = not for this kernel
+
 __global__ void __launch_bounds__(128)
 exact_worklist_kernel(const ScoreArgs a) {
+    __shared__ uint2 s_item[kExactTile];
+    __shared__ uint32_t s_hist[kExactBins], s_base[kExactBins + 1];
     pdl_wait();      // the second-look kernel's worklist
     const uint32_t cnt = min(*reinterpret_cast<const volatile uint32_t *>(a.work_count), a.work_cap);
-    for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < cnt;
-         idx += gridDim.x * blockDim.x) {
-        const uint2 w = a.work[idx];
-        const RowRef r = locate_row(a.bk, w.y);
-        const int m = (int)r.m;
-        if (m > kExactRegSteps) continue;   // long alignments: exact_worklist_long_kernel
-        const uint32_t po = a.poff[w.x];
-        const int n = (int)(a.poff[w.x + 1] - po);
-        int tf, tr;
-        exact_both(a.pstep + po, n, r.ptr, m, false, &tf, &tr);
-        const bool good = (tf == 0) || (tr == 0);
-        atomicAdd(&a.counts[2 * (size_t)w.x + (good ? 1 : 0)], 1u);
+    for (uint32_t tile0 = blockIdx.x * kExactTile; tile0 < cnt; tile0 += gridDim.x * kExactTile) {
+        if (threadIdx.x < kExactBins) s_hist[threadIdx.x] = 0;
+        __syncthreads();
+        uint2 w[kExactTile / 128];
+        uint32_t bin[kExactTile / 128], pos[kExactTile / 128];
+#pragma unroll
+        for (int k = 0; k < kExactTile / 128; ++k) {
+            const uint32_t idx = tile0 + k * 128 + threadIdx.x;
+            bin[k] = kExactBins;                      // nothing loaded
+            if (idx < cnt) {
+                w[k] = a.work[idx];
+                const uint32_t m = locate_row(a.bk, w[k].y).m;
+                const uint32_t n = a.poff[w[k].x + 1] - a.poff[w[k].x];
+                const uint32_t tier = m <= 8 ? 0u : (m <= 16 ? 1u : 2u);
+                // long alignments: exact_worklist_long_kernel
+                bin[k] = m > (uint32_t)kExactRegSteps ? (uint32_t)kExactBins - 1u : tier * 8u + min(n >> 5, 7u);
+                pos[k] = atomicAdd(&s_hist[bin[k]], 1u);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {                       // exclusive prefix over the bins
+            const uint32_t h = s_hist[threadIdx.x];
+            uint32_t incl = h;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                if ((int)threadIdx.x >= o) incl += t;
+            }
+            s_base[threadIdx.x] = incl - h;
+            if (threadIdx.x == 31) s_base[32] = incl;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < kExactTile / 128; ++k)
+            if (bin[k] < (uint32_t)kExactBins) s_item[s_base[bin[k]] + pos[k]] = w[k];
+        __syncthreads();
+        const uint32_t todo = s_base[kExactBins - 1];  // everything below the "not for this kernel" bin
+        for (uint32_t j = threadIdx.x; j < todo; j += blockDim.x) {
+            const uint2 it = s_item[j];
+            const RowRef r = locate_row(a.bk, it.y);
+            const uint32_t po = a.poff[it.x];
+            const int n = (int)(a.poff[it.x + 1] - po);
+            int tf, tr;
+            exact_both(a.pstep + po, n, r.ptr, (int)r.m, false, &tf, &tr);
+            const bool good = (tf == 0) || (tr == 0);
+            atomicAdd(&a.counts[2 * (size_t)it.x + (good ? 1 : 0)], 1u);
+        }
+        __syncthreads();
     }
 }
 
