@@ -79,7 +79,7 @@ EXPORTS = [
     "gfe_last_kernel_ms", "gfe_kernel_time_stats", "gfe_device_status",
     "gfe_trace_pairs", "gfe_filter_alignments",
     "gfe_text_open", "gfe_text_close", "gfe_text_get", "gfe_text_node_name", "gfe_text_node_id",
-    "gfe_text_qname", "gfe_peer_sum_u32",
+    "gfe_text_qname", "gfe_peer_sum_u32", "gfe_device_status_to",
 ]
 
 PEER_MAX = 16      # GFE_PEER_MAX
@@ -126,6 +126,7 @@ def load_library() -> C.CDLL:
     lib.gfe_edge_traversals_device.argtypes = [C.c_void_p, _u32p, _u32p, C.c_uint32, C.c_void_p,
                                                C.c_void_p]
     lib.gfe_edge_weights_from_counts.argtypes = [_u32p, _u32p, C.c_uint32, _u32p, _u32p]
+    lib.gfe_device_status_to.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.gfe_peer_sum_u32.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_int, C.c_uint32, C.c_uint32,
                                      C.c_uint32, C.c_void_p, C.c_void_p]
     lib.gfe_search.argtypes = [C.c_void_p, C.POINTER(_Graph), C.POINTER(_SearchParams), _ROW_FN,
@@ -340,6 +341,10 @@ class Engine:
         f = C.c_uint32()
         self._check(self._lib.gfe_device_status(self._h, C.byref(f)))
         return f.value
+
+    def device_status_to(self, d_flags: int, stream: int = 0):
+        """device_status() written to the device word at d_flags, stream-ordered, no synchronisation."""
+        self._check(self._lib.gfe_device_status_to(self._h, C.c_void_p(d_flags), C.c_void_p(stream)))
 
     def kernel_time_stats(self):
         """(total ms, launches) of the dominant kernel since the previous call; synchronises."""

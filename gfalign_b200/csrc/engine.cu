@@ -179,6 +179,15 @@ int gfe_device_status(gfe_engine *e, uint32_t *flags) {
     return GFE_OK;
 }
 
+int gfe_device_status_to(gfe_engine *e, uint32_t *d_flags, void *cuda_stream) {
+    if (!e || !d_flags) return GFE_ERR_ARG;
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    launch_status_flag(e->d_err.ptr, e->d_work_count.ptr, d_flags, (cudaStream_t)cuda_stream);
+    e->kernel_launches += 1;
+    CUDA_TRY(e, cudaGetLastError());
+    return GFE_OK;
+}
+
 int gfe_get_counters(const gfe_engine *e, gfe_counters *out) {
     if (!e || !out) return GFE_ERR_ARG;
     out->kernel_launches = e->kernel_launches;

@@ -1040,6 +1040,14 @@ void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uin
                                                                ldesc, perm, cursors, pd, n_pairs, pair_bias);
 }
 
+__global__ void status_flag_kernel(const uint32_t *err, const uint32_t *wc, uint32_t *out) {
+    *out = ((err && *err) ? 1u : 0u) | ((wc && (wc[1] || wc[3])) ? 2u : 0u);
+}
+
+void launch_status_flag(const uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st) {
+    status_flag_kernel<<<1, 1, 0, st>>>(err, wc, out);
+}
+
 void launch_prologue(const PrologueArgs &a, int sm_count, cudaStream_t st) {
     uint64_t most = a.psteps ? a.total : 0;
     for (int r = 0; r < 4; ++r) most = std::max<uint64_t>(most, a.zero_words[r] / 4 + 1);

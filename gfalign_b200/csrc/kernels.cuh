@@ -250,6 +250,8 @@ struct PrologueArgs {
     uint32_t *err;
 };
 void launch_prologue(const PrologueArgs &a, int sm_count, cudaStream_t st);
+// *out = bit0 a path step outside the universe, bit1 a worklist overflowed (gfe_device_status, on the device)
+void launch_status_flag(const uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st);
 // masks == nullptr: tables only (legacy kernel); else also ORs path p into the batch's bitsets
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
                          uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, uint32_t *masks,

@@ -116,6 +116,12 @@ def main(argv=None):
 
         if world > 1:
             scorer = sharded.ShardedScorer(local_score, device=device)
+            if os.environ.get("GFE_EXCHANGE", "peer") == "peer":
+                try:      # counts stay on the device, summed by the peer-memory kernel (csrc/peer.cu)
+                    px = sharded.PeerExchange(2 * 4096, device)
+                    scorer = sharded.PeerShardedScorer(eng, px, device, filter=True, fallback=scorer)
+                except Exception as ex:
+                    sys.stderr.write(f"[multigpu] peer exchange unavailable ({ex!r}); using NCCL\n")
         else:
             scorer = local_score
         out = sys.stdout
@@ -129,6 +135,9 @@ def main(argv=None):
                                               src, dst, nodes, counts, node_count, max_steps=a.max_steps,
                                               min_nodes=a.min_nodes, return_all_paths=a.return_all_paths,
                                               speculate=a.speculate, on_row=on_row)
+        if rank == 0 and os.environ.get("GFE_DEBUG_TIMING"):
+            sys.stderr.write(f"[multigpu] scorer {type(scorer).__name__}, {getattr(scorer, 'calls', 0)} exchanges, "
+                             f"{stats['kernel_batches']} batches, scoring {stats['seconds_scoring']:.3f} s\n")
         if rank == 0 and stats["extractions"] >= a.max_steps:
             out.write(f"Reached maximum number of steps ({stats['extractions']})\n")
     else:

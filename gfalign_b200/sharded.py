@@ -99,6 +99,45 @@ class ShardedScorer:
         return t.cpu().numpy().astype(np.uint32)
 
 
+class PeerShardedScorer:
+    """The same contract as ShardedScorer for GPU ranks of one box, with the counts kept on the device:
+    the batch goes host -> device once, `Engine.score_paths_device` accumulates this rank's records
+    into the exchange buffer, the peer-memory kernel sums all shards, and only the summed P x 2 record
+    comes back (no NCCL call, no extra device<->host hop).  Batches above `n_cap / 2` paths fall back
+    to `fallback` (a ShardedScorer)."""
+
+    def __init__(self, engine, exchange: PeerExchange, device, filter: bool = True, fallback=None):
+        import torch
+        self.torch, self.engine, self.px, self.device = torch, engine, exchange, device
+        self.filter, self.fallback = filter, fallback
+        self.out = torch.zeros(exchange.n_cap, dtype=torch.int32, device=device)
+        self.calls = 0
+
+    def __call__(self, path_offsets: np.ndarray, path_steps: np.ndarray) -> np.ndarray:
+        torch = self.torch
+        P = int(path_offsets.size) - 1
+        if 2 * P + 1 > self.px.n_cap:
+            if self.fallback is None:
+                raise ValueError(f"batch of {P} paths exceeds the exchange buffer")
+            return self.fallback(path_offsets, path_steps)
+        d_po = torch.from_numpy(np.ascontiguousarray(path_offsets, dtype=np.uint32).view(np.int32)).to(self.device)
+        d_ps = torch.from_numpy(np.ascontiguousarray(path_steps, dtype=np.uint32).view(np.int32)).to(self.device)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        self.engine.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), P, int(path_steps.size),
+                                       self.px.half_ptr(), filter=self.filter, stream=stream)
+        # slot 2P of the record = this rank's status flags: the sum tells every rank alike whether
+        # any shard overflowed a worklist (or saw a bad step), and all repeat the batch the slow way
+        self.engine.device_status_to(self.px.half_ptr() + 8 * P, stream)
+        self.px.sum_into(self.out.data_ptr(), 2 * P + 1, stream)
+        self.calls += 1
+        rec = self.out[:2 * P + 1].cpu().numpy().view(np.uint32)
+        if rec[2 * P]:
+            if self.fallback is None:
+                raise RuntimeError("a shard reported a worklist overflow or a step outside the universe")
+            return self.fallback(path_offsets, path_steps)
+        return rec[:2 * P].reshape(P, 2).copy()
+
+
 def sharded_search(scorer: ShardedScorer, tangle, nodes, counts, node_count, **kw):
     """`gfalign search` over sharded alignments: identical rows on every rank."""
     return capi.search_with_scorer(scorer, tangle.adj_offsets, tangle.adj_target, tangle.adj_or0,

@@ -247,6 +247,10 @@ int gfe_get_counters(const gfe_engine *e, gfe_counters *out);
  * bit1: the exact-DP worklist overflowed (results of that batch are incomplete; re-run it through
  * gfe_score_paths, which grows the list and retries by itself). */
 int gfe_device_status(gfe_engine *e, uint32_t *flags);
+/* The same flags written to a device word, stream-ordered behind the *_device calls on `cuda_stream`
+ * (no synchronisation): sharded callers add the word to the exchanged record so that every rank
+ * learns of any rank's overflow and repeats the batch through the host call together. */
+int gfe_device_status_to(gfe_engine *e, uint32_t *d_flags, void *cuda_stream);
 /* Milliseconds the last scoring / edge-support call spent in its dominant kernel (CUDA events on
  * the engine's stream); 0 if timing was not enabled with gfe_set_timing(e, 1). */
 int gfe_set_timing(gfe_engine *e, int enabled);
