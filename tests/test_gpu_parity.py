@@ -339,3 +339,51 @@ def test_filter_alignments(engine):
         want = np.array([bool(inset[st[off[a]:off[a + 1]] >> 1].all()) and (off[a + 1] - off[a]) >= mn
                          for a in range(5000)])
         assert np.array_equal(keep, want), (nodes.size, mn)
+
+
+# ---- sharded-path plumbing that also runs on one GPU ----------------------------------------------
+
+def test_peer_sum_single_rank_is_identity_and_epochs_alternate_halves():
+    """gfe_peer_sum_u32 with world = 1: the rank publishes to and reads from its own buffer; both
+    halves and growing epochs; n < n_cap leaves the rest of `out` untouched."""
+    import torch
+    from gfalign_b200 import capi
+    dev = torch.device("cuda", 0)
+    n_cap = 3000
+    buf = torch.zeros(2 * n_cap + capi.PEER_MAX, dtype=torch.int32, device=dev)
+    out = torch.full((n_cap,), -1, dtype=torch.int32, device=dev)
+    g = torch.Generator().manual_seed(5)
+    for epoch in range(1, 8):
+        n = [1, 2, 2047, 2048, 2049, 3000, 17][epoch - 1]
+        rec = torch.randint(0, 1 << 30, (n,), generator=g, dtype=torch.int32).to(dev)
+        half = n_cap * (epoch & 1)
+        buf[half:half + n].copy_(rec)
+        out.fill_(-1)
+        capi.peer_sum_u32([buf.data_ptr()], 0, n_cap, n, epoch, out.data_ptr(),
+                          torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        assert torch.equal(out[:n], rec), epoch
+        assert bool((out[n:] == -1).all()), epoch
+        assert int(buf[2 * n_cap].item()) == epoch
+    with pytest.raises(capi.GfeError):
+        capi.peer_sum_u32([buf.data_ptr()], 0, n_cap, n_cap + 1, 9, out.data_ptr())
+
+
+def test_device_status_word_matches_host_status(engine):
+    import torch
+    w = synth.make_workload("cfg3", A=5000)
+    t = w.tangle
+    nodes, _, _ = synth.node_table(t)
+    po, ps = synth.candidate_paths(t, 8, seed=1)
+    engine.set_alignments(w.offsets, w.steps, t.n_nodes)
+    engine.set_universe(nodes[:max(2, len(nodes) // 2)])       # half the universe: some steps fall outside
+    dev = torch.device("cuda", 0)
+    d_po = torch.from_numpy(po.astype(np.int64)).to(dev).to(torch.int32)
+    d_ps = torch.from_numpy(ps.astype(np.int64)).to(dev).to(torch.int32)
+    d_counts = torch.zeros(2 * 8, dtype=torch.int32, device=dev)
+    flag = torch.full((1,), 77, dtype=torch.int32, device=dev)
+    engine.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), 8, int(ps.size), d_counts.data_ptr(), filter=True)
+    engine.device_status_to(flag.data_ptr())
+    torch.cuda.synchronize()
+    assert int(flag.item()) == engine.device_status()
+    assert int(flag.item()) & 1          # a step outside the universe was seen
