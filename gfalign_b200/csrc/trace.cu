@@ -132,22 +132,34 @@ __global__ void trace_bases_kernel(const uint32_t *off, uint64_t first, uint32_t
     if (k < count) base[k] = (uint64_t)(off[first + k] - off[first]) + (uint64_t)k * n;
 }
 
-// pass 1, flat over the step array: one step per thread and iteration, the warp's ballot is the
-// word of the "outside the set" bitmap for its 32 consecutive steps
+// pass 1, flat over the step array: four steps (one 128-bit load) per lane and iteration, so a warp
+// covers 128 steps = four words of the "outside the set" bitmap; the lanes' 4-bit results are OR-ed
+// over groups of eight lanes with three shuffles and lanes 0, 8, 16, 24 store the words.
 __global__ void __launch_bounds__(256) filter_mark_kernel(FilterArgs a) {
-    const uint64_t n_words = (a.S + 31) / 32;
+    const uint64_t n_groups = (a.S + 127) / 128;                  // 128 steps per warp iteration
     const uint64_t warp = (blockIdx.x * (uint64_t)blockDim.x + threadIdx.x) >> 5;
     const uint64_t n_warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
     const uint32_t lane = threadIdx.x & 31;
-    for (uint64_t w = warp; w < n_words; w += n_warps) {
-        const uint64_t s = w * 32 + lane;
-        bool bad = false;
-        if (s < a.S) {
-            const uint32_t node = __ldg(a.steps + s) >> 1;
-            bad = !(node < a.n_nodes && ((__ldg(a.node_bits + (node >> 5)) >> (node & 31)) & 1u));
+    auto outside = [&](uint32_t step) -> uint32_t {
+        const uint32_t node = step >> 1;
+        return (node < a.n_nodes && ((__ldg(a.node_bits + (node >> 5)) >> (node & 31)) & 1u)) ? 0u : 1u;
+    };
+    const bool vec = (reinterpret_cast<uintptr_t>(a.steps) & 15u) == 0;   // caller-owned device arrays may not be
+    for (uint64_t g = warp; g < n_groups; g += n_warps) {
+        const uint64_t s = g * 128 + 4ull * lane;
+        uint32_t nib = 0;
+        if (vec && s + 4 <= a.S) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4 *>(a.steps + s));
+            nib = outside(v.x) | (outside(v.y) << 1) | (outside(v.z) << 2) | (outside(v.w) << 3);
+        } else {
+            for (uint32_t k = 0; k < 4 && s + k < a.S; ++k) nib |= outside(__ldg(a.steps + s + k)) << k;
         }
-        const uint32_t word = __ballot_sync(0xFFFFFFFFu, bad);
-        if (lane == 0) a.bad_bits[w] = word;
+        uint32_t word = nib << (4u * (lane & 7u));
+        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 1);
+        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 2);
+        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 4);
+        const uint64_t w = g * 4 + (lane >> 3);
+        if ((lane & 7u) == 0 && w * 32 < a.S) a.bad_bits[w] = word;
     }
 }
 
@@ -192,9 +204,9 @@ void launch_pair_trace(const TraceArgs &a, cudaStream_t st) {
 
 void launch_filter_rows(const FilterArgs &a, int sm_count, cudaStream_t st) {
     if (!a.A) return;
-    const uint64_t n_words = (a.S + 31) / 32;
-    if (n_words) {
-        uint64_t blocks = (n_words + 7) / 8;           // 8 warps per CTA
+    const uint64_t n_groups = (a.S + 127) / 128;
+    if (n_groups) {
+        uint64_t blocks = (n_groups + 7) / 8;          // 8 warps per CTA
         const uint64_t cap = (uint64_t)sm_count * 32;
         if (blocks > cap) blocks = cap;
         filter_mark_kernel<<<(unsigned)blocks, 256, 0, st>>>(a);
