@@ -348,8 +348,8 @@ def main():
     # dram__bytes_read+write of ONE launch from the committed ncu --set full capture of this command
     # (profiles/r01_score_bitset_ncu_full_summary.csv; cfg3, P = 1024): 20.41 MB read
     traffic = 20.41e6 if (args.workload == "cfg3" and P == 1024 and A == 1_000_000 and not legacy) else None
-    # the limiter of the bitset kernel is the SM (issue slots + shared-memory reads), not HBM:
-    # warp instructions per launch from the same capture (1.1-1.5e8) vs 4 issue slots/clk/SM
+    # the limiter of the bitset kernel is the SM (integer ALU pipe 70 % busy, issue slots 61 %), not HBM:
+    # warp instructions per launch from the same capture (1.1e8) vs 4 issue slots/clk/SM
     sm_clock = 1.965e9
     roofline = {"bound": "hbm", "kernel": "score_paths_kernel" if legacy else "score_bitset_kernel",
                 "achieved": achieved, "peak": peak,
@@ -358,7 +358,7 @@ def main():
                 "algorithmic_bytes_per_launch": alg_bytes,
                 "note": "algorithmic bytes = P x A x 4(m+1) (SURVEY.md 8d); one pass over the table "
                         "serves every path of a chunk from shared-memory bitsets, so DRAM traffic "
-                        "is ~1/1000 of it and frac > 1; the kernel is issue/shared-memory bound "
+                        "is ~1/1000 of it and frac > 1; the kernel is integer-ALU/issue bound "
                         "(DESIGN.md 4)",
                 "issue_bound": {"checks_per_sm_clock": float(P) * A / (k1_ms * 1e-3) / (eng_sms * sm_clock),
                                 "sms": eng_sms, "sm_clock_hz": sm_clock}}
