@@ -509,12 +509,6 @@ score_bitset_kernel(const BitsetArgs a) {
 
 template <int W>
 void launch_w(const BitsetArgs &a, int sm_count, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        cudaFuncSetAttribute(score_bitset_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)(kBitsetSmemBudget + 1024));
-        configured = true;
-    }
     const size_t smem = (size_t)a.mg.entries * W * 4 + 64 * W * 4 + 16;
     const uint32_t chunks = (a.P + 32 * W - 1) / (32 * W);
     uint32_t gx = (uint32_t)sm_count / chunks;
@@ -525,7 +519,25 @@ void launch_w(const BitsetArgs &a, int sm_count, cudaStream_t st) {
     launch_pdl(1, score_bitset_kernel<W>, dim3(gx, chunks), dim3(kBitThreads), smem, st, a);
 }
 
+template <int W>
+cudaError_t configure_w() {
+    return cudaFuncSetAttribute(score_bitset_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(kBitsetSmemBudget + 1024));
+}
+
 }  // namespace
+
+// cudaFuncSetAttribute applies to the CURRENT device: called from configure_kernels(), i.e. once per
+// gfe_create, so every engine's device gets the large-shared-memory opt-in
+int configure_bitset_kernels() {
+    cudaError_t e;
+    if ((e = configure_w<1>()) != cudaSuccess) return (int)e;
+    if ((e = configure_w<2>()) != cudaSuccess) return (int)e;
+    if ((e = configure_w<4>()) != cudaSuccess) return (int)e;
+    if ((e = configure_w<8>()) != cudaSuccess) return (int)e;
+    if ((e = configure_w<16>()) != cudaSuccess) return (int)e;
+    return (int)configure_w<32>();
+}
 
 void launch_score_bitset(const BitsetArgs &a, int sm_count, cudaStream_t st) {
     if (a.P == 0) return;

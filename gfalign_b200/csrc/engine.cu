@@ -170,12 +170,16 @@ int gfe_device_status(gfe_engine *e, uint32_t *flags) {
     if (!e || !flags) return GFE_ERR_ARG;
     CUDA_TRY(e, cudaSetDevice(e->device));
     CUDA_TRY(e, cudaDeviceSynchronize());
-    uint32_t err = 0, wc[4] = {0, 0, 0, 0};
-    if (e->d_err.ptr)
-        CUDA_TRY(e, cudaMemcpy(&err, e->d_err.ptr, sizeof(err), cudaMemcpyDeviceToHost));
+    uint32_t err[2] = {0, 0}, wc[4] = {0, 0, 0, 0};
+    if (e->d_err.ptr) {
+        CUDA_TRY(e, cudaMemcpy(err, e->d_err.ptr, sizeof(err), cudaMemcpyDeviceToHost));
+        CUDA_TRY(e, cudaMemset(e->d_err.ptr, 0, sizeof(err)));   // reported once
+    }
     if (e->d_work_count.ptr)
         CUDA_TRY(e, cudaMemcpy(wc, e->d_work_count.ptr, sizeof(wc), cudaMemcpyDeviceToHost));
-    *flags = (err ? 1u : 0u) | ((wc[1] || wc[3]) ? 2u : 0u);
+    // err[1]: overflow bits of every batch since the last report (the prologue of the next batch
+    // folds them in before it clears the counters); wc: the batch still in the counters
+    *flags = (err[0] ? 1u : 0u) | ((wc[1] || wc[3] || err[1]) ? 2u : 0u);
     return GFE_OK;
 }
 
@@ -419,7 +423,8 @@ static uint32_t pick_chunk(const gfe_engine *e, uint32_t P) {
 // d_raw_steps != nullptr: d_pstep is the engine's scratch the prologue fills from the raw steps.
 static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *d_pstep, uint32_t P,
                          uint32_t total_steps, int filter, uint32_t *d_counts, uint32_t *d_work_count,
-                         const uint32_t *d_raw_steps, uint32_t *d_bad_step, cudaStream_t st) {
+                         const uint32_t *d_raw_steps, uint32_t *d_bad_step, uint32_t *d_sticky,
+                         cudaStream_t st) {
     TRY(ensure_dev(e, e->d_ptab, (size_t)P * e->tab_stride));
     TRY(ensure_dev(e, e->d_pnext, (size_t)total_steps + 8));
     // exact-DP worklist: sized for 1 ambiguous pair in 128 checks (cfg3 measures ~1 in 2500)
@@ -445,6 +450,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     pro.out = const_cast<uint16_t *>(d_pstep);
     pro.total = total_steps;
     pro.err = d_bad_step;
+    pro.sticky = d_sticky;
     ScoreArgs a;
     a.bk = e->bk;
     a.poff = d_poff;
@@ -623,7 +629,7 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
     const uint32_t *d_raw = reinterpret_cast<const uint32_t *>(e->d_stage.ptr + off_bytes);
     uint32_t *d_hdr = e->d_counts.ptr, *d_cnt = e->d_counts.ptr + kHdr;
     TRY(enqueue_score(e, d_poff, e->d_plocal.ptr, P, total, filter, d_cnt, d_hdr, d_raw, d_hdr + kWorkCounters,
-                      e->stream));
+                      nullptr, e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, ((size_t)P * 2 + kHdr) * sizeof(uint32_t),
                                 cudaMemcpyDeviceToHost, e->stream));
     uint32_t wc[kWorkCounters] = {};
@@ -692,9 +698,14 @@ int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
         TRY(ensure_dev(e, e->d_err, 4));
         CUDA_TRY(e, cudaMemsetAsync(e->d_err.ptr, 0, 4 * sizeof(uint32_t), st));
     }
-    TRY(ensure_dev(e, e->d_work_count, kWorkCounters));
+    if (!e->d_work_count.ptr) {
+        // zero-filled on allocation: the prologue folds the previous batch's overflow flags into the
+        // sticky word before it clears the counters
+        TRY(ensure_dev(e, e->d_work_count, kWorkCounters));
+        CUDA_TRY(e, cudaMemsetAsync(e->d_work_count.ptr, 0, kWorkCounters * sizeof(uint32_t), st));
+    }
     return enqueue_score(e, d_path_offsets, e->d_plocal.ptr, P, total_path_steps, filter, d_counts,
-                         e->d_work_count.ptr, d_path_steps, e->d_err.ptr, st);
+                         e->d_work_count.ptr, d_path_steps, e->d_err.ptr, e->d_err.ptr + 1, st);
 }
 
 // ---- evalPath scoring ---------------------------------------------------------------------------

@@ -172,6 +172,13 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
 // outside the universe raises *err.
 __global__ void __launch_bounds__(256) prologue_kernel(PrologueArgs a) {
     const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, nthr = gridDim.x * blockDim.x;
+    if (a.sticky && blockIdx.x == 0) {
+        // the overflow flags of the previous batch survive its counters (words 1 and 3 are cleared
+        // by threads of block 0 below)
+        if (threadIdx.x == 0 && a.zero[1] && a.zero_words[1] > 3 && (a.zero[1][1] | a.zero[1][3]))
+            atomicOr(a.sticky, 2u);
+        __syncthreads();
+    }
 #pragma unroll
     for (int r = 0; r < 4; ++r) {
         uint32_t *z = a.zero[r];
@@ -1006,6 +1013,8 @@ int configure_kernels() {
     e = cudaFuncSetAttribute(pair_classify_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)kMaxDynSmem);
     if (e != cudaSuccess) return (int)e;
+    const int rc = configure_bitset_kernels();
+    if (rc != 0) return rc;
     return configure_edge_kernels();
 }
 
@@ -1040,11 +1049,12 @@ void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uin
                                                                ldesc, perm, cursors, pd, n_pairs, pair_bias);
 }
 
-__global__ void status_flag_kernel(const uint32_t *err, const uint32_t *wc, uint32_t *out) {
-    *out = ((err && *err) ? 1u : 0u) | ((wc && (wc[1] || wc[3])) ? 2u : 0u);
+__global__ void status_flag_kernel(uint32_t *err, const uint32_t *wc, uint32_t *out) {
+    *out = ((err && err[0]) ? 1u : 0u) | (((wc && (wc[1] || wc[3])) || (err && err[1])) ? 2u : 0u);
+    if (err) err[0] = err[1] = 0;   // reported: a later batch starts clean
 }
 
-void launch_status_flag(const uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st) {
+void launch_status_flag(uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st) {
     status_flag_kernel<<<1, 1, 0, st>>>(err, wc, out);
 }
 

@@ -248,10 +248,13 @@ struct PrologueArgs {
     uint16_t *out;
     uint32_t total;
     uint32_t *err;
+    uint32_t *sticky;         // may be null: the work counters' overflow flags (zero[1][1], [3]) of the PREVIOUS
+                              // batch are OR-ed in here (bit1) before they are cleared
 };
 void launch_prologue(const PrologueArgs &a, int sm_count, cudaStream_t st);
-// *out = bit0 a path step outside the universe, bit1 a worklist overflowed (gfe_device_status, on the device)
-void launch_status_flag(const uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st);
+// *out = bit0 a path step outside the universe, bit1 a worklist overflowed (gfe_device_status, on the
+// device); err[0] (bad step) and err[1] (sticky overflow of earlier batches) are cleared once reported
+void launch_status_flag(uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st);
 // masks == nullptr: tables only (legacy kernel); else also ORs path p into the batch's bitsets
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
                          uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, uint32_t *masks,
@@ -276,6 +279,7 @@ void launch_edge_scatter(const EdgeSlot *table, uint32_t cap, uint32_t *counts, 
 void launch_edge_weights(const uint32_t *d_ef, const uint32_t *d_et, uint32_t E, const EdgeSlot *table,
                          uint32_t cap, uint32_t *weights, cudaStream_t st);
 int configure_edge_kernels();
+int configure_bitset_kernels();
 void launch_max_len(const uint32_t *off, uint64_t first, uint32_t count, uint32_t *out,
                     cudaStream_t st);
 void launch_trace_bases(const uint32_t *off, uint64_t first, uint32_t count, uint32_t n,

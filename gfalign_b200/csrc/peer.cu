@@ -16,6 +16,7 @@
 // then it writes the OTHER half, so no second barrier is needed; flags only grow, hence ">=".
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/gfalign_b200.h"
 
@@ -28,7 +29,14 @@ struct PeerArgs {
     int world, rank;
     uint32_t n, n_cap, epoch;
     uint32_t *out;
+    unsigned long long timeout_ns;
 };
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
 
 __device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -50,16 +58,32 @@ __global__ void __launch_bounds__(512) peer_sum_kernel(PeerArgs a) {
         __threadfence_system();   // this rank's records (written by earlier kernels of the stream)
         st_release_sys(a.base[threadIdx.x] + flag0 + a.rank, a.epoch);
     }
+    // Lock-step is the caller's contract (every rank calls with the same epoch); a peer that never
+    // arrives (it raised, or skipped the batch) must not hang this GPU: the wait is bounded by
+    // a.timeout_ns of %globaltimer, after which every output slot is poisoned with GFE_PEER_TIMEOUT
+    // (no sum of real counts reaches it: counts are bounded by the number of alignments < 2^32 - 1).
+    __shared__ int s_timeout;
+    if (threadIdx.x == 0) s_timeout = 0;
+    __syncthreads();
     if (threadIdx.x < a.world) {
         const uint32_t *f = a.base[a.rank] + flag0 + threadIdx.x;
-        while ((int32_t)(ld_acquire_sys(f) - a.epoch) < 0) __nanosleep(20);
+        const unsigned long long t0 = global_ns();
+        while ((int32_t)(ld_acquire_sys(f) - a.epoch) < 0) {
+            __nanosleep(20);
+            if (global_ns() - t0 > a.timeout_ns) {
+                s_timeout = 1;
+                break;
+            }
+        }
     }
     __syncthreads();
+    const bool dead = s_timeout != 0;
     const size_t half = (size_t)(a.epoch & 1u) * a.n_cap;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += gridDim.x * blockDim.x) {
         uint32_t s = 0;
-        for (int q = 0; q < a.world; ++q) s += ld_relaxed_sys(a.base[q] + half + i);
-        a.out[i] = s;
+        if (!dead)
+            for (int q = 0; q < a.world; ++q) s += ld_relaxed_sys(a.base[q] + half + i);
+        a.out[i] = dead ? GFE_PEER_TIMEOUT : s;
     }
 }
 
@@ -78,6 +102,10 @@ extern "C" int gfe_peer_sum_u32(const uint64_t *peer_bases, int world, int rank,
     a.n_cap = n_cap;
     a.epoch = epoch;
     a.out = d_out;
+    {
+        static const long long ms = getenv("GFE_PEER_TIMEOUT_MS") ? atoll(getenv("GFE_PEER_TIMEOUT_MS")) : 20000;
+        a.timeout_ns = (unsigned long long)(ms > 0 ? ms : 20000) * 1000000ull;
+    }
     unsigned blocks = (n + 2047) / 2048;
     if (blocks < 1) blocks = 1;
     if (blocks > 64) blocks = 64;

@@ -131,6 +131,8 @@ class PeerShardedScorer:
         self.px.sum_into(self.out.data_ptr(), 2 * P + 1, stream)
         self.calls += 1
         rec = self.out[:2 * P + 1].cpu().numpy().view(np.uint32)
+        if rec[2 * P] == 0xFFFFFFFF:
+            raise RuntimeError("peer exchange timed out: a rank never reached this batch (GFE_PEER_TIMEOUT)")
         if rec[2 * P]:
             if self.fallback is None:
                 raise RuntimeError("a shard reported a worklist overflow or a step outside the universe")

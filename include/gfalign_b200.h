@@ -147,8 +147,11 @@ int gfe_edge_weights_from_counts(const uint32_t *edge_from, const uint32_t *edge
  * peer_bases[q] = rank q's exchange buffer as mapped into THIS process (e.g. torch symmetric memory
  * buffer_ptrs), laid out as  u32 data[2][n_cap]; u32 flags[GFE_PEER_MAX]  and zero-filled once
  * before the first call.  Epoch e = 1, 2, ... (the same on every rank): the caller has this rank's
- * records written to data[e & 1] by earlier work on `cuda_stream`; d_out receives the sums. */
+ * records written to data[e & 1] by earlier work on `cuda_stream`; d_out receives the sums.
+ * The wait for the peers is bounded (20 s, GFE_PEER_TIMEOUT_MS): a rank whose peer never reaches the
+ * epoch gets every output slot set to GFE_PEER_TIMEOUT instead of hanging. */
 #define GFE_PEER_MAX 16
+#define GFE_PEER_TIMEOUT 0xFFFFFFFFu
 int gfe_peer_sum_u32(const uint64_t *peer_bases, int world, int rank, uint32_t n_cap, uint32_t n,
                      uint32_t epoch, uint32_t *d_out, void *cuda_stream);
 
@@ -242,10 +245,11 @@ typedef struct gfe_counters {
     uint64_t slow_pairs;          // pairs the bitset kernel handed to the second-look kernel
 } gfe_counters;
 int gfe_get_counters(const gfe_engine *e, gfe_counters *out);
-/* After the *_device entry points (which do not synchronise): waits for the device and reports
- * sticky flags of the enqueued work — bit0: a candidate path named a node outside the universe,
- * bit1: the exact-DP worklist overflowed (results of that batch are incomplete; re-run it through
- * gfe_score_paths, which grows the list and retries by itself). */
+/* After the *_device entry points (which do not synchronise): waits for the device and reports the
+ * flags of ALL batches enqueued since the previous report (they are sticky across batches and are
+ * cleared by the report) — bit0: a candidate path named a node outside the universe, bit1: a
+ * worklist overflowed (results of that batch are incomplete; re-run it through gfe_score_paths,
+ * which grows the list and retries by itself). */
 int gfe_device_status(gfe_engine *e, uint32_t *flags);
 /* The same flags written to a device word, stream-ordered behind the *_device calls on `cuda_stream`
  * (no synchronisation): sharded callers add the word to the exchanged record so that every rank

@@ -1,0 +1,43 @@
+"""The non-bitset scoring path (score_paths_kernel, kernels.cu): forced with GFE_FORCE_LEGACY=1, and
+reached naturally by a universe whose pair dictionary + node planes do not fit shared memory."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from gfalign_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pytestmark = pytest.mark.gpu
+
+
+def test_force_legacy_env_matches_oracle():
+    env = dict(os.environ, GFE_FORCE_LEGACY="1")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "legacy_worker.py")], env=env,
+                       capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-3000:]
+    assert "legacy ok" in p.stdout
+
+
+def test_pair_dictionary_overflow_falls_back_and_matches_oracle(engine, oracle):
+    """20 000-node universe: the node planes alone take 40 k of the 52 k shared-memory words, the
+    graph's ~28 k distinct pairs do not fit the rest -> no dictionary -> position-table kernel."""
+    t = synth.make_tangle(20000, 8000, seed=41, minus_frac=0.05, count2_frac=0.05)
+    off, st = synth.random_walk_alignments(t.n_nodes, t.edge_from, t.edge_to, 120000,
+                                           *synth.HIFI_LENGTHS, seed=42)
+    nodes, _, _ = synth.node_table(t)
+    po, ps = synth.candidate_paths(t, 48, seed=43, max_len=400)
+    engine.set_alignments(off, st, t.n_nodes)
+    engine.set_universe(nodes)
+    c0 = engine.counters()
+    got = engine.score_paths(po, ps, filter=True)
+    c1 = engine.counters()
+    # prologue + tables + score_paths + exact worklist: the bitset chain would add a second-look launch
+    assert c1["kernel_launches"] - c0["kernel_launches"] == 4
+    want = oracle.evaluate_paths(po, ps, off, st, True, os.cpu_count() or 1)
+    assert np.array_equal(got, want)
+    assert int(got.sum()) > 0
+    got = engine.score_paths(po, ps, filter=False)
+    assert np.array_equal(got, oracle.evaluate_paths(po, ps, off, st, False, os.cpu_count() or 1))

@@ -138,7 +138,7 @@ def test_golden_search_rows(engine):
 
 
 def test_golden_evalpath_scores(engine):
-    from gfalign_b200 import textio
+    import textio
     from test_oracle import _evalpath_expect
     seen = 0
     for c in _cases():
@@ -160,7 +160,7 @@ def test_golden_evalpath_scores(engine):
 
 
 def test_golden_evalgfa_weights(engine):
-    from gfalign_b200 import textio
+    import textio
     seen = 0
     for c in _cases():
         if not c["name"].endswith("_evalgfa"):
@@ -282,7 +282,7 @@ def test_trace_pairs_matches_oracle(engine, oracle, alpha, n_hi, m_hi, seed):
 def test_golden_evalpath_stdout_through_engine(engine):
     """Full evalPath stdout (gapped strings, scores, totals) of the golden cases from
     gfe_score_pairs + gfe_trace_pairs."""
-    from gfalign_b200 import textio
+    import textio
     from evalpath_text import evalpath_stdout
     seen = 0
     for c in _cases():

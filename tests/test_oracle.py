@@ -8,7 +8,8 @@ import os
 import numpy as np
 import pytest
 
-from gfalign_b200 import synth, textio
+from gfalign_b200 import synth
+import textio
 
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
@@ -143,7 +144,7 @@ def test_oracle_threads_agree(oracle):
 def test_golden_evalpath_gapped_strings(oracle, cli_cases):
     """Pins the oracle's traceback (orc_pair_alignment) to the reference: the full evalPath stdout —
     every gapped alignment string, score and the totals — of the 18 golden CLI cases."""
-    from gfalign_b200 import textio
+    import textio
     from evalpath_text import evalpath_stdout, ops_from_gapped
     seen = 0
     for c in cli_cases.values():

@@ -1,5 +1,5 @@
 """CPU suite: the C++ text packers (gfe_text_*: GFA1 / GAF -> packed arrays, the host side of the
-drop-in CLI) against the Python restatement in gfalign_b200/textio.py — which the golden search /
+drop-in CLI) against the Python restatement in tests/textio.py — which the golden search /
 evalPath / evalGFA tests pin to the reference — on every golden case, on odd walks, and on a GAF
 large enough to be split across parser threads."""
 import os
@@ -7,7 +7,8 @@ import os
 import numpy as np
 import pytest
 
-from gfalign_b200 import capi, synth, textio
+from gfalign_b200 import capi, synth
+import textio
 from test_gpu_parity import _cases
 
 

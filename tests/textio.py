@@ -14,7 +14,7 @@ from typing import Dict, List, Tuple
 
 import numpy as np
 
-from . import synth
+from gfalign_b200 import synth
 
 
 def parse_gfa(text: str):
