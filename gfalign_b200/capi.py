@@ -80,6 +80,7 @@ EXPORTS = [
     "gfe_trace_pairs", "gfe_filter_alignments",
     "gfe_text_open", "gfe_text_close", "gfe_text_get", "gfe_text_node_name", "gfe_text_node_id",
     "gfe_text_qname", "gfe_peer_sum_u32", "gfe_device_status_to",
+    "gfe_exchange_create", "gfe_exchange_destroy", "gfe_score_paths_sharded", "gfe_search_sharded",
 ]
 
 PEER_MAX = 16      # GFE_PEER_MAX
@@ -95,6 +96,31 @@ def peer_sum_u32(peer_bases, rank: int, n_cap: int, n: int, epoch: int, d_out: i
     rc = lib.gfe_peer_sum_u32(arr, len(peer_bases), rank, n_cap, n, epoch, C.c_void_p(d_out), C.c_void_p(stream))
     if rc != 0:
         raise GfeError(rc, "gfe_peer_sum_u32: bad arguments or launch failure")
+
+
+class Exchange:
+    """gfe_exchange: this rank's view of the box's peer-mapped exchange buffer (see sharded.PeerExchange
+    for the allocation through torch symmetric memory)."""
+
+    def __init__(self, peer_bases, rank: int, n_cap: int):
+        lib = load_library()
+        arr = (C.c_uint64 * len(peer_bases))(*[int(b) for b in peer_bases])
+        h = C.c_void_p()
+        rc = lib.gfe_exchange_create(arr, len(peer_bases), rank, n_cap, C.byref(h))
+        if rc != 0:
+            raise GfeError(rc, "gfe_exchange_create: bad arguments")
+        self.handle, self._lib, self.n_cap = h, lib, n_cap
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self._lib.gfe_exchange_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def load_library() -> C.CDLL:
@@ -129,6 +155,13 @@ def load_library() -> C.CDLL:
     lib.gfe_device_status_to.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.gfe_peer_sum_u32.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_int, C.c_uint32, C.c_uint32,
                                      C.c_uint32, C.c_void_p, C.c_void_p]
+    lib.gfe_exchange_create.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_int, C.c_uint32,
+                                        C.POINTER(C.c_void_p)]
+    lib.gfe_exchange_destroy.argtypes = [C.c_void_p]
+    lib.gfe_exchange_destroy.restype = None
+    lib.gfe_score_paths_sharded.argtypes = [C.c_void_p, C.c_void_p, _u32p, _u32p, C.c_uint32, C.c_int, _u32p]
+    lib.gfe_search_sharded.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(_Graph), C.POINTER(_SearchParams),
+                                       _ROW_FN, C.c_void_p, C.POINTER(_SearchStats)]
     lib.gfe_search.argtypes = [C.c_void_p, C.POINTER(_Graph), C.POINTER(_SearchParams), _ROW_FN,
                                C.c_void_p, C.POINTER(_SearchStats)]
     lib.gfe_search_with_scorer.argtypes = [_SCORE_FN, C.c_void_p, C.POINTER(_Graph),
@@ -243,6 +276,25 @@ class Engine:
         self._check(self._lib.gfe_score_paths(self._h, _ptr(po), _ptr(ps), P, int(filter),
                                               _ptr(counts)))
         return counts
+
+    def score_paths_sharded(self, exchange, path_offsets, path_steps, filter: bool = True) -> np.ndarray:
+        """gfe_score_paths_sharded: (P, 2) counts summed over every rank's alignment shard."""
+        po, ps = _u32(path_offsets), _u32(path_steps)
+        P = po.size - 1
+        counts = np.zeros((max(P, 0), 2), dtype=np.uint32)
+        self._check(self._lib.gfe_score_paths_sharded(self._h, exchange.handle, _ptr(po), _ptr(ps), P,
+                                                      int(filter), _ptr(counts)))
+        return counts
+
+    def search_sharded(self, exchange, adj_offsets, adj_target, adj_or0, adj_or1, source: int,
+                       destination: int, budget_nodes, budget_counts, node_count: int,
+                       max_steps: int = 100000, min_nodes: int = 0, return_all_paths: bool = False,
+                       speculate: int = 0, on_row=None):
+        """gfe_search_sharded: dijkstra() replayed on every rank over the summed shard counts."""
+        return _run_search(lambda g, p, cb, st: self._check(
+            self._lib.gfe_search_sharded(self._h, exchange.handle, g, p, cb, None, st)),
+            adj_offsets, adj_target, adj_or0, adj_or1, source, destination, budget_nodes,
+            budget_counts, node_count, max_steps, min_nodes, return_all_paths, speculate, on_row)
 
     def score_paths_device(self, d_path_offsets: int, d_path_steps: int, P: int, total: int,
                            d_counts: int, filter: bool = True, stream: int = 0):

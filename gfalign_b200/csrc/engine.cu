@@ -578,8 +578,20 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     return GFE_OK;
 }
 
-int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t *path_steps,
-                    uint32_t P, int filter, uint32_t *counts) {
+}  // extern "C"
+
+// One exchange buffer of the sharded path as seen from this rank (gfe_exchange_create).
+struct gfe_exchange {
+    uint64_t bases[GFE_PEER_MAX];
+    int world = 1, rank = 0;
+    uint32_t n_cap = 0, epoch = 0;
+};
+
+// gfe_score_paths, and with `x` its sharded form: the kernels accumulate this rank's records
+// straight into the exchange buffer, the status word rides along as slot 2P, the peer kernel sums
+// all shards into the result block and ONE device->host copy brings back header + summed counts.
+static int score_paths_impl(gfe_engine *e, gfe_exchange *x, const uint32_t *path_offsets,
+                            const uint32_t *path_steps, uint32_t P, int filter, uint32_t *counts) {
     if (!e || !path_offsets || !counts) return GFE_ERR_ARG;
     if (!e->have_alignments || !e->have_universe) {
         set_error(e, "gfe_score_paths: alignments and universe must be set first");
@@ -614,10 +626,10 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
     TRY(ensure_pinned(e, e->h_stage, bytes));
     TRY(ensure_dev(e, e->d_stage, bytes));
     TRY(ensure_dev(e, e->d_plocal, (size_t)total + 8));
-    TRY(ensure_pinned(e, e->h_counts, (size_t)P * 2 + kHdr));
+    TRY(ensure_pinned(e, e->h_counts, (size_t)P * 2 + kHdr + 1));
     {
         const uint32_t *before = e->d_counts.ptr;
-        TRY(ensure_dev(e, e->d_counts, (size_t)P * 2 + kHdr));
+        TRY(ensure_dev(e, e->d_counts, (size_t)P * 2 + kHdr + 1));
         if (e->d_counts.ptr != before)
             CUDA_TRY(e, cudaMemsetAsync(e->d_counts.ptr, 0, kHdr * sizeof(uint32_t), e->stream));
     }
@@ -628,16 +640,64 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
     const uint32_t *d_poff = reinterpret_cast<const uint32_t *>(e->d_stage.ptr);
     const uint32_t *d_raw = reinterpret_cast<const uint32_t *>(e->d_stage.ptr + off_bytes);
     uint32_t *d_hdr = e->d_counts.ptr, *d_cnt = e->d_counts.ptr + kHdr;
-    TRY(enqueue_score(e, d_poff, e->d_plocal.ptr, P, total, filter, d_cnt, d_hdr, d_raw, d_hdr + kWorkCounters,
-                      nullptr, e->stream));
-    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, ((size_t)P * 2 + kHdr) * sizeof(uint32_t),
+    if (x) {
+        if (2 * (uint64_t)P + 1 > x->n_cap) {
+            set_error(e, "gfe_score_paths_sharded: %u paths exceed the exchange buffer (%u slots)", P, x->n_cap);
+            return GFE_ERR_ARG;
+        }
+        uint32_t *d_mine = reinterpret_cast<uint32_t *>(x->bases[x->rank]) + (size_t)x->n_cap * ((x->epoch + 1) & 1u);
+        TRY(enqueue_score(e, d_poff, e->d_plocal.ptr, P, total, filter, d_mine, d_hdr, d_raw,
+                          d_hdr + kWorkCounters, nullptr, e->stream));
+        // slot 2P: this rank's flags (bad step | overflow).  Its sum tells every rank alike to repeat the
+        // batch, so the ranks stay in lock step.  The header keeps the local counters for the retry below.
+        launch_flag_word(d_hdr + kWorkCounters, d_hdr, d_mine + 2 * (size_t)P, e->stream);
+        e->kernel_launches += 2;
+        x->epoch += 1;
+        const int prc = gfe_peer_sum_u32(x->bases, x->world, x->rank, x->n_cap, 2 * P + 1, x->epoch, d_cnt, e->stream);
+        if (prc != GFE_OK) {
+            set_error(e, "gfe_score_paths_sharded: peer sum launch failed");
+            return prc;
+        }
+    } else {
+        TRY(enqueue_score(e, d_poff, e->d_plocal.ptr, P, total, filter, d_cnt, d_hdr, d_raw, d_hdr + kWorkCounters,
+                          nullptr, e->stream));
+    }
+    const size_t res_words = (size_t)P * 2 + kHdr + (x ? 1 : 0);
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, res_words * sizeof(uint32_t),
                                 cudaMemcpyDeviceToHost, e->stream));
     uint32_t wc[kWorkCounters] = {};
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     for (int i = 0; i < kWorkCounters; ++i) wc[i] = e->h_counts.ptr[i];
     if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
     e->h2d_bytes += bytes;
-    e->d2h_bytes += ((size_t)P * 2 + kHdr) * sizeof(uint32_t);
+    e->d2h_bytes += res_words * sizeof(uint32_t);
+    const uint32_t any_flags = x ? e->h_counts.ptr[kHdr + 2 * (size_t)P] : 0u;   // summed over the ranks
+    if (x && any_flags == GFE_PEER_TIMEOUT) {
+        set_error(e, "gfe_score_paths_sharded: a peer never reached epoch %u (GFE_PEER_TIMEOUT_MS)", x->epoch);
+        return GFE_ERR_CUDA;
+    }
+    if (x && any_flags && !e->h_counts.ptr[kWorkCounters]) {
+        // some rank overflowed a list (or all saw a bad step, handled below): every rank repeats the
+        // batch; the ranks that overflowed grow their lists first
+        if (wc[3] && e->d_slow.cap < (1ull << 28)) {
+            e->slow_cap = std::min<size_t>(std::max<size_t>(e->d_slow.cap * 4, (size_t)wc[2] + 1024), (size_t)1 << 28);
+            TRY(ensure_dev(e, e->d_slow, e->slow_cap));
+        } else if (wc[3]) {
+            set_error(e, "gfe_score_paths_sharded: second-look list overflow at its maximum size");
+            return GFE_ERR_LIMIT;
+        }
+        if (wc[1]) {
+            e->work_cap = std::max<size_t>(e->d_work.cap * 2, (size_t)wc[0] + 1024);
+            TRY(ensure_dev(e, e->d_work, e->work_cap));
+        }
+        if (++e->shard_retries > 8) {
+            set_error(e, "gfe_score_paths_sharded: batch still overflows after 8 collective retries");
+            return GFE_ERR_LIMIT;
+        }
+        const int rc = score_paths_impl(e, x, path_offsets, path_steps, P, filter, counts);
+        e->shard_retries = 0;
+        return rc;
+    }
     if (e->h_counts.ptr[kWorkCounters]) {
         // a step outside the universe: name it the way the host check did, and clear the flag
         CUDA_TRY(e, cudaMemset(e->d_counts.ptr + kWorkCounters, 0, sizeof(uint32_t)));
@@ -651,13 +711,13 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
         set_error(e, "gfe_score_paths: a step names a node outside the universe");
         return GFE_ERR_ARG;
     }
-    if (wc[3]) {
+    if (!x && wc[3]) {
         // the list of pairs the bitsets could not settle overflowed: grow it, or halve the batch
         if (e->d_slow.cap < (1ull << 28)) {
             e->slow_cap = std::min<size_t>(std::max<size_t>(e->d_slow.cap * 4, (size_t)wc[2] + 1024),
                                            (size_t)1 << 28);
             TRY(ensure_dev(e, e->d_slow, e->slow_cap));
-            return gfe_score_paths(e, path_offsets, path_steps, P, filter, counts);
+            return score_paths_impl(e, nullptr, path_offsets, path_steps, P, filter, counts);
         }
         if (P < 2) {
             set_error(e, "gfe_score_paths: work list overflow on a single path");
@@ -666,20 +726,48 @@ int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t 
         const uint32_t h = P / 2;
         std::vector<uint32_t> off2(path_offsets + h, path_offsets + P + 1);
         for (uint32_t &o : off2) o -= path_offsets[h];
-        TRY(gfe_score_paths(e, path_offsets, path_steps, h, filter, counts));
-        return gfe_score_paths(e, off2.data(), path_steps + path_offsets[h], P - h, filter,
-                               counts + 2 * (size_t)h);
+        TRY(score_paths_impl(e, nullptr, path_offsets, path_steps, h, filter, counts));
+        return score_paths_impl(e, nullptr, off2.data(), path_steps + path_offsets[h], P - h, filter,
+                                counts + 2 * (size_t)h);
     }
-    if (wc[1]) {
+    if (!x && wc[1]) {
         // the exact-DP worklist overflowed: grow it and redo the batch (never silently wrong)
         e->work_cap = std::max<size_t>(e->d_work.cap * 2, (size_t)wc[0] + 1024);
         TRY(ensure_dev(e, e->d_work, e->work_cap));
-        return gfe_score_paths(e, path_offsets, path_steps, P, filter, counts);
+        return score_paths_impl(e, nullptr, path_offsets, path_steps, P, filter, counts);
     }
     e->exact_pairs += wc[0];
     e->slow_pairs += wc[2] - wc[4];   // reserved slots minus the holes
     memcpy(counts, e->h_counts.ptr + 16, (size_t)P * 2 * sizeof(uint32_t));
     return GFE_OK;
+}
+
+extern "C" {
+
+int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t *path_steps,
+                    uint32_t P, int filter, uint32_t *counts) {
+    return score_paths_impl(e, nullptr, path_offsets, path_steps, P, filter, counts);
+}
+
+int gfe_exchange_create(const uint64_t *peer_bases, int world, int rank, uint32_t n_cap, gfe_exchange **out) {
+    if (!peer_bases || !out || world < 1 || world > GFE_PEER_MAX || rank < 0 || rank >= world || n_cap == 0)
+        return GFE_ERR_ARG;
+    gfe_exchange *x = new (std::nothrow) gfe_exchange();
+    if (!x) return GFE_ERR_NOMEM;
+    for (int q = 0; q < world; ++q) x->bases[q] = peer_bases[q];
+    x->world = world;
+    x->rank = rank;
+    x->n_cap = n_cap;
+    *out = x;
+    return GFE_OK;
+}
+
+void gfe_exchange_destroy(gfe_exchange *x) { delete x; }
+
+int gfe_score_paths_sharded(gfe_engine *e, gfe_exchange *x, const uint32_t *path_offsets,
+                            const uint32_t *path_steps, uint32_t P, int filter, uint32_t *counts) {
+    if (!x) return GFE_ERR_ARG;
+    return score_paths_impl(e, x, path_offsets, path_steps, P, filter, counts);
 }
 
 int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,
@@ -775,6 +863,7 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
     a.pstep = d_pstep;
     a.n = n;
     a.ptab = e->d_ptab.ptr;
+    a.pnext = e->d_pnext.ptr;
     a.tab_entries = e->tab_stride;
     a.filter = filter;
     a.t_fw = want_scores ? e->d_tfw.ptr : nullptr;

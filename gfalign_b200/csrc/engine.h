@@ -70,6 +70,7 @@ struct gfe_engine {
     DevBuf<uint2> d_work;
     DevBuf<uint32_t> d_work_count, d_pair_work;
     size_t work_cap = 1u << 20;
+    int shard_retries = 0;           // collective batch repeats of gfe_score_paths_sharded
 
     // evalPath outputs
     DevBuf<int32_t> d_tfw, d_trc;

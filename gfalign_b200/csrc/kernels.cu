@@ -8,6 +8,7 @@ namespace gfe {
 namespace {
 
 constexpr unsigned kFull = 0xFFFFFFFFu;
+constexpr int GFE_MAX_STEPS_DEV = 1000;   // GFE_MAX_STEPS (include/gfalign_b200.h): longest path / alignment
 enum Verdict : int { kNone = 0, kBad = 1, kGood = 2, kExact = 3, kSlow = 4 };
 
 __device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }
@@ -386,9 +387,23 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
 // Row 0 of dp is -j for j <= n and 0 beyond (loop bound n at :500), column 0 is 0.
 // One row of (dp, F, F0) lives in registers: MCAP+1 values each, fully unrolled.
 // ------------------------------------------------------------------------------------------------
+// Sparse rows.  A row i of the matrix whose path step A[i-1] visits no node of B is all-mismatch,
+// and all-mismatch rows drive the DP row into a fixed point within at most m rows:
+//     dp[j] = F[j] = F0[j] = -j   for j < m        (diagonal move, checked first, reproduces -j)
+//     dp[m] = best so far;  best > -m: "up" move, F[m] -= 1 per row, F0[m] unchanged
+//                           best == -m: diagonal, F[m] = F0[m] = -m
+// (column 0 is 0, the last column takes up-moves for free, src/alignments.cpp:503-504).  So only the
+// rows that touch B, plus the few rows after each until the fixed point is reached again, are
+// computed cell by cell; a run of k further all-mismatch rows is applied in closed form.  For an
+// evalPath path of 1000 steps against a 5-step alignment that is ~30 rows instead of 1000.
+// `touch` = bitmap over path positions (bit p: node of A[p] is a node of B), either orientation.
+constexpr int kTouchWords = (GFE_MAX_STEPS_DEV + 31) / 32;
+
 template <int MCAP>
 __device__ __forceinline__ int exact_T_regs(const uint16_t *__restrict__ A, int n,
-                                            const uint32_t (&B)[MCAP], int m) {
+                                            const uint32_t (&B)[MCAP], int m,
+                                            const uint32_t *__restrict__ touch) {
+    if (m == 0) return 0;   // the walk only consumes A, free
     int dp[MCAP + 1], F[MCAP + 1], F0[MCAP + 1];
 #pragma unroll
     for (int j = 0; j <= MCAP; ++j) {
@@ -396,11 +411,13 @@ __device__ __forceinline__ int exact_T_regs(const uint16_t *__restrict__ A, int 
         F[j] = 0;
         F0[j] = 0;
     }
-    int res = 0;
-    for (int i = 1; i <= n; ++i) {
+    const int nw = (n + 31) >> 5;
+    int i = 1;
+    while (i <= n) {
         const uint32_t a = A[i - 1];
         int diag_dp = 0, diag_F = 0;     // column 0 of row i-1
         int left_dp = 0, left_F = 0;     // column 0 of row i
+        bool steady = true;              // columns 1..m-1 of row i at the fixed point
 #pragma unroll
         for (int j = 1; j <= MCAP; ++j) {
             if (j > m) break;
@@ -428,10 +445,47 @@ __device__ __forceinline__ int exact_T_regs(const uint16_t *__restrict__ A, int 
             F0[j] = nF0;
             left_dp = v;
             left_F = nF;
-            if (j == m) res = nF0;
+            if (j < m) steady = steady && v == -j && nF == -j && nF0 == -j;
         }
+        const int p = i - 1;
+        const bool touched = (touch[p >> 5] >> (p & 31)) & 1u;
+        if (touched || !steady) {
+            ++i;
+            continue;
+        }
+        // next row that touches B (n + 1: none); rows i+1 .. nt-1 in closed form
+        int w = i >> 5;
+        uint32_t bits = w < nw ? touch[w] & (0xFFFFFFFFu << (i & 31)) : 0u;
+        while (!bits && ++w < nw) bits = touch[w];
+        const int nt = bits ? w * 32 + __ffs(bits) : n + 1;
+        const int k = nt - 1 - i;
+        if (k > 0) {
+#pragma unroll
+            for (int j = 1; j <= MCAP; ++j)
+                if (j == m) {
+                    if (dp[j] > -m) F[j] -= k;
+                    else F[j] = F0[j] = -m;
+                }
+        }
+        i = nt;
     }
-    return res;   // m == 0: 0 (the walk only consumes A, free)
+    int res = 0;
+#pragma unroll
+    for (int j = 1; j <= MCAP; ++j)
+        if (j == m) res = F0[j];
+    return res;
+}
+
+// bitmap of the path positions that visit a node of B (tab: node -> first visit, nxt: visit chain)
+__device__ __forceinline__ void touch_map(const uint16_t *__restrict__ tab, const uint16_t *__restrict__ nxt,
+                                          int n, const uint16_t *__restrict__ b, int m, uint32_t *touch) {
+    const int nw = (n + 31) >> 5;
+    for (int w = 0; w < nw; ++w) touch[w] = 0;
+    for (int j = 0; j < m; ++j) {
+        const uint32_t e = tab[b[j] >> 1];
+        if (e == kTabAbsent) continue;
+        for (int q = (int)(e >> 2) - 1; q != 0xFFFF; q = nxt[q]) touch[q >> 5] |= 1u << (q & 31);
+    }
 }
 
 // Load an alignment (local ids) into registers, forward and reverse-complemented
@@ -449,22 +503,27 @@ __device__ __forceinline__ void load_fw_rc(const uint16_t *__restrict__ b, int m
 template <int MCAP>
 __device__ __noinline__ void exact_both_regs(const uint16_t *__restrict__ A, int n,
                                              const uint16_t *__restrict__ b, int m, bool need_both,
-                                             int *tf, int *tr) {
+                                             const uint32_t *__restrict__ touch, int *tf, int *tr) {
     uint32_t Bf[MCAP], Br[MCAP];
     load_fw_rc<MCAP>(b, m, Bf, Br);
-    int f = exact_T_regs<MCAP>(A, n, Bf, m);
+    int f = exact_T_regs<MCAP>(A, n, Bf, m, touch);
     int r = -1;
-    if (need_both || f != 0) r = exact_T_regs<MCAP>(A, n, Br, m);
+    if (need_both || f != 0) r = exact_T_regs<MCAP>(A, n, Br, m, touch);
     *tf = f;
     *tr = r;
 }
 
+// tab / nxt: the path's node -> first-visit table row and visit chain (build_tables_kernel)
 __device__ __forceinline__ void exact_both(const uint16_t *__restrict__ A, int n,
+                                           const uint16_t *__restrict__ tab,
+                                           const uint16_t *__restrict__ nxt,
                                            const uint16_t *__restrict__ b, int m, bool need_both,
                                            int *tf, int *tr) {
-    if (m <= 8) exact_both_regs<8>(A, n, b, m, need_both, tf, tr);
-    else if (m <= 16) exact_both_regs<16>(A, n, b, m, need_both, tf, tr);
-    else exact_both_regs<kExactRegSteps>(A, n, b, m, need_both, tf, tr);
+    uint32_t touch[kTouchWords];
+    touch_map(tab, nxt, n, b, m, touch);
+    if (m <= 8) exact_both_regs<8>(A, n, b, m, need_both, touch, tf, tr);
+    else if (m <= 16) exact_both_regs<16>(A, n, b, m, need_both, touch, tf, tr);
+    else exact_both_regs<kExactRegSteps>(A, n, b, m, need_both, touch, tf, tr);
 }
 
 // Exact T for alignments longer than kExactRegSteps: one warp per direction, anti-diagonal
@@ -846,7 +905,8 @@ exact_worklist_kernel(const ScoreArgs a) {
             const uint32_t po = a.poff[it.x];
             const int n = (int)(a.poff[it.x + 1] - po);
             int tf, tr;
-            exact_both(a.pstep + po, n, r.ptr, (int)r.m, false, &tf, &tr);
+            exact_both(a.pstep + po, n, a.ptab + (size_t)it.x * a.tab_stride, a.pnext + po, r.ptr, (int)r.m, false,
+                       &tf, &tr);
             const bool good = (tf == 0) || (tr == 0);
             atomicAdd(&a.counts[2 * (size_t)it.x + (good ? 1 : 0)], 1u);
         }
@@ -960,7 +1020,7 @@ pair_exact_kernel(const PairArgs a) {
         const int m = (int)r.m;
         if (m > kExactRegSteps) continue;
         int tf, tr;
-        exact_both(s_path, (int)a.n, r.ptr, m, true, &tf, &tr);
+        exact_both(s_path, (int)a.n, a.ptab, a.pnext, r.ptr, m, true, &tf, &tr);
         const uint32_t ai = a.bk.perm[r.sorted];
         if (a.t_fw) a.t_fw[ai] = tf;
         if (a.t_rc) a.t_rc[ai] = tr;
@@ -1052,6 +1112,14 @@ void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uin
 __global__ void status_flag_kernel(uint32_t *err, const uint32_t *wc, uint32_t *out) {
     *out = ((err && err[0]) ? 1u : 0u) | (((wc && (wc[1] || wc[3])) || (err && err[1])) ? 2u : 0u);
     if (err) err[0] = err[1] = 0;   // reported: a later batch starts clean
+}
+
+__global__ void flag_word_kernel(const uint32_t *err, const uint32_t *wc, uint32_t *out) {
+    *out = (*err ? 1u : 0u) | ((wc[1] || wc[3]) ? 2u : 0u);
+}
+
+void launch_flag_word(const uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st) {
+    flag_word_kernel<<<1, 1, 0, st>>>(err, wc, out);
 }
 
 void launch_status_flag(uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st) {

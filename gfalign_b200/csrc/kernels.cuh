@@ -131,6 +131,7 @@ struct PairArgs {             // evalPath: one path against every alignment
     const uint16_t *pstep;    // the path, local ids
     uint32_t n;
     const uint16_t *ptab;     // one row
+    const uint16_t *pnext;    // next visit of the same node, per path position (0xFFFF = none)
     uint32_t tab_entries;
     int filter;
     int32_t *t_fw, *t_rc;     // may be null; indexed by ORIGINAL alignment index
@@ -255,6 +256,8 @@ void launch_prologue(const PrologueArgs &a, int sm_count, cudaStream_t st);
 // *out = bit0 a path step outside the universe, bit1 a worklist overflowed (gfe_device_status, on the
 // device); err[0] (bad step) and err[1] (sticky overflow of earlier batches) are cleared once reported
 void launch_status_flag(uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st);
+// the same word without clearing anything (the host API reads the header itself afterwards)
+void launch_flag_word(const uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st);
 // masks == nullptr: tables only (legacy kernel); else also ORs path p into the batch's bitsets
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
                          uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, uint32_t *masks,

@@ -431,6 +431,16 @@ static int engine_scorer(void *user, const uint32_t *path_offsets, const uint32_
     return gfe_score_paths(static_cast<gfe_engine *>(user), path_offsets, path_steps, P, 1, counts);
 }
 
+// universe = every node that owns a NodeTable record (nodelist + source + destination)
+static void search_universe(const gfe_graph *g, const gfe_search_params *p, std::vector<uint32_t> &uni) {
+    std::vector<uint8_t> in(g->n_nodes, 0);
+    for (uint32_t i = 0; i < p->n_budget; ++i)
+        if (p->budget_counts[i]) in[p->budget_nodes[i]] = 1;
+    in[p->source] = in[p->destination] = 1;
+    for (uint32_t v = 0; v < g->n_nodes; ++v)
+        if (in[v]) uni.push_back(v);
+}
+
 static int check_search_args(const gfe_graph *g, const gfe_search_params *p) {
     if (!g || !p || !g->adj_offsets) return GFE_ERR_ARG;
     if (p->source >= g->n_nodes || p->destination >= g->n_nodes) return GFE_ERR_ARG;
@@ -444,19 +454,37 @@ extern "C" int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_pa
     if (!e) return GFE_ERR_ARG;
     int rc = check_search_args(g, p);
     if (rc != GFE_OK) return rc;
-    // universe = every node that owns a NodeTable record (nodelist + source + destination)
     std::vector<uint32_t> uni;
-    {
-        std::vector<uint8_t> in(g->n_nodes, 0);
-        for (uint32_t i = 0; i < p->n_budget; ++i)
-            if (p->budget_counts[i]) in[p->budget_nodes[i]] = 1;
-        in[p->source] = in[p->destination] = 1;
-        for (uint32_t v = 0; v < g->n_nodes; ++v)
-            if (in[v]) uni.push_back(v);
-    }
+    search_universe(g, p, uni);
     rc = gfe_set_universe(e, uni.data(), (uint32_t)uni.size());
     if (rc != GFE_OK) return rc;
     return run_search(engine_scorer, e, g, p, emit, user, stats);
+}
+
+namespace {
+struct ShardedUser {
+    gfe_engine *e;
+    gfe_exchange *x;
+};
+int sharded_scorer(void *user, const uint32_t *path_offsets, const uint32_t *path_steps, uint32_t P,
+                   uint32_t *counts) {
+    ShardedUser *u = static_cast<ShardedUser *>(user);
+    return gfe_score_paths_sharded(u->e, u->x, path_offsets, path_steps, P, 1, counts);
+}
+}  // namespace
+
+extern "C" int gfe_search_sharded(gfe_engine *e, gfe_exchange *x, const gfe_graph *g,
+                                  const gfe_search_params *p, gfe_row_fn emit, void *user,
+                                  gfe_search_stats *stats) {
+    if (!e || !x) return GFE_ERR_ARG;
+    int rc = check_search_args(g, p);
+    if (rc != GFE_OK) return rc;
+    std::vector<uint32_t> uni;
+    search_universe(g, p, uni);
+    rc = gfe_set_universe(e, uni.data(), (uint32_t)uni.size());
+    if (rc != GFE_OK) return rc;
+    ShardedUser u{e, x};
+    return run_search(sharded_scorer, &u, g, p, emit, user, stats);
 }
 
 extern "C" int gfe_search_with_scorer(gfe_score_fn score, void *score_user, const gfe_graph *g,

@@ -114,16 +114,6 @@ def main(argv=None):
         def local_score(po, ps):
             return eng.score_paths(po, ps, filter=True)
 
-        if world > 1:
-            scorer = sharded.ShardedScorer(local_score, device=device)
-            if os.environ.get("GFE_EXCHANGE", "peer") == "peer":
-                try:      # counts stay on the device, summed by the peer-memory kernel (csrc/peer.cu)
-                    px = sharded.PeerExchange(2 * 4096, device)
-                    scorer = sharded.PeerShardedScorer(eng, px, device, filter=True, fallback=scorer)
-                except Exception as ex:
-                    sys.stderr.write(f"[multigpu] peer exchange unavailable ({ex!r}); using NCCL\n")
-        else:
-            scorer = local_score
         out = sys.stdout
 
         def on_row(row):
@@ -131,12 +121,26 @@ def main(argv=None):
                 out.write(row.columns(tp.names) + "\n")
                 out.flush()
 
-        rows, stats = capi.search_with_scorer(scorer, tp.adj_offsets, tp.adj_target, tp.adj_or0, tp.adj_or1,
-                                              src, dst, nodes, counts, node_count, max_steps=a.max_steps,
-                                              min_nodes=a.min_nodes, return_all_paths=a.return_all_paths,
-                                              speculate=a.speculate, on_row=on_row)
+        kw = dict(max_steps=a.max_steps, min_nodes=a.min_nodes, return_all_paths=a.return_all_paths,
+                  speculate=a.speculate, on_row=on_row)
+        px = None
+        scorer = local_score
+        if world > 1:
+            scorer = sharded.ShardedScorer(local_score, device=device)      # counts over NCCL
+            if os.environ.get("GFE_EXCHANGE", "peer") == "peer":
+                try:      # counts stay on the device, summed by the peer-memory kernel (csrc/peer.cu)
+                    px = sharded.PeerExchange(2 * 4096 + 1, device)
+                except Exception as ex:
+                    sys.stderr.write(f"[multigpu] peer exchange unavailable ({ex!r}); using NCCL\n")
+        if px is not None:
+            # the whole loop in C: gfe_search_sharded -> gfe_score_paths_sharded per batch
+            rows, stats = eng.search_sharded(px.c_exchange(), tp.adj_offsets, tp.adj_target, tp.adj_or0,
+                                             tp.adj_or1, src, dst, nodes, counts, node_count, **kw)
+        else:
+            rows, stats = capi.search_with_scorer(scorer, tp.adj_offsets, tp.adj_target, tp.adj_or0,
+                                                  tp.adj_or1, src, dst, nodes, counts, node_count, **kw)
         if rank == 0 and os.environ.get("GFE_DEBUG_TIMING"):
-            sys.stderr.write(f"[multigpu] scorer {type(scorer).__name__}, {getattr(scorer, 'calls', 0)} exchanges, "
+            sys.stderr.write(f"[multigpu] exchange {'peer kernel (C loop)' if px is not None else type(scorer).__name__}, "
                              f"{stats['kernel_batches']} batches, scoring {stats['seconds_scoring']:.3f} s\n")
         if rank == 0 and stats["extractions"] >= a.max_steps:
             out.write(f"Reached maximum number of steps ({stats['extractions']})\n")

@@ -64,6 +64,15 @@ class PeerExchange:
         dist.barrier(group=group)          # every rank's flags are zero before the first epoch
         self.epoch = 0
 
+    def c_exchange(self) -> "capi.Exchange":
+        """The same buffer as a gfe_exchange for gfe_score_paths_sharded / gfe_search_sharded.  Use either
+        this handle or half_ptr()/sum_into() on one PeerExchange, not both (each keeps its own epoch)."""
+        if getattr(self, "_cx", None) is None:
+            if self.epoch:
+                raise RuntimeError("PeerExchange already used through sum_into()")
+            self._cx = capi.Exchange(self.bases, self.rank, self.n_cap)
+        return self._cx
+
     def half_ptr(self) -> int:
         """Device address of the half the NEXT sum_into() reads on this rank."""
         return self.bases[self.rank] + 4 * self.n_cap * ((self.epoch + 1) & 1)
@@ -100,44 +109,27 @@ class ShardedScorer:
 
 
 class PeerShardedScorer:
-    """The same contract as ShardedScorer for GPU ranks of one box, with the counts kept on the device:
-    the batch goes host -> device once, `Engine.score_paths_device` accumulates this rank's records
-    into the exchange buffer, the peer-memory kernel sums all shards, and only the summed P x 2 record
-    comes back (no NCCL call, no extra device<->host hop).  Batches above `n_cap / 2` paths fall back
-    to `fallback` (a ShardedScorer)."""
+    """The same contract as ShardedScorer for GPU ranks of one box, through ONE C call per batch
+    (gfe_score_paths_sharded): the batch goes host -> device once, the kernels accumulate this rank's
+    records into the exchange buffer, the peer-memory kernel sums all shards, and only the summed
+    P x 2 record comes back (no NCCL call, no extra device<->host hop).  A rank's worklist overflow
+    travels as one more slot of the record, so all ranks repeat that batch together.  Batches above
+    `(n_cap - 1) / 2` paths go to `fallback` (a ShardedScorer); P is the same on every rank, so the
+    decision is too."""
 
-    def __init__(self, engine, exchange: PeerExchange, device, filter: bool = True, fallback=None):
-        import torch
-        self.torch, self.engine, self.px, self.device = torch, engine, exchange, device
+    def __init__(self, engine, exchange: PeerExchange, device=None, filter: bool = True, fallback=None):
+        self.engine, self.px, self.cx = engine, exchange, exchange.c_exchange()
         self.filter, self.fallback = filter, fallback
-        self.out = torch.zeros(exchange.n_cap, dtype=torch.int32, device=device)
         self.calls = 0
 
     def __call__(self, path_offsets: np.ndarray, path_steps: np.ndarray) -> np.ndarray:
-        torch = self.torch
         P = int(path_offsets.size) - 1
         if 2 * P + 1 > self.px.n_cap:
             if self.fallback is None:
                 raise ValueError(f"batch of {P} paths exceeds the exchange buffer")
             return self.fallback(path_offsets, path_steps)
-        d_po = torch.from_numpy(np.ascontiguousarray(path_offsets, dtype=np.uint32).view(np.int32)).to(self.device)
-        d_ps = torch.from_numpy(np.ascontiguousarray(path_steps, dtype=np.uint32).view(np.int32)).to(self.device)
-        stream = torch.cuda.current_stream(self.device).cuda_stream
-        self.engine.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), P, int(path_steps.size),
-                                       self.px.half_ptr(), filter=self.filter, stream=stream)
-        # slot 2P of the record = this rank's status flags: the sum tells every rank alike whether
-        # any shard overflowed a worklist (or saw a bad step), and all repeat the batch the slow way
-        self.engine.device_status_to(self.px.half_ptr() + 8 * P, stream)
-        self.px.sum_into(self.out.data_ptr(), 2 * P + 1, stream)
         self.calls += 1
-        rec = self.out[:2 * P + 1].cpu().numpy().view(np.uint32)
-        if rec[2 * P] == 0xFFFFFFFF:
-            raise RuntimeError("peer exchange timed out: a rank never reached this batch (GFE_PEER_TIMEOUT)")
-        if rec[2 * P]:
-            if self.fallback is None:
-                raise RuntimeError("a shard reported a worklist overflow or a step outside the universe")
-            return self.fallback(path_offsets, path_steps)
-        return rec[:2 * P].reshape(P, 2).copy()
+        return self.engine.score_paths_sharded(self.cx, path_offsets, path_steps, self.filter)
 
 
 def sharded_search(scorer: ShardedScorer, tangle, nodes, counts, node_count, **kw):

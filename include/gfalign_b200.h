@@ -155,6 +155,19 @@ int gfe_edge_weights_from_counts(const uint32_t *edge_from, const uint32_t *edge
 int gfe_peer_sum_u32(const uint64_t *peer_bases, int world, int rank, uint32_t n_cap, uint32_t n,
                      uint32_t epoch, uint32_t *d_out, void *cuda_stream);
 
+/* The sharded form of gfe_score_paths as ONE call (host paths in, summed host counts out): this rank's
+ * kernels accumulate into its half of the exchange buffer, the rank's status word rides along as one
+ * more slot, gfe_peer_sum_u32 sums all shards, one device->host copy returns the result.  Every rank
+ * of the box calls it with the same batch, in the same order (the search is replayed in lock step on
+ * every rank, reference src/eval.cpp:134-189); if any rank overflowed a worklist, all ranks repeat
+ * the batch together.  gfe_exchange wraps the peer-mapped buffer (layout above; n_cap >= 2P + 1). */
+typedef struct gfe_exchange gfe_exchange;
+int gfe_exchange_create(const uint64_t *peer_bases, int world, int rank, uint32_t n_cap,
+                        gfe_exchange **out);
+void gfe_exchange_destroy(gfe_exchange *x);
+int gfe_score_paths_sharded(gfe_engine *e, gfe_exchange *x, const uint32_t *path_offsets,
+                            const uint32_t *path_steps, uint32_t P, int filter, uint32_t *counts);
+
 /* ---- best-first search driver -------------------------------------------------------------------
  * Replaces dijkstra() (reference src/eval.cpp:110-193) on packed inputs: the bidirected adjacency
  * of InSequences::buildEdgeGraph (reference gfalibs/src/gfa.cpp:1076-1097) as CSR over nodes
@@ -200,6 +213,12 @@ typedef struct gfe_search_stats {
 
 int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_params *p, gfe_row_fn emit,
                void *user, gfe_search_stats *stats);
+
+/* gfe_search over alignment shards: every rank calls it with its own engine (holding its shard) and the
+ * box's exchange buffer; evaluatePath is answered by gfe_score_paths_sharded, so all ranks emit the
+ * same rows. */
+int gfe_search_sharded(gfe_engine *e, gfe_exchange *x, const gfe_graph *g, const gfe_search_params *p,
+                       gfe_row_fn emit, void *user, gfe_search_stats *stats);
 
 /* The same driver with the evaluatePath calls answered by a caller-supplied backend: `score`
  * receives a batch of P candidate paths (CSR, oriented steps) and must fill counts[2p] = bad,

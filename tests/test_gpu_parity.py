@@ -387,3 +387,68 @@ def test_device_status_word_matches_host_status(engine):
     torch.cuda.synchronize()
     assert int(flag.item()) == engine.device_status()
     assert int(flag.item()) & 1          # a step outside the universe was seen
+
+
+def _world1_exchange(n_cap):
+    """A one-rank exchange buffer: plain device memory, the rank publishes to and reads from itself."""
+    import torch
+    from gfalign_b200 import capi
+    buf = torch.zeros(2 * n_cap + capi.PEER_MAX, dtype=torch.int32, device="cuda")
+    return buf, capi.Exchange([buf.data_ptr()], 0, n_cap)
+
+
+def test_sharded_entry_world1_scores_and_search_rows(engine, oracle):
+    """gfe_score_paths_sharded / gfe_search_sharded with world = 1 (the code path every rank of a
+    multi-GPU run takes: accumulate into the exchange buffer, status slot, peer sum, one copy back):
+    counts == oracle, search rows == the reference CLI's on every golden search case."""
+    from test_oracle import _search_inputs, search_rows_text
+    buf, x = _world1_exchange(2 * 4096 + 1)
+    w = synth.make_workload("cfg3", A=30000)
+    t = w.tangle
+    nodes, _, _ = synth.node_table(t)
+    po, ps = synth.candidate_paths(t, 200, seed=8)
+    engine.set_alignments(w.offsets, w.steps, t.n_nodes)
+    engine.set_universe(nodes)
+    for _ in range(3):     # both halves of the buffer, growing epochs
+        got = engine.score_paths_sharded(x, po, ps, filter=True)
+        assert np.array_equal(got, oracle.evaluate_paths(po, ps, w.offsets, w.steps, True, 4))
+    assert np.array_equal(got, engine.score_paths(po, ps, filter=True))
+    seen = 0
+    for c in _cases():
+        if "_search" not in c["name"]:
+            continue
+        tt, off, st, kw = _search_inputs(c)
+        nd, cn, node_count = synth.node_table(tt)
+        engine.set_alignments(off, st, tt.n_nodes)
+        rows, stats = engine.search_sharded(x, tt.adj_offsets, tt.adj_target, tt.adj_or0, tt.adj_or1,
+                                            tt.source, tt.destination, nd, cn, node_count, **kw)
+        assert search_rows_text(rows, stats, tt.names, kw) == c["stdout"].splitlines(), c["name"]
+        seen += 1
+    assert seen >= 13
+    x.close()
+
+
+def test_device_status_is_sticky_across_batches_and_cleared_by_the_report(engine):
+    """A bad step in batch 1 must still be reported after a clean batch 2 (flags of all batches since
+    the last report), and the report clears it."""
+    import torch
+    w = synth.make_workload("cfg3", A=5000)
+    t = w.tangle
+    nodes, _, _ = synth.node_table(t)
+    po, ps = synth.candidate_paths(t, 8, seed=1)
+    engine.set_alignments(w.offsets, w.steps, t.n_nodes)
+    dev = torch.device("cuda", 0)
+    d_po = torch.from_numpy(po.astype(np.int64)).to(dev).to(torch.int32)
+    d_ps = torch.from_numpy(ps.astype(np.int64)).to(dev).to(torch.int32)
+    d_counts = torch.zeros(2 * 8, dtype=torch.int32, device=dev)
+    engine.set_universe(nodes)
+    engine.device_status()                                        # clear whatever earlier tests left
+    bad = d_ps.clone()
+    bad[1] = int((t.n_nodes + 5) << 1)                           # a node outside the universe
+    engine.score_paths_device(d_po.data_ptr(), bad.data_ptr(), 8, int(ps.size), d_counts.data_ptr(), filter=True)
+    engine.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), 8, int(ps.size), d_counts.data_ptr(), filter=True)
+    assert engine.device_status() & 1
+    assert engine.device_status() == 0
+    engine.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), 8, int(ps.size), d_counts.data_ptr(), filter=True)
+    assert engine.device_status() == 0
+    assert np.array_equal(d_counts.cpu().numpy().view(np.uint32).reshape(8, 2), engine.score_paths(po, ps, True))
