@@ -1,21 +1,36 @@
 #!/usr/bin/env python
-"""bench.py — headline benchmark of the gfalign hot path on B200 (contract: see DESIGN.md §Measurement).
+"""bench.py — headline benchmark of the gfalign hot path on B200 (contract: see DESIGN.md §6).
 
 One "step" = one pass of the hot path over one batch: P candidate paths (the kind `gfalign search`
 expands) scored against every alignment of the resident table with the id filter on
 (evaluatePath x P, reference src/eval.cpp:67-108).  metric = path x alignment checks per second,
 whole job.  N > 1 (torchrun): every rank holds its own alignment shard of the same shape (weak
-scaling), scores the same batch, and the P x {bad, good} counts are combined with one NCCL
-all-reduce per step inside the timed region.
+scaling, `value`), scores the same batch, and the P x {bad, good} records are summed by the peer-memory
+exchange kernel inside the timed step.  Every run — at every N — checks a few of the scored paths
+against the CPU oracle (`parity_check`) and fails loudly when they differ.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg3|cfg5] [--paths P]
+Blocks of the one JSON line (beside the contract's keys):
+  parity_check   oracle spot check of the timed configuration (all shards), peer and NCCL exchange
+  roofline       dominant kernel against the SM issue roof (it is integer-ALU/issue bound), with the
+                 HBM view (algorithmic bytes, measured DRAM traffic) next to it; counters from a live
+                 `ncu --metrics` child run when ncu is on the box, else from the committed capture
+  e2e            host buffers in, host counts out, through the C ABI (N > 1: gfe_score_paths_sharded)
+  search         `gfalign search -m 100000` driver: search paths/s (BASELINE's second metric)
+  strong_cfg5    BASELINE configs[4]: 50 M alignments split over the N GPUs (N = 1: the whole table)
+  extras         N = 1: BASELINE configs[3] (cfg4): evalGFA / evalPath / trace / filter kernels
+  cpu_baseline   N = 1: the unmodified reference CLI on a bounded sample + the oracle port
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--paths P] [--no-extras] [--no-cfg5] ...
   python bench.py --impl reference ...   # the reference's own CPU implementation, bounded sample
 """
 from __future__ import annotations
 
 import argparse
+import csv
+import io
 import json
 import os
+import shutil
 import subprocess
 import sys
 import tempfile
@@ -29,6 +44,8 @@ sys.path.insert(0, ROOT)
 
 METRIC = "path_x_alignment_checks_per_sec"
 UNIT = "checks/s"
+# the committed capture the roofline falls back to when no live ncu run is possible
+FALLBACK_CAPTURE = "profiles/r02_score_bitset_ncu_counters.json"
 
 
 def measured_peak_gbs():
@@ -80,7 +97,10 @@ class ClockSampler(threading.Thread):
 
 # ---- reference / CPU baselines -----------------------------------------------------------------
 
-def reference_sample(workdir: str, A: int = 20000):
+REF_SAMPLE_A, REF_SAMPLE_M = 20000, 60
+
+
+def reference_sample(workdir: str, A: int = REF_SAMPLE_A):
     """Text files of a bounded cfg3 sample for the reference CLI."""
     from gfalign_b200 import synth
     w = synth.make_workload("cfg3", A=A)
@@ -108,6 +128,12 @@ def time_reference_cli(binary: str, gfa: str, gaf: str, nl: str, t, m_steps: int
     return max(full - load, 1e-9), calls, load
 
 
+REF_WORKLOAD = ("cfg3 HiFi tangle (200 nodes, 1M alignments) — EXTRAPOLATED SAMPLE: the reference CLI runs "
+                f"on a {REF_SAMPLE_A}-alignment subsample (2% of the table) with `search -m {REF_SAMPLE_M}`; its "
+                "cost per check is flat in A (one loop over the alignments per evaluatePath call, "
+                "src/eval.cpp:80-99), so checks/s carries over, paths/s scales with 1/A")
+
+
 def run_reference_arm(args):
     """--impl reference: the UNMODIFIED reference CLI (oracle/_ref/gfalign, built by
     oracle/Makefile from the reference sources) on a bounded cfg3 sample; its hot path is
@@ -118,8 +144,8 @@ def run_reference_arm(args):
         return
     from oracle import binding
     binary = binding.ref_binary()
-    A_s, m_steps = 20000, 60
-    rates = []
+    A_s, m_steps = REF_SAMPLE_A, REF_SAMPLE_M
+    rates, prates = [], []
     with tempfile.TemporaryDirectory() as wd:
         w, gfa, gaf, nl = reference_sample(wd, A_s)
         t = w.tangle
@@ -131,6 +157,7 @@ def run_reference_arm(args):
                 sec, calls, _ = time_reference_cli(binary, gfa, gaf, nl, t, m_steps)
                 if i >= args.warmup:
                     rates.append(calls * A_s / sec)
+                    prates.append(calls / sec)
             ms = 1e3 * calls * A_s / np.mean(rates)
         else:
             from gfalign_b200 import synth
@@ -144,28 +171,33 @@ def run_reference_arm(args):
                 sec = time.perf_counter() - t0
                 if i >= args.warmup:
                     rates.append(64 * A_s / sec)
+                    prates.append(64 / sec)
             ms = 1e3 * 64 * A_s / np.mean(rates)
     value = float(np.mean(rates))
     line = {"metric": METRIC, "value": value, "unit": UNIT, "impl": "reference",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
             "data": "synthetic",
-            "config": {"workload": "cfg3 HiFi tangle (200 nodes, 1M alignments) — bounded sample",
-                       "sample": sample},
+            "config": {"workload": REF_WORKLOAD, "sample": sample, "extrapolated": True,
+                       "alignments_sample": A_s, "alignments_named_config": 1_000_000},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
                              "sample": sample},
+            "search_paths_per_s": {"sample": float(np.mean(prates)), "alignments_sample": A_s,
+                                   "extrapolated_to_1M_alignments": float(np.mean(prates)) * A_s / 1e6},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
 
 
-def cpu_baseline_block():
+def cpu_baseline_block(workload=None):
     """cpu_baseline of the default run: reference CLI on a bounded sample (kind=reference), with
-    the oracle port's 1-thread and all-core rates on the same sample alongside."""
+    the oracle port's 1-thread and all-core rates on the same sample AND on the GPU arm's own CSR
+    and paths (`same_inputs_port`) alongside."""
     from oracle import binding
     from gfalign_b200 import synth
-    A_s, m_steps = 20000, 60
+    A_s, m_steps = REF_SAMPLE_A, REF_SAMPLE_M
     out = {}
+    cores = os.cpu_count() or 1
     with tempfile.TemporaryDirectory() as wd:
         w, gfa, gaf, nl = reference_sample(wd, A_s)
         t = w.tangle
@@ -175,21 +207,246 @@ def cpu_baseline_block():
         t0 = time.perf_counter()
         orc.evaluate_paths(po, ps, w.offsets, w.steps, True, 1)
         port1 = 32 * A_s / (time.perf_counter() - t0)
-        cores = os.cpu_count() or 1
         t0 = time.perf_counter()
         orc.evaluate_paths(po, ps, w.offsets, w.steps, True, cores)
         portn = 32 * A_s / (time.perf_counter() - t0)
         if binary:
             sec, calls, load = time_reference_cli(binary, gfa, gaf, nl, t, m_steps)
             out = {"value": calls * A_s / sec, "unit": UNIT, "cores": 1, "kind": "reference",
-                   "sample": f"cfg3 subsample A={A_s} (2% of 1M), unmodified reference CLI "
+                   "sample": f"EXTRAPOLATED: cfg3 subsample A={A_s} (2% of 1M), unmodified reference CLI "
                              f"`search -j 1 -m {m_steps}`: {calls} evaluatePath calls in {sec:.2f} s "
-                             f"(wall minus {load:.2f} s load); hot path is single-threaded"}
+                             f"(wall minus {load:.2f} s load); hot path is single-threaded; checks/s is flat "
+                             "in A (one pass over the alignments per call)",
+                   "search_paths_per_s": {"sample": calls / sec, "alignments_sample": A_s,
+                                          "extrapolated_to_1M_alignments": calls / sec * A_s / 1e6}}
         else:
             out = {"value": portn, "unit": UNIT, "cores": cores, "kind": "port",
                    "sample": f"cfg3 subsample A={A_s}, 32 candidate paths, oracle port"}
         out["port_1core"] = port1
         out["port_allcores"] = {"value": portn, "cores": cores}
+    if workload is not None:
+        off, steps, po, pst, k = workload
+        sel_o = np.zeros(k + 1, dtype=np.uint32)
+        sel_o[1:] = np.cumsum(np.diff(po[:k + 1].astype(np.int64)))
+        sel_s = pst[:int(po[k])]
+        t0 = time.perf_counter()
+        orc.evaluate_paths(sel_o, sel_s, off, steps, True, cores)
+        dt = time.perf_counter() - t0
+        out["same_inputs_port"] = {"value": k * (off.size - 1) / dt, "unit": UNIT, "cores": cores, "kind": "port",
+                                   "sample": f"oracle port, all cores, the GPU arm's own CSR (A={off.size - 1}) and "
+                                             f"its first {k} candidate paths ({dt:.2f} s)"}
+    return out
+
+
+# ---- helpers of the GPU arm -----------------------------------------------------------------------
+
+def parity_check(orc, eng, off, steps, po, pst, pick, summed_rows, dist, dev, threads, exchange_name):
+    """k candidate paths against the CPU oracle over EVERY rank's shard: each rank runs the oracle on
+    its own shard (counts are sums over alignments, src/eval.cpp:80-99, so the oracle over the union is
+    the sum of the per-shard oracles), the oracle counts are summed over the ranks and compared on
+    every rank with `summed_rows` (what the exchange delivered for those paths)."""
+    import torch
+    k = len(pick)
+    so = np.zeros(k + 1, dtype=np.uint32)
+    ss = []
+    for i, p in enumerate(pick):
+        ss.append(pst[po[p]:po[p + 1]])
+        so[i + 1] = so[i] + ss[-1].size
+    t0 = time.perf_counter()
+    want = orc.evaluate_paths(so, np.concatenate(ss), off, steps, True, threads).astype(np.int64)
+    sec = time.perf_counter() - t0
+    tw = torch.from_numpy(want).to(dev)
+    if dist is not None:
+        dist.all_reduce(tw)
+    want = tw.cpu().numpy()
+    ok = bool(np.array_equal(want, summed_rows.astype(np.int64)))
+    t_ok = torch.tensor([1 if ok else 0], device=dev)
+    if dist is not None:
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+    return {"paths": k, "path_ids": [int(p) for p in pick], "ok": bool(t_ok.item()),
+            "checked_against": "CPU oracle (oracle/liboracle.so) over every rank's shard, summed",
+            "exchange": exchange_name, "oracle_seconds": sec, "oracle_threads": threads,
+            "bad_good_of_first": want[0].tolist()}
+
+
+NCU_METRICS = ("dram__bytes_read.sum,dram__bytes_write.sum,smsp__inst_executed.sum,"
+               "smsp__issue_active.avg.pct_of_peak_sustained_elapsed,"
+               "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_elapsed,"
+               "sm__warps_active.avg.pct_of_peak_sustained_active,gpu__time_duration.sum")
+
+
+def ncu_counters(args):
+    """Counters of ONE launch of the dominant kernel from a live `ncu --metrics` child run of this very
+    script (`--counters-child`: same workload, a few steps, nothing timed).  Durations printed under ncu
+    are not used.  -> (dict, source string) or (None, reason)."""
+    ncu = shutil.which("ncu") or ("/usr/local/cuda/bin/ncu" if os.path.exists("/usr/local/cuda/bin/ncu") else None)
+    if not ncu or os.environ.get("GFE_BENCH_NO_NCU"):
+        return None, "ncu not available"
+    cmd = [ncu, "--metrics", NCU_METRICS, "--clock-control", "none", "-k", "regex:score_bitset", "-s", "3",
+           "-c", "1", "--csv", sys.executable, os.path.abspath(__file__), "--counters-child", "--paths",
+           str(args.paths)] + (["--alignments", str(args.alignments)] if args.alignments else [])
+    try:
+        p = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT,
+                           env=dict(os.environ, GFE_BENCH_NO_NCU="1"))
+    except Exception as ex:   # noqa: BLE001
+        return None, f"ncu child failed: {ex!r}"[:200]
+    rows = [r for r in csv.reader(io.StringIO(p.stdout)) if len(r) > 3]
+    if not rows or "Metric Name" not in rows[0]:
+        hdr = [i for i, r in enumerate(rows) if "Metric Name" in r]
+        if not hdr:
+            return None, ("ncu produced no metric table: " + (p.stderr or p.stdout)[-200:].replace("\n", " "))
+        rows = rows[hdr[0]:]
+    h = rows[0]
+    ni, ui, vi = h.index("Metric Name"), h.index("Metric Unit"), h.index("Metric Value")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "inst": 1.0, "%": 1.0, "": 1.0,
+             "nsecond": 1e-9, "usecond": 1e-6, "msecond": 1e-3, "second": 1.0, "warp": 1.0}
+    out = {}
+    for r in rows[1:]:
+        try:
+            out[r[ni]] = float(r[vi].replace(",", "")) * scale.get(r[ui], 1.0)
+        except ValueError:
+            pass
+    if "smsp__inst_executed.sum" not in out:
+        return None, "ncu output lacks smsp__inst_executed.sum"
+    return out, "ncu --metrics child run of this bench (live, this box)"
+
+
+def counters_child(args):
+    """The workload of the timed region, a few steps, under ncu (see ncu_counters)."""
+    import torch
+    import gfalign_b200
+    from gfalign_b200 import synth
+    t = synth.make_tangle(200, 200, seed=1, minus_frac=0.05, count2_frac=0.05)
+    A = args.alignments or 1_000_000
+    off, steps = synth.random_walk_alignments(t.n_nodes, t.edge_from, t.edge_to, A, *synth.HIFI_LENGTHS, seed=11)
+    nodes, _, _ = synth.node_table(t)
+    po, pst = synth.candidate_paths(t, args.paths, seed=5)
+    eng = gfalign_b200.Engine(0)
+    eng.set_alignments(off, steps, t.n_nodes)
+    eng.set_universe(nodes)
+    dev = torch.device("cuda", 0)
+    d_po = torch.from_numpy(po.astype(np.int64)).to(dev).to(torch.int32)
+    d_ps = torch.from_numpy(pst.astype(np.int64)).to(dev).to(torch.int32)
+    d_counts = torch.zeros(args.paths * 2, dtype=torch.int32, device=dev)
+    flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    for _ in range(5):
+        flush.zero_()
+        eng.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), args.paths, int(pst.size), d_counts.data_ptr(),
+                               filter=True, stream=0)
+    torch.cuda.synchronize()
+    eng.close()
+
+
+def strong_cfg5(args, rank, world, local, dist, dev, orc, flush):
+    """BASELINE configs[4]: 400-node dense ONT tangle, 50 M alignments split over the N ranks (N = 1: the
+    whole table on one GPU), P candidate paths per step, exchange inside the timed step."""
+    import torch
+    import gfalign_b200
+    from gfalign_b200 import synth
+    from gfalign_b200.sharded import PeerExchange
+    A_total = args.cfg5_alignments
+    A = A_total // world
+    P = args.cfg5_paths
+    t = synth.make_tangle(400, 800, seed=3, minus_frac=0.05, count2_frac=0.10)
+    nodes, counts, node_count = synth.node_table(t)
+    t0 = time.perf_counter()
+    d_off, d_st = synth.random_walk_alignments_device(t.n_nodes, t.edge_from, t.edge_to, A, *synth.ONT_LENGTHS,
+                                                      seed=1300 + rank, device=dev)
+    torch.cuda.synchronize(dev)
+    gen_s = time.perf_counter() - t0
+    S = int(d_off[-1].item())
+    po, pst = synth.candidate_paths(t, P, seed=5)
+    eng = gfalign_b200.Engine(local)
+    eng.set_alignments_device(d_off.data_ptr(), d_st.data_ptr(), A, S, t.n_nodes)
+    eng.set_universe(nodes)
+    d_po = torch.from_numpy(po.astype(np.int64)).to(dev).to(torch.int32)
+    d_ps = torch.from_numpy(pst.astype(np.int64)).to(dev).to(torch.int32)
+    d_counts = torch.zeros(P * 2, dtype=torch.int32, device=dev)
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    px = None
+    if dist is not None:
+        try:
+            px = PeerExchange(P * 2, dev)
+        except Exception as ex:   # noqa: BLE001
+            sys.stderr.write(f"[bench cfg5] peer exchange unavailable ({ex!r}); using NCCL\n")
+
+    def step():
+        if px is not None:
+            eng.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), P, int(pst.size), px.half_ptr(),
+                                   filter=True, stream=stream)
+            px.sum_into(d_counts.data_ptr(), P * 2, stream)
+            return
+        eng.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), P, int(pst.size), d_counts.data_ptr(),
+                               filter=True, stream=stream)
+        if dist is not None:
+            dist.all_reduce(d_counts)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    steps_k = max(3, min(args.steps, 5))
+    for _ in range(3):
+        flush.zero_()
+        step()
+    barrier()
+    assert eng.device_status() == 0, "cfg5: device flags raised (worklist overflow / bad path)"
+    eng.set_timing(True)
+    eng.kernel_time_stats()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps_k)]
+    c0 = eng.counters()
+    barrier()
+    for k in range(steps_k):
+        flush.zero_()
+        ev[k][0].record()
+        step()
+        ev[k][1].record()
+    barrier()
+    k1_ms, k1_n = eng.kernel_time_stats()
+    eng.set_timing(False)
+    c1 = eng.counters()
+    assert eng.device_status() == 0, "cfg5: device flags raised in the timed region"
+    total_ms = float(sum(a.elapsed_time(b) for a, b in ev))
+    tm = torch.tensor([total_ms, k1_ms / max(k1_n, 1)], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+    total_ms, k1_mean = float(tm[0].item()), float(tm[1].item())
+    # exchange alone (peer kernel incl. the wait for the slowest rank, nothing to wait for here)
+    ex_ms = None
+    if px is not None:
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            px.sum_into(d_counts.data_ptr(), P * 2, stream)
+        e1.record()
+        torch.cuda.synchronize(dev)
+        ex_ms = e0.elapsed_time(e1) / 20
+        step()          # leave d_counts holding real sums again
+        barrier()
+    # oracle spot check over all shards
+    off_h = d_off.cpu().numpy().view(np.uint32)
+    st_h = d_st.cpu().numpy().view(np.uint32)
+    pick = np.linspace(0, P - 1, 3).astype(int)
+    got = d_counts.cpu().numpy().view(np.uint32).reshape(P, 2)[pick]
+    par = parity_check(orc, eng, off_h, st_h, po, pst, pick, got, dist, dev,
+                       max(1, (os.cpu_count() or 1) // world),
+                       "peer-memory sum kernel" if px is not None else ("nccl all-reduce" if dist is not None else "none"))
+    ms_step = total_ms / steps_k
+    out = {"workload": "cfg5 synthetic dense ONT tangle: 400 nodes, 50M alignments split over the GPUs "
+                       "(table drawn on the device, seed 1300 + rank)",
+           "A_total": A * world, "alignments_per_gpu": A, "mean_steps": S / A, "candidate_paths_per_step": P,
+           "n_gpus": world, "steps": steps_k, "ms_per_step": ms_step,
+           "checks_per_s": float(P) * A * world / (ms_step * 1e-3), "k1_ms": k1_mean,
+           "worklist_and_launch_ms": ms_step - k1_mean - (ex_ms or 0.0), "exchange_ms": ex_ms,
+           "slow_pairs_per_step": None, "exact_pairs_per_step": int(c1["exact_pairs"] - c0["exact_pairs"]) // steps_k,
+           "synth_seconds": gen_s, "parity_check": par, "scaling": "strong",
+           "l2": "flushed (512 MiB write) before every timed step"}
+    eng.close()
+    del d_off, d_st
+    if not par["ok"]:
+        raise SystemExit("cfg5 parity check failed: " + json.dumps(par))
     return out
 
 
@@ -201,21 +458,32 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="cfg3", choices=["cfg3", "cfg5"])
     ap.add_argument("--paths", type=int, default=1024, help="candidate paths per step")
     ap.add_argument("--alignments", type=int, default=0, help="override A per GPU (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-search", action="store_true")
+    ap.add_argument("--search-steps", type=int, default=100000)
+    ap.add_argument("--no-extras", action="store_true", help="skip the cfg4 block (N = 1)")
+    ap.add_argument("--extras-alignments", type=int, default=20_000_000)
+    ap.add_argument("--no-cfg5", action="store_true", help="skip the cfg5 strong-scaling block")
+    ap.add_argument("--cfg5-alignments", type=int, default=50_000_000)
+    ap.add_argument("--cfg5-paths", type=int, default=1024)
+    ap.add_argument("--no-ncu", action="store_true")
+    ap.add_argument("--counters-child", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
     if args.impl == "reference":
         run_reference_arm(args)
         return
+    if args.counters_child:
+        counters_child(args)
+        return
 
     import torch
     import gfalign_b200
     from gfalign_b200 import synth
+    from oracle.binding import Oracle   # the checker of parity_check / cpu_baseline only
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -236,19 +504,14 @@ def main():
         os.dup2(2, 1)
         sys.stdout = _real
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    orc = Oracle()
+    cores = os.cpu_count() or 1
 
-    # workload: every rank builds the same tangle and its own alignment shard (seed + rank)
-    if args.workload == "cfg3":
-        t = synth.make_tangle(200, 200, seed=1, minus_frac=0.05, count2_frac=0.05)
-        A = args.alignments or 1_000_000
-        ls, ps_ = synth.HIFI_LENGTHS
-        desc = "cfg3 synthetic HiFi tangle: 200-node utig4 nodelist, 1M q60 alignments per GPU"
-    else:
-        t = synth.make_tangle(400, 800, seed=3, minus_frac=0.05, count2_frac=0.10)
-        A = args.alignments or (50_000_000 // world)
-        ls, ps_ = synth.ONT_LENGTHS
-        desc = "cfg5 synthetic dense ONT tangle: 400 nodes, 50M alignments split over the GPUs"
-    off, steps = synth.random_walk_alignments(t.n_nodes, t.edge_from, t.edge_to, A, ls, ps_,
+    # workload (headline): every rank builds the same tangle and its own alignment shard (seed + rank)
+    t = synth.make_tangle(200, 200, seed=1, minus_frac=0.05, count2_frac=0.05)
+    A = args.alignments or 1_000_000
+    desc = "cfg3 synthetic HiFi tangle: 200-node utig4 nodelist, 1M q60 alignments per GPU"
+    off, steps = synth.random_walk_alignments(t.n_nodes, t.edge_from, t.edge_to, A, *synth.HIFI_LENGTHS,
                                               seed=11 + rank)
     nodes, counts, node_count = synth.node_table(t)
     po, pst = synth.candidate_paths(t, args.paths, seed=5)
@@ -272,7 +535,7 @@ def main():
 
     # the exchange step of the sharded path: one peer-memory kernel per rank (csrc/peer.cu) reading
     # every shard's record over NVLink; GFE_EXCHANGE=nccl selects a NCCL all-reduce instead
-    px = None
+    px = px_e2e = None
     exchange = "none"
     if dist is not None:
         exchange = "nccl all-reduce"
@@ -280,12 +543,14 @@ def main():
             try:
                 from gfalign_b200.sharded import PeerExchange
                 px = PeerExchange(P * 2, dev)
+                px_e2e = PeerExchange(max(P, 4096) * 2 + 1, dev)
                 exchange = "peer-memory sum kernel (NVLink P2P loads)"
             except Exception as ex:   # no peer access between the GPUs of this box
                 sys.stderr.write(f"[bench] peer exchange unavailable ({ex!r}); using NCCL\n")
+                px = px_e2e = None
 
-    def step():
-        if px is not None:
+    def step(use_px=True):
+        if px is not None and use_px:
             eng.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), P, int(pst.size),
                                    px.half_ptr(), filter=True, stream=stream)
             px.sum_into(d_counts.data_ptr(), P * 2, stream)
@@ -305,6 +570,22 @@ def main():
         step()
     barrier()
     ref_counts = d_counts.clone()
+
+    # ---- parity: the configuration about to be timed, against the CPU oracle, on every rank's shard ----
+    pick = np.linspace(0, P - 1, 4).astype(int)
+    got = ref_counts.cpu().numpy().view(np.uint32).reshape(P, 2)
+    parity = parity_check(orc, eng, off, steps, po, pst, pick, got[pick], dist, dev, max(1, cores // world),
+                          exchange)
+    if dist is not None:
+        step(use_px=False)                       # the same batch through NCCL
+        barrier()
+        same = bool(torch.equal(ref_counts, d_counts))
+        parity["nccl_exchange_equals_peer_exchange"] = same
+        parity["ok"] = parity["ok"] and same
+        step()
+        barrier()
+    if not parity["ok"]:
+        raise SystemExit("parity check failed: " + json.dumps(parity))
 
     # ---- timed region: K steps, device-timed, L2 flushed between steps -------------------------
     sampler = ClockSampler(local)
@@ -328,6 +609,7 @@ def main():
     c1 = eng.counters()
     sampler.stop_flag.set()
     sampler.join()
+    clocks = sampler.summary()
     step_ms = [a.elapsed_time(b) for a, b in ev]
     total_ms = float(sum(step_ms))
     t_max = torch.tensor([total_ms], dtype=torch.float64, device=dev)
@@ -339,29 +621,55 @@ def main():
     checks_per_step = float(P) * A * world
     value = checks_per_step * args.steps / (total_ms * 1e-3)
 
-    # ---- roofline of the dominant kernel (score_paths) -----------------------------------------
+    # ---- roofline of the dominant kernel -----------------------------------------------------------
     peak, peak_src = measured_peak_gbs()
     k1_ms = kern_ms / max(kern_n, 1)
     alg_bytes = float(P) * A * bytes_per_check
-    achieved = alg_bytes / (k1_ms * 1e-3) / 1e9
     legacy = os.environ.get("GFE_FORCE_LEGACY") == "1"
-    # dram__bytes_read+write of ONE launch from the committed ncu --set full capture of this command
-    # (profiles/r01_score_bitset_ncu_full_summary.csv; cfg3, P = 1024): 20.41 MB read
-    traffic = 20.41e6 if (args.workload == "cfg3" and P == 1024 and A == 1_000_000 and not legacy) else None
-    # the limiter of the bitset kernel is the SM (integer ALU pipe 70 % busy, issue slots 61 %), not HBM:
-    # warp instructions per launch from the same capture (1.1e8) vs 4 issue slots/clk/SM
-    sm_clock = 1.965e9
-    roofline = {"bound": "hbm", "kernel": "score_paths_kernel" if legacy else "score_bitset_kernel",
-                "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "peak_source": peak_src, "kernel_ms": k1_ms, "kernel_launches_timed": kern_n,
-                "algorithmic_bytes_per_launch": alg_bytes,
-                "note": "algorithmic bytes = P x A x 4(m+1) (SURVEY.md 8d); one pass over the table "
-                        "serves every path of a chunk from shared-memory bitsets, so DRAM traffic "
-                        "is ~1/1000 of it and frac > 1; the kernel is integer-ALU/issue bound "
-                        "(DESIGN.md 4)",
-                "issue_bound": {"checks_per_sm_clock": float(P) * A / (k1_ms * 1e-3) / (eng_sms * sm_clock),
-                                "sms": eng_sms, "sm_clock_hz": sm_clock}}
+    ctr, ctr_src = (None, "skipped")
+    if rank == 0 and world == 1 and not args.no_ncu and not legacy:
+        ctr, ctr_src = ncu_counters(args)
+    if ctr is None:
+        try:
+            with open(os.path.join(ROOT, FALLBACK_CAPTURE)) as f:
+                cap = json.load(f)
+            if cap.get("paths") == P and cap.get("alignments") == A and not legacy:
+                ctr, ctr_src = cap["counters"], f"{FALLBACK_CAPTURE} (commit {cap.get('commit', '?')}); live ncu: {ctr_src}"
+        except Exception:
+            pass
+    sm_hz = (clocks["sm_mhz"] or 1965.0) * 1e6
+    issue_peak = eng_sms * 4 * sm_hz                      # 4 schedulers per SM, one warp instruction per clock each
+    roofline = {"kernel": "score_paths_kernel" if legacy else "score_bitset_kernel", "kernel_ms": k1_ms,
+                "kernel_launches_timed": kern_n, "counters_source": ctr_src}
+    hbm = {"algorithmic_bytes_per_launch": alg_bytes, "algorithmic_gbs": alg_bytes / (k1_ms * 1e-3) / 1e9,
+           "algorithmic_frac": alg_bytes / (k1_ms * 1e-3) / 1e9 / peak, "peak": peak, "peak_source": peak_src,
+           "note": "algorithmic bytes = P x A x 4(m+1) (SURVEY.md 8d: one row read per check); one pass over the "
+                   "rows serves all P paths from shared-memory bitsets (P-way reuse), so the algorithmic figure "
+                   "exceeds the HBM peak and is not a bound; frac_actual is the DRAM traffic the kernel really moves"}
+    if ctr is not None:
+        inst = float(ctr["smsp__inst_executed.sum"])
+        traffic = float(ctr.get("dram__bytes_read.sum", 0.0)) + float(ctr.get("dram__bytes_write.sum", 0.0))
+        roofline.update({"bound": "issue (integer ALU)", "achieved": inst / (k1_ms * 1e-3), "peak": issue_peak,
+                         "unit": "warp-inst/s", "frac": inst / (k1_ms * 1e-3) / issue_peak, "traffic": traffic,
+                         "warp_instructions_per_launch": inst, "warp_instructions_per_row": inst / A / max(1, (P + 1023) // 1024),
+                         "issue_active_pct": ctr.get("smsp__issue_active.avg.pct_of_peak_sustained_elapsed"),
+                         "alu_pipe_active_pct": ctr.get("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_elapsed"),
+                         "warps_active_pct": ctr.get("sm__warps_active.avg.pct_of_peak_sustained_active"),
+                         "peak_definition": f"{eng_sms} SMs x 4 schedulers x {sm_hz / 1e6:.0f} MHz (clock sampled "
+                                            "during the timed region)"})
+        hbm["traffic"] = traffic
+        hbm["frac_actual"] = traffic / (k1_ms * 1e-3) / 1e9 / peak
+        # one pass over the length-bucketed 16-bit view (row_stride(m) u16 per row, kernels.cuh)
+        m_all = np.diff(off.astype(np.int64))
+        stride = np.where(m_all <= 0, 0, (2 * m_all - 1 + np.where(m_all > 2, (m_all - 1) // 2, 0) + 3) & ~3)
+        view_bytes = float((stride * 2).sum())
+        hbm["one_table_pass_bytes"] = view_bytes
+        hbm["traffic_over_one_table_pass"] = traffic / view_bytes * max(1, 1) / max(1, (P + 1023) // 1024)
+    else:
+        roofline.update({"bound": "issue (integer ALU)", "achieved": None, "peak": issue_peak, "unit": "warp-inst/s",
+                         "frac": None, "traffic": None})
+    roofline["hbm"] = hbm
+    roofline["checks_per_sm_clock"] = float(P) * A / (k1_ms * 1e-3) / (eng_sms * sm_hz)
 
     # single-path launches: the streaming (HBM/L2-bound) regime of the non-speculative driver
     d_c1 = torch.zeros(2, dtype=torch.int32, device=dev)
@@ -380,23 +688,32 @@ def main():
     ms1, n1 = eng.kernel_time_stats()
     eng.set_timing(False)
     p1_ms = ms1 / max(n1, 1)
-    roofline["single_path_launch"] = {"kernel_ms": p1_ms,
-                                      "achieved": A * bytes_per_check / (p1_ms * 1e-3) / 1e9,
-                                      "frac": A * bytes_per_check / (p1_ms * 1e-3) / 1e9 / peak,
-                                      "note": "P=1, L2 flushed before every launch"}
+    roofline["single_path_launch"] = {"bound": "hbm", "kernel_ms": p1_ms,
+                                      "achieved": A * bytes_per_check / (p1_ms * 1e-3) / 1e9, "peak": peak,
+                                      "unit": "GB/s", "frac": A * bytes_per_check / (p1_ms * 1e-3) / 1e9 / peak,
+                                      "note": "P=1 (no reuse: here 4(m+1) B per check IS the traffic), L2 flushed "
+                                              "before every launch"}
 
     # ---- e2e: the host C-ABI call with host buffers (H2D paths, D2H counts every step) ----------
+    cx = px_e2e.c_exchange() if px_e2e is not None else None
+
+    def e2e_call():
+        if cx is not None:
+            return eng.score_paths_sharded(cx, po, pst, filter=True)       # ONE C call: H2D, kernels, peer sum, D2H
+        g = eng.score_paths(po, pst, filter=True)
+        if dist is not None:
+            tcount = torch.from_numpy(g.astype(np.int64)).to(dev)
+            dist.all_reduce(tcount)
+            g = tcount.cpu().numpy()
+        return g
+
     for _ in range(3):
-        eng.score_paths(po, pst, filter=True)
+        e2e_call()
     c_e0 = eng.counters()
     barrier()
     e0 = time.perf_counter()
     for _ in range(args.steps):
-        got = eng.score_paths(po, pst, filter=True)
-        if dist is not None:
-            tcount = torch.from_numpy(got.astype(np.int64)).to(dev)
-            dist.all_reduce(tcount)
-            got = tcount.cpu().numpy()
+        got_e = e2e_call()
     barrier()
     e_sec = time.perf_counter() - e0
     c_e1 = eng.counters()
@@ -407,11 +724,16 @@ def main():
     e2e = {"value": checks_per_step * args.steps / e_sec, "unit": UNIT,
            "h2d_bytes_per_step": (c_e1["h2d_bytes"] - c_e0["h2d_bytes"]) // args.steps,
            "d2h_bytes_per_step": (c_e1["d2h_bytes"] - c_e0["d2h_bytes"]) // args.steps,
-           "call": "gfe_score_paths(host path CSR) -> host counts; alignment table resident",
+           "call": ("gfe_score_paths_sharded(host path CSR) -> summed host counts: kernels accumulate into the "
+                    "exchange buffer, peer kernel sums the shards, one D2H; alignment shards resident"
+                    if cx is not None else
+                    "gfe_score_paths(host path CSR) -> host counts; alignment table resident"
+                    + (" + NCCL all-reduce of the counts" if dist is not None else "")),
            "slow_pairs_per_step": int(c_e1["slow_pairs"] - c_e0["slow_pairs"]) // args.steps,
            "exact_pairs_per_step": int(c_e1["exact_pairs"] - c_e0["exact_pairs"]) // args.steps}
-    assert np.array_equal(got.reshape(-1).astype(np.int64),
+    assert np.array_equal(np.asarray(got_e).reshape(-1).astype(np.int64),
                           d_counts.cpu().numpy().astype(np.int64)), "host and device API disagree"
+    parity["e2e_call_equals_device_path"] = True
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
@@ -422,29 +744,75 @@ def main():
                        "l2": "flushed (512 MiB write) before every timed step",
                        "parallelism": f"alignment shards x{world}, counts summed by {exchange}"
                        if world > 1 else "single GPU"},
-            "clocks": sampler.summary(), "e2e": e2e, "roofline": roofline,
+            "clocks": clocks, "e2e": e2e, "roofline": roofline, "parity_check": parity,
             "gpu_launches": int(c1["kernel_launches"] - c0["kernel_launches"]) + (args.steps if px is not None else 0),
             "wall_ms_timed_region": wall * 1e3,
             "exact_dp_pairs_per_step": int(c1["exact_pairs"] - c0["exact_pairs"]) // args.steps}
 
-    if rank == 0 and not args.no_search and world == 1:
-        # the `gfalign search` driver itself, table upload included: search paths/s
+    # ---- the `gfalign search` driver itself: search paths/s -------------------------------------------
+    if not args.no_search:
+        m_steps = args.search_steps if world == 1 else min(args.search_steps, 20000)
         with gfalign_b200.Engine(local) as e2:
+            barrier()
             s0 = time.perf_counter()
             e2.set_alignments(off, steps, t.n_nodes)
-            rows, st = e2.search(t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source,
-                                 t.destination, nodes, counts, node_count, max_steps=2000)
+            up_s = time.perf_counter() - s0
+            if cx is not None:
+                rows, st = e2.search_sharded(cx, t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source,
+                                             t.destination, nodes, counts, node_count, max_steps=m_steps)
+            else:
+                rows, st = e2.search(t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source,
+                                     t.destination, nodes, counts, node_count, max_steps=m_steps)
             s_sec = time.perf_counter() - s0
-        line["search"] = {"max_steps": 2000, "seconds": s_sec, "evaluatePath_calls": st["evaluations"],
-                          "paths_per_s": st["evaluations"] / s_sec,
-                          "checks_per_s": st["evaluations"] * A / s_sec,
-                          "kernel_batches": st["kernel_batches"], "paths_scored": st["paths_scored"],
-                          "rows": len(rows), "seconds_scoring": st["seconds_scoring"]}
+        ts = torch.tensor([s_sec], dtype=torch.float64, device=dev)
+        sig = torch.tensor([len(rows), sum(r.bad * 31 + r.good for r in rows) % (1 << 31)], dtype=torch.int64, device=dev)
+        rows_agree = True
+        if dist is not None:
+            dist.all_reduce(ts, op=dist.ReduceOp.MAX)
+            lo, hi = sig.clone(), sig.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            rows_agree = bool(torch.equal(lo, hi))
+        s_sec = float(ts.item())
+        srch = {"max_steps": m_steps, "seconds": s_sec, "seconds_table_upload": up_s,
+                "seconds_search_loop": st["seconds_total"], "evaluatePath_calls": st["evaluations"],
+                "paths_per_s": st["evaluations"] / st["seconds_total"],
+                "paths_per_s_incl_upload": st["evaluations"] / s_sec,
+                "effective_checks_per_s": st["evaluations"] * float(A) * world / st["seconds_total"],
+                "kernel_batches": st["kernel_batches"], "paths_scored": st["paths_scored"],
+                "speculation_hit_rate": st["evaluations"] / max(st["paths_scored"], 1),
+                "rows": len(rows), "seconds_scoring": st["seconds_scoring"],
+                "alignments_total": A * world, "rows_identical_on_all_ranks": rows_agree,
+                "note": "search paths/s = evaluatePath calls the reference's dijkstra() would make (heap replay is "
+                        "exact) / seconds of the search loop; reported separately from brute-force checks/s"}
+        if not rows_agree:
+            raise SystemExit("search rows differ between ranks")
+        line["search"] = srch
+
+    # ---- BASELINE configs[4]: cfg5, 50 M alignments split over the ranks -------------------------------
+    eng.close()
+    del flush
+    torch.cuda.empty_cache()
+    flush = torch.empty(512 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    if not args.no_cfg5:
+        line["strong_cfg5"] = strong_cfg5(args, rank, world, local, dist, dev, orc, flush)
+    # ---- BASELINE configs[3]: cfg4 kernels (N = 1) ---------------------------------------------------------
+    if rank == 0 and world == 1 and not args.no_extras:
+        import bench_extras
+        line["extras"] = bench_extras.run_cfg4(local, args.extras_alignments, 5, not args.no_cpu_baseline, flush=flush)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline_block()
+        cb = cpu_baseline_block((off, steps, po, pst, 4))
+        line["cpu_baseline"] = cb
+        # BASELINE.md publishes no number for this metric: vs_baseline stays null (contract); the ratio to the
+        # same-run reference CLI sample is given beside it, labelled
+        line["vs_reference_sample"] = {"value": value / cb["value"], "note": "value / cpu_baseline.value; the reference "
+                                       f"ran a {REF_SAMPLE_A}-alignment sample (extrapolated, see cpu_baseline.sample)"}
+        if "search" in line and "search_paths_per_s" in cb:
+            line["search"]["reference_paths_per_s"] = cb["search_paths_per_s"]
     if rank == 0:
         print(json.dumps(line))
     if dist is not None:
+        dist.barrier()
         dist.destroy_process_group()
 
 

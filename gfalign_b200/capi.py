@@ -262,6 +262,7 @@ class Engine:
                               n_nodes: int):
         self._check(self._lib.gfe_set_alignments_device(self._h, d_offsets_ptr, d_steps_ptr, A,
                                                         total_steps, n_nodes))
+        self._A_hint = int(A)
 
     def set_universe(self, nodes):
         nodes = _u32(nodes)

@@ -255,3 +255,57 @@ def write_nodelist(path: str, t: Tangle):
     with open(path, "w") as f:
         for node, count in t.nodelist:
             f.write(f"{t.names[node]}\t{count}\n")
+
+
+# ---- full-size tables generated on the device (bench.py: cfg4 / cfg5) ---------------------------
+
+def random_walk_alignments_device(n_nodes: int, edge_from: np.ndarray, edge_to: np.ndarray, A: int,
+                                  lengths: Sequence[int], probs: Sequence[float], seed: int, device,
+                                  rc_frac: float = 0.5, chunk: int = 4_000_000):
+    """The same walks as random_walk_alignments (same rules: uniform oriented start, uniform
+    successor, cut at dead ends, `rc_frac` emitted reverse-complemented), drawn with torch on
+    `device` in chunks of rows -> (offsets int32[A+1], steps int32[S]) device tensors (bit patterns
+    of the uint32 CSR).  Deterministic for a given (seed, A, chunk) on one GPU model; NOT the same
+    stream of random numbers as the numpy generator."""
+    import torch
+    g = torch.Generator(device=device)
+    g.manual_seed(int(seed))
+    soff_np, sto_np = oriented_successors(n_nodes, edge_from, edge_to)
+    soff = torch.from_numpy(soff_np.astype(np.int64)).to(device)
+    sto = torch.from_numpy(sto_np.astype(np.int64)).to(device)
+    if sto.numel() == 0:
+        sto = torch.zeros(1, dtype=torch.int64, device=device)
+    deg = soff[1:] - soff[:-1]
+    lens = torch.tensor(list(lengths), dtype=torch.int64, device=device)
+    pr = torch.tensor(list(probs), dtype=torch.float32, device=device)
+    maxlen = int(max(lengths)) if A else 0
+    col = torch.arange(maxlen, device=device)[None, :]
+    got_all, step_chunks = [], []
+    for lo in range(0, A, chunk):
+        n = min(chunk, A - lo)
+        want = lens[torch.multinomial(pr, n, replacement=True, generator=g)]
+        cur = torch.randint(0, 2 * n_nodes, (n,), generator=g, device=device)
+        walk = torch.zeros((n, maxlen), dtype=torch.int64, device=device)
+        walk[:, 0] = cur
+        got = torch.ones(n, dtype=torch.int64, device=device)
+        alive = want > 1
+        for j in range(1, maxlen):
+            alive = alive & (deg[cur] > 0) & (want > j)
+            k = (torch.rand(n, generator=g, device=device) * deg[cur]).to(torch.int64)
+            k = torch.minimum(k, torch.clamp(deg[cur] - 1, min=0))
+            nxt = sto[torch.clamp(soff[cur] + k, max=sto.numel() - 1)]
+            cur = torch.where(alive, nxt, cur)
+            walk[:, j] = torch.where(alive, nxt, torch.zeros_like(nxt))
+            got += alive.to(torch.int64)
+        rc = torch.rand(n, generator=g, device=device) < rc_frac
+        src_col = torch.where(rc[:, None], got[:, None] - 1 - col, col).clamp_(0, max(maxlen - 1, 0))
+        out = torch.gather(walk, 1, src_col) ^ rc[:, None].to(torch.int64)
+        step_chunks.append(out[col < got[:, None]].to(torch.int32))
+        got_all.append(got)
+        del walk, out, src_col
+    got = torch.cat(got_all) if got_all else torch.zeros(0, dtype=torch.int64, device=device)
+    offsets = torch.zeros(A + 1, dtype=torch.int64, device=device)
+    offsets[1:] = torch.cumsum(got, 0)
+    assert int(offsets[-1]) < 2 ** 31
+    steps = torch.cat(step_chunks) if step_chunks else torch.zeros(0, dtype=torch.int32, device=device)
+    return offsets.to(torch.int32), steps
