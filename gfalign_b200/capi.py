@@ -62,6 +62,11 @@ class _SearchStats(C.Structure):
                 ("seconds_total", C.c_double)]
 
 
+class _PathBatch(C.Structure):
+    _fields_ = [("n_bases", C.c_uint32), ("base_offsets", _u32p), ("base_steps", _u32p), ("P", C.c_uint32),
+                ("item_base", _u32p), ("suffix_offsets", _u32p), ("suffix_steps", _u32p), ("mode", _u8p)]
+
+
 class _Counters(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("exact_pairs", C.c_uint64),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("slow_pairs", C.c_uint64)]
@@ -81,6 +86,7 @@ EXPORTS = [
     "gfe_text_open", "gfe_text_close", "gfe_text_get", "gfe_text_node_name", "gfe_text_node_id",
     "gfe_text_qname", "gfe_peer_sum_u32", "gfe_device_status_to",
     "gfe_exchange_create", "gfe_exchange_destroy", "gfe_score_paths_sharded", "gfe_search_sharded",
+    "gfe_score_paths_incremental",
 ]
 
 PEER_MAX = 16      # GFE_PEER_MAX
@@ -155,6 +161,7 @@ def load_library() -> C.CDLL:
     lib.gfe_device_status_to.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.gfe_peer_sum_u32.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_int, C.c_uint32, C.c_uint32,
                                      C.c_uint32, C.c_void_p, C.c_void_p]
+    lib.gfe_score_paths_incremental.argtypes = [C.c_void_p, C.POINTER(_PathBatch), _i32p]
     lib.gfe_exchange_create.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_int, C.c_uint32,
                                         C.POINTER(C.c_void_p)]
     lib.gfe_exchange_destroy.argtypes = [C.c_void_p]
@@ -277,6 +284,20 @@ class Engine:
         self._check(self._lib.gfe_score_paths(self._h, _ptr(po), _ptr(ps), P, int(filter),
                                               _ptr(counts)))
         return counts
+
+    def score_paths_incremental(self, base_offsets, base_steps, item_base, suffix_offsets, suffix_steps,
+                                mode) -> np.ndarray:
+        """gfe_score_paths_incremental: path i = bases[item_base[i]] ++ suffix i -> int32 (P, 4):
+        mode 0: bad, good over all alignments, then bad, good over the fresh set F;
+        mode 1: bad/good DIFFERENCE to the parent (path minus its last step) outside F, then F."""
+        bo, bs, ib = _u32(base_offsets), _u32(base_steps), _u32(item_base)
+        so, ss = _u32(suffix_offsets), _u32(suffix_steps)
+        md = np.ascontiguousarray(mode, dtype=np.uint8)
+        P = ib.size
+        out = np.zeros((max(P, 1), 4), dtype=np.int32)
+        b = _PathBatch(bo.size - 1, _ptr(bo), _ptr(bs), P, _ptr(ib), _ptr(so), _ptr(ss), _ptr(md, _u8p))
+        self._check(self._lib.gfe_score_paths_incremental(self._h, C.byref(b), _ptr(out, _i32p)))
+        return out[:P]
 
     def score_paths_sharded(self, exchange, path_offsets, path_steps, filter: bool = True) -> np.ndarray:
         """gfe_score_paths_sharded: (P, 2) counts summed over every rank's alignment shard."""

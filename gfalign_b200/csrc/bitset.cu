@@ -148,9 +148,12 @@ __device__ __forceinline__ void fill_slow_holes(uint2 *__restrict__ slow, uint32
 __device__ __noinline__ uint2 push_slow8(uint2 *__restrict__ slow, uint32_t *work_count,
                                          uint32_t slow_cap, uint2 win, uint32_t s0, uint32_t s1, uint32_t s2,
                                          uint32_t s3, uint32_t s4, uint32_t s5, uint32_t s6,
-                                         uint32_t s7, uint32_t word_base, uint32_t row_first,
-                                         uint32_t row_step, int lane) {
+                                         uint32_t s7, uint32_t word_base, uint32_t r0, uint32_t r1,
+                                         uint32_t r2, uint32_t r3, int lane) {
+    // word_base: first path of this lane's word, OR-ed with the accumulator-set tag (bit 30);
+    // r0..r3: sorted row ids of this lane's four rows
     const uint32_t sm[8] = {s0, s1, s2, s3, s4, s5, s6, s7};
+    const uint32_t rid[4] = {r0, r1, r2, r3};
     uint32_t n = 0;
 #pragma unroll
     for (int u = 0; u < 8; ++u) n += (uint32_t)__popc(sm[u]);
@@ -181,8 +184,7 @@ __device__ __noinline__ uint2 push_slow8(uint2 *__restrict__ slow, uint32_t *wor
             mask &= mask - 1u;
             // masks 0-3: rows counted good for now, masks 4-7: the same rows counted bad for now
             if (idx < slow_cap)
-                slow[idx] = make_uint2((word_base + c) | (u < 4 ? 0x80000000u : 0u),
-                                       row_first + (u & 3) * row_step);
+                slow[idx] = make_uint2((word_base + c) | (u < 4 ? 0x80000000u : 0u), rid[u & 3]);
             else atomicOr(work_count + 3, 1u);
             ++idx;
         }
@@ -305,42 +307,58 @@ __device__ __forceinline__ void eval_row(const uint2 *__restrict__ nt, const uns
     bad = open & ~amb & ~over;
 }
 
+// What a scheduling unit needs besides its rows (both scoring kernels fill one per warp).
+struct UnitCtx {
+    const uint2 *nt;          // node plane at this lane's word (shared memory)
+    const uint2 *nf;          // {F+, F-} plane at this lane's word (global memory)
+    const uint32_t *s_tab;    // table base (shared memory)
+    const uint32_t *tab;      // table at this lane's word
+    uint32_t pair_base, bt_base;
+    int filter;
+    uint2 *slow;
+    uint32_t *work_count;
+    uint32_t slow_cap;
+    uint32_t word_base;       // first path of this lane's word | accumulator-set tag (bit 30)
+};
+
 // One scheduling unit (rows of one length M).  Four (two for M > 8) rows per lane and loop trip:
 // their data is loaded first (independent LDG.64s in flight together), then scored, then ONE warp
 // vote decides whether any of them needs the second look at the start overhang.  The loop is kept
 // rolled and short so that the body stays in the instruction cache.
-template <int M, int W>
-__device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__restrict__ nt,
-                                           const uint2 *__restrict__ nf, const uint32_t *__restrict__ s_tab,
-                                           const uint32_t *__restrict__ tab, uint32_t unit,
-                                           uint32_t word_base, Planes &G, Planes &B, uint2 &slow_win,
-                                           int lane) {
+// kGather = false: the unit is rows [0, nrows) of the dense matrix at `base`, sorted ids sorted0 + r.
+// kGather = true:  the unit is the rows idx[0..nrows) of the bucket matrix at `base` (inverted-index
+//                  list), sorted ids sorted0 + idx[r].
+template <int M, int W, bool kGather>
+__device__ __forceinline__ void score_unit(const UnitCtx &c, const uint16_t *__restrict__ base,
+                                           const uint32_t *__restrict__ idx, uint32_t nrows, uint32_t sorted0,
+                                           uint32_t lm, Planes &G, Planes &B, uint2 &slow_win, int lane) {
     constexpr int R = 32 / W;                       // rows per warp step
     constexpr int RS = (int)row_stride(M);
     constexpr int UB = M <= 8 ? 4 : 2;   // rows scored per loop trip (their data is loaded first)
-    const uint32_t row0 = (unit - a.unit_start[M]) * a.unit_rows;
-    const uint32_t nrows = min(a.unit_rows, a.bk.count[M] - row0);
-    const uint16_t *base = a.bk.bstep + a.bk.step_base[M] + (size_t)row0 * RS;
-    const uint32_t sorted0 = a.bk.row_start[M] + row0;
-    const uint32_t lm = tab[(a.mg.lm_base + M) * W];
     // warp-uniform region bases (the lane's word offset is OR-ed into each entry offset)
     const uint32_t lane_off = 4u * ((uint32_t)lane % W);
     // the rows hold absolute pair entries and BT sits at entry 0: both offsets are relative to the table
-    const unsigned char *mt = reinterpret_cast<const unsigned char *>(s_tab);
+    const unsigned char *mt = reinterpret_cast<const unsigned char *>(c.s_tab);
     const unsigned char *bt = mt;
     const uint32_t sub = (uint32_t)lane / W;
-    const bool filter = a.filter != 0;
+    const bool filter = c.filter != 0;
     // rows of trip `it0` into registers (independent LDG.64s in flight together)
-    auto load_rows = [&](uint32_t it0, uint32_t (&qq)[UB][RS / 2]) {
+    auto load_rows = [&](uint32_t it0, uint32_t (&qq)[UB][RS / 2], uint32_t (&ri)[UB]) {
 #pragma unroll
         for (int k = 0; k < UB; ++k) {
             const uint32_t r = it0 + k * R + sub;
-            const uint2 *src = reinterpret_cast<const uint2 *>(base + (size_t)(r < nrows ? r : 0u) * RS);
+            uint32_t row = r < nrows ? r : 0u;
+            if (kGather) row = __ldg(idx + row);
+            ri[k] = row;
+        }
 #pragma unroll
-            for (int c = 0; c < RS / 4; ++c) {
-                const uint2 t = __ldg(src + c);
-                qq[k][2 * c] = t.x;
-                qq[k][2 * c + 1] = t.y;
+        for (int k = 0; k < UB; ++k) {
+            const uint2 *src = reinterpret_cast<const uint2 *>(base + (size_t)ri[k] * RS);
+#pragma unroll
+            for (int cc = 0; cc < RS / 4; ++cc) {
+                const uint2 t = __ldg(src + cc);
+                qq[k][2 * cc] = t.x;
+                qq[k][2 * cc + 1] = t.y;
             }
         }
     };
@@ -348,26 +366,32 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__r
     // the global-load latency hides behind ~4 rows of table work
     constexpr bool kPrefetch = M <= 5;
     uint32_t qn[kPrefetch ? UB : 1][RS / 2];
-    if (kPrefetch) load_rows(0, reinterpret_cast<uint32_t (&)[UB][RS / 2]>(qn));
+    uint32_t rn[kPrefetch ? UB : 1];
+    if (kPrefetch)
+        load_rows(0, reinterpret_cast<uint32_t (&)[UB][RS / 2]>(qn), reinterpret_cast<uint32_t (&)[UB]>(rn));
 #pragma unroll 1
     for (uint32_t it = 0; it < nrows; it += UB * R) {
-        uint32_t q[UB][RS / 2];
+        uint32_t q[UB][RS / 2], ri[UB];
         bool valid[UB];
 #pragma unroll
         for (int k = 0; k < UB; ++k) valid[k] = it + k * R + sub < nrows;
         if (kPrefetch) {
 #pragma unroll
-            for (int k = 0; k < UB; ++k)
+            for (int k = 0; k < UB; ++k) {
+                ri[k] = rn[kPrefetch ? k : 0];
 #pragma unroll
-                for (int c = 0; c < RS / 2; ++c) q[k][c] = qn[kPrefetch ? k : 0][c];
-            if (it + UB * R < nrows) load_rows(it + UB * R, reinterpret_cast<uint32_t (&)[UB][RS / 2]>(qn));
+                for (int cc = 0; cc < RS / 2; ++cc) q[k][cc] = qn[kPrefetch ? k : 0][cc];
+            }
+            if (it + UB * R < nrows)
+                load_rows(it + UB * R, reinterpret_cast<uint32_t (&)[UB][RS / 2]>(qn),
+                          reinterpret_cast<uint32_t (&)[UB]>(rn));
         } else {
-            load_rows(it, q);
+            load_rows(it, q, ri);
         }
         uint32_t gm[UB], bm[UB], sm[UB], sb[UB], ov[UB], any_over = 0, any_slow = 0;
 #pragma unroll
         for (int k = 0; k < UB; ++k) {
-            eval_row<M, W>(nt, mt, bt, lane_off, q[k], lm, valid[k] ? 0xFFFFFFFFu : 0u, filter, gm[k], bm[k],
+            eval_row<M, W>(c.nt, mt, bt, lane_off, q[k], lm, valid[k] ? 0xFFFFFFFFu : 0u, filter, gm[k], bm[k],
                            sm[k], ov[k]);
             sb[k] = 0;
             any_over |= ov[k];
@@ -376,9 +400,8 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__r
 #pragma unroll
             for (int k = 0; k < UB; ++k) {
                 if (!__any_sync(0xFFFFFFFFu, ov[k] != 0)) continue;
-                const uint32_t r = it + k * R + sub;
-                const uint4 x = refine_row<W>(nt, tab, base + (size_t)(valid[k] ? r : 0u) * RS, M,
-                                              a.mg.pair_base, a.mg.bt_base, lm, a.filter, nf);
+                const uint4 x = refine_row<W>(c.nt, c.tab, base + (size_t)ri[k] * RS, M, c.pair_base, c.bt_base, lm,
+                                              c.filter, c.nf);
                 gm[k] = valid[k] ? x.x : 0u;
                 bm[k] = valid[k] ? x.y : 0u;
                 sm[k] = valid[k] ? x.z : 0u;
@@ -390,10 +413,11 @@ __device__ __forceinline__ void score_unit(const BitsetArgs &a, const uint2 *__r
 #pragma unroll
         for (int k = 0; k < UB; ++k) any_slow |= sm[k] | sb[k];
         if (__any_sync(0xFFFFFFFFu, any_slow != 0)) {
-            slow_win = push_slow8(a.slow, a.work_count, a.slow_cap, slow_win, sm[0], sm[1],
+            slow_win = push_slow8(c.slow, c.work_count, c.slow_cap, slow_win, sm[0], sm[1],
                                   UB > 2 ? sm[UB > 2 ? 2 : 0] : 0u, UB > 2 ? sm[UB > 2 ? 3 : 0] : 0u, sb[0], sb[1],
-                                  UB > 2 ? sb[UB > 2 ? 2 : 0] : 0u, UB > 2 ? sb[UB > 2 ? 3 : 0] : 0u, word_base,
-                                  sorted0 + it + sub, (uint32_t)R, lane);
+                                  UB > 2 ? sb[UB > 2 ? 2 : 0] : 0u, UB > 2 ? sb[UB > 2 ? 3 : 0] : 0u, c.word_base,
+                                  sorted0 + ri[0], sorted0 + ri[1], sorted0 + ri[UB > 2 ? 2 : 0],
+                                  sorted0 + ri[UB > 2 ? 3 : 0], lane);
         }
     }
 }
@@ -441,6 +465,18 @@ score_bitset_kernel(const BitsetArgs a) {
     uint32_t rows_acc = 0;
     uint2 slow_win = make_uint2(0u, 0u);   // this warp's reserved window of the second-look list
     const uint32_t n_units = a.unit_start[kMaxBucket + 1];
+    UnitCtx ctx;
+    ctx.nt = nt;
+    ctx.nf = nf;
+    ctx.s_tab = s_tab;
+    ctx.tab = tab;
+    ctx.pair_base = a.mg.pair_base;
+    ctx.bt_base = a.mg.bt_base;
+    ctx.filter = a.filter;
+    ctx.slow = a.slow;
+    ctx.work_count = a.work_count;
+    ctx.slow_cap = a.slow_cap;
+    ctx.word_base = word_base;
 
     auto flush = [&]() {
 #pragma unroll 2
@@ -483,8 +519,14 @@ score_bitset_kernel(const BitsetArgs a) {
             next_b = unit_bucket(s_ustart, n_units - 1u - next, lane);
             prefetch_unit(a, n_units - 1u - next, next_b, lane);
         }
+        // rows [row0, row0 + unrows) of bucket b's dense matrix
+        const uint32_t row0 = (unit - a.unit_start[b]) * a.unit_rows;
+        const uint32_t unrows = min(a.unit_rows, a.bk.count[b] - row0);
+        const uint16_t *ubase = a.bk.bstep + a.bk.step_base[b] + (size_t)row0 * row_stride(b);
+        const uint32_t usorted = a.bk.row_start[b] + row0;
+        const uint32_t ulm = tab[(a.mg.lm_base + b) * W];
         switch (b) {
-#define GFE_CASE(M_) case M_: score_unit<M_, W>(a, nt, nf, s_tab, tab, unit, word_base, G, B, slow_win, lane); break;
+#define GFE_CASE(M_) case M_: score_unit<M_, W, false>(ctx, ubase, nullptr, unrows, usorted, ulm, G, B, slow_win, lane); break;
             GFE_CASE(1) GFE_CASE(2) GFE_CASE(3) GFE_CASE(4) GFE_CASE(5) GFE_CASE(6) GFE_CASE(7)
             GFE_CASE(8) GFE_CASE(9) GFE_CASE(10) GFE_CASE(11) GFE_CASE(12) GFE_CASE(13)
             GFE_CASE(14) GFE_CASE(15) GFE_CASE(16)
@@ -504,6 +546,146 @@ score_bitset_kernel(const BitsetArgs a) {
         if (p >= a.P) continue;
         const uint32_t v = s_cnt[i] + ((i & 1u) ? empty_rows : 0u);
         if (v) atomicAdd(&a.counts[2 * (size_t)p_base + i], v);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1i: score_incr — incremental scoring for the search.  A candidate path that
+// extends its parent by one step v can only change the verdict of rows that contain v (a new
+// occurrence ends at the new step, a newly passing row names v) and of the rows of F (rows with the
+// root node: the start-overhang class; scored afresh for every path).  A chunk is <= 32 paths that
+// end in the same node v (one word per table entry, W = 1): pass 0 scores the inverted-index lists
+// of v into accumulator set 0, pass 1 the lists of F into set 1.  Same table, row evaluation,
+// counters and second-look list as score_bitset_kernel; rows are gathered through the index.
+// ------------------------------------------------------------------------------------------------
+constexpr int kIncrThreads = 128;
+
+__global__ void __launch_bounds__(kIncrThreads)
+score_incr_kernel(const IncrArgs a) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    uint32_t *s_tab = reinterpret_cast<uint32_t *>(smem);
+    const uint32_t tab_words = a.mg.entries;                   // W = 1
+    uint32_t *s_cnt = s_tab + tab_words;                       // 2 sets x 32 paths x {bad, good}
+    uint64_t *s_bar = reinterpret_cast<uint64_t *>(s_cnt + 128);
+    __shared__ uint32_t s_ustart[33], s_goff[32], s_gsize[32];
+
+    const uint32_t chunk = blockIdx.y;
+    const uint32_t p_base = chunk * 32u;
+    const int lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) mbar_init(s_bar, 1);
+    if (threadIdx.x < 128) s_cnt[threadIdx.x] = 0;
+    if (threadIdx.x < 32) {
+        // group k: pass (k >> 4), rows of length (k & 15) + 1 of node v (pass 0) / of F (pass 1)
+        const uint32_t v = a.chunk_node[chunk];
+        const uint32_t node = (threadIdx.x >> 4) ? a.mg.L : v;
+        const uint32_t m = (threadIdx.x & 15u) + 1u;
+        uint32_t o0 = 0, size = 0;
+        if (node != 0xFFFFFFFFu) {
+            o0 = a.inv.off[node * kIdxLens + m];
+            size = a.inv.off[node * kIdxLens + m + 1] - o0;
+        }
+        const uint32_t units = (size + a.unit_rows - 1) / a.unit_rows;
+        uint32_t incl = units;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        s_ustart[threadIdx.x] = incl - units;
+        s_goff[threadIdx.x] = o0;
+        s_gsize[threadIdx.x] = size;
+        if (threadIdx.x == 31) s_ustart[32] = incl;
+    }
+    __syncthreads();
+    pdl_wait();      // build_tables' mask tables (everything above read only the index and this CTA's shared memory)
+    pdl_trigger();
+    if (threadIdx.x == 0) {
+        const uint32_t bytes = tab_words * 4u;
+        const unsigned char *src = reinterpret_cast<const unsigned char *>(a.masks + (size_t)chunk * tab_words);
+        mbar_expect_tx(s_bar, bytes);
+        for (uint32_t o = 0; o < bytes; o += 65536u) bulk_g2s(smem + o, src + o, min(65536u, bytes - o), s_bar);
+    }
+    mbar_wait(s_bar, 0);
+
+    UnitCtx ctx;
+    ctx.nt = reinterpret_cast<const uint2 *>(s_tab + geom_node_base());
+    ctx.nf = reinterpret_cast<const uint2 *>(a.fplane) + (size_t)chunk * (a.mg.L + 1);
+    ctx.s_tab = s_tab;
+    ctx.tab = s_tab;
+    ctx.pair_base = a.mg.pair_base;
+    ctx.bt_base = a.mg.bt_base;
+    ctx.filter = 1;
+    ctx.slow = a.slow;
+    ctx.work_count = a.work_count;
+    ctx.slow_cap = a.slow_cap;
+    ctx.word_base = p_base;
+    Planes G, B;
+    G.clear();
+    B.clear();
+    uint32_t rows_acc = 0, cur_set = 0;
+    uint2 slow_win = make_uint2(0u, 0u);
+    const uint32_t n_units = s_ustart[32];
+
+    auto flush = [&](uint32_t set) {
+#pragma unroll 2
+        for (int c = 0; c < 8; ++c) {
+            uint32_t gl, gh, bl, bh;
+            G.value4(c, gl, gh);
+            B.value4(c, bl, bh);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t g = ((gl >> (8 * j)) & 0xFFu) | (((gh >> (8 * j)) & 0xFFu) << 8);
+                const uint32_t b = ((bl >> (8 * j)) & 0xFFu) | (((bh >> (8 * j)) & 0xFFu) << 8);
+                const uint32_t col = c + 8 * j;
+                if (b) atomicAdd(&s_cnt[64 * set + 2 * col], b);
+                if (g) atomicAdd(&s_cnt[64 * set + 2 * col + 1], g);
+            }
+        }
+        G.clear();
+        B.clear();
+        rows_acc = 0;
+    };
+
+    // units are claimed in ascending order (one atomic each), so a warp sees pass 0 before pass 1
+    for (;;) {
+        uint32_t unit = 0;
+        if (lane == 0) unit = atomicAdd(a.unit_ctr + chunk, 1u);
+        unit = __shfl_sync(0xFFFFFFFFu, unit, 0);
+        if (unit >= n_units) break;
+        const int g = __popc(__ballot_sync(0xFFFFFFFFu, unit >= s_ustart[lane])) - 1;
+        const uint32_t set = (uint32_t)g >> 4;
+        const int m = (g & 15) + 1;
+        if (set != cur_set) {
+            flush(cur_set);
+            cur_set = set;
+            ctx.word_base = p_base | (set << 30);
+        }
+        const uint32_t row0 = (unit - s_ustart[g]) * a.unit_rows;
+        const uint32_t nrows = min(a.unit_rows, s_gsize[g] - row0);
+        const uint32_t *idx = a.inv.rows + s_goff[g] + row0;
+        const uint16_t *base = a.bk.bstep + a.bk.step_base[m];
+        const uint32_t sorted0 = a.bk.row_start[m];
+        const uint32_t lm = s_tab[a.mg.lm_base + m];
+        switch (m) {
+#define GFE_CASE(M_) case M_: score_unit<M_, 1, true>(ctx, base, idx, nrows, sorted0, lm, G, B, slow_win, lane); break;
+            GFE_CASE(1) GFE_CASE(2) GFE_CASE(3) GFE_CASE(4) GFE_CASE(5) GFE_CASE(6) GFE_CASE(7)
+            GFE_CASE(8) GFE_CASE(9) GFE_CASE(10) GFE_CASE(11) GFE_CASE(12) GFE_CASE(13)
+            GFE_CASE(14) GFE_CASE(15) GFE_CASE(16)
+#undef GFE_CASE
+            default: break;
+        }
+        rows_acc += (a.unit_rows + 31u) / 32u;      // W = 1: a lane sees every 32nd row of the unit
+        if (rows_acc > (1u << kPlanes) - 2u * ((a.unit_rows + 31u) / 32u)) flush(cur_set);
+    }
+    flush(cur_set);
+    fill_slow_holes(a.slow, a.work_count, a.slow_cap, slow_win, lane);
+    __syncthreads();
+    // alignments without steps pass the filter and score 0 against every path: good, in the fresh set
+    const uint32_t empty_rows = blockIdx.x == 0 ? a.bk.count[0] : 0u;
+    for (uint32_t i = threadIdx.x; i < 128u; i += blockDim.x) {
+        const uint32_t set = i >> 6, col = (i & 63u) >> 1, gb = i & 1u;
+        const uint32_t v = s_cnt[i] + ((set == 1u && gb == 1u) ? empty_rows : 0u);
+        if (v) atomicAdd(&a.counts[4 * (size_t)(p_base + col) + 2 * set + gb], v);
     }
 }
 
@@ -536,7 +718,20 @@ int configure_bitset_kernels() {
     if ((e = configure_w<4>()) != cudaSuccess) return (int)e;
     if ((e = configure_w<8>()) != cudaSuccess) return (int)e;
     if ((e = configure_w<16>()) != cudaSuccess) return (int)e;
+    if ((e = cudaFuncSetAttribute(score_incr_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(kBitsetSmemBudget + 1024))) != cudaSuccess)
+        return (int)e;
     return (int)configure_w<32>();
+}
+
+void launch_score_incr(const IncrArgs &a, int sm_count, cudaStream_t st) {
+    if (a.chunks == 0) return;
+    const size_t smem = (size_t)a.mg.entries * 4 + 128 * 4 + 16;
+    // enough CTAs to fill the machine (4 per SM at 128 registers), shared between the chunks
+    uint32_t gx = ((uint32_t)sm_count * 4 + a.chunks - 1) / a.chunks;
+    if (gx < 1) gx = 1;
+    if (gx > 64) gx = 64;
+    launch_pdl(1, score_incr_kernel, dim3(gx, a.chunks), dim3(kIncrThreads), smem, st, a);
 }
 
 void launch_score_bitset(const BitsetArgs &a, int sm_count, cudaStream_t st) {

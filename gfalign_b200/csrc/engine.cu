@@ -406,6 +406,7 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) 
     e->h2d_bytes += (size_t)e->n_nodes * sizeof(uint32_t);
     e->tab_stride = ((e->L + 1 + 7) / 8) * 8;
     e->have_universe = true;
+    e->have_index = false;
     return GFE_OK;
 }
 
@@ -768,6 +769,391 @@ int gfe_score_paths_sharded(gfe_engine *e, gfe_exchange *x, const uint32_t *path
                             const uint32_t *path_steps, uint32_t P, int filter, uint32_t *counts) {
     if (!x) return GFE_ERR_ARG;
     return score_paths_impl(e, x, path_offsets, path_steps, P, filter, counts);
+}
+
+}  // extern "C"
+
+// ---- incremental search scoring (the ABI comment in include/gfalign_b200.h) ------------
+
+static int ensure_index(gfe_engine *e, uint32_t root_local, cudaStream_t st) {
+    if (e->have_index && e->inv_root == root_local) return GFE_OK;
+    const uint32_t groups = (e->L + 1) * (uint32_t)kIdxLens;
+    TRY(ensure_dev(e, e->d_inv_off, (size_t)groups + 1));
+    TRY(ensure_dev(e, e->d_inv_cursor, (size_t)groups + 1));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_inv_cursor.ptr, 0, ((size_t)groups + 1) * 4, st));
+    launch_index_count(e->bk, e->L, root_local, e->d_inv_cursor.ptr, st);
+    // counters -> exclusive offsets; the same array becomes the fill cursors (each thread reads its
+    // counter before it overwrites it)
+    launch_index_scan(e->d_inv_cursor.ptr, groups, e->d_inv_off.ptr, e->d_inv_cursor.ptr, st);
+    uint32_t total = 0;
+    CUDA_TRY(e, cudaMemcpyAsync(&total, e->d_inv_off.ptr + groups, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(e, cudaStreamSynchronize(st));
+    TRY(ensure_dev(e, e->d_inv_rows, std::max<size_t>(total, 1)));
+    launch_index_fill(e->bk, e->L, root_local, e->d_inv_cursor.ptr, e->d_inv_rows.ptr, st);
+    CUDA_TRY(e, cudaGetLastError());
+    e->kernel_launches += 3;
+    e->inv_entries = total;
+    e->inv_root = root_local;
+    e->have_index = true;
+    return GFE_OK;
+}
+
+namespace {
+constexpr uint32_t kNoNode = 0xFFFFFFFFu;
+constexpr size_t kHdrWords = 16;   // [8 work counters][bad-step flag][sticky overflow][pad]
+inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
+}  // namespace
+
+static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_t *counts) {
+    if (!e || !b || !counts) return GFE_ERR_ARG;
+    if (!e->have_alignments || !e->have_universe) {
+        set_error(e, "gfe_score_paths_incremental: alignments and universe must be set first");
+        return GFE_ERR_STATE;
+    }
+    if (!e->have_dict || e->force_legacy) {
+        set_error(e, "gfe_score_paths_incremental: this universe has no pair dictionary (bitset path off)");
+        return GFE_ERR_STATE;
+    }
+    const uint32_t P = b->P;
+    if (P == 0) return GFE_OK;
+    if (!b->n_bases || !b->base_offsets || !b->base_steps || !b->item_base || !b->suffix_offsets || !b->mode ||
+        b->base_offsets[0] != 0 || b->suffix_offsets[0] != 0 || (b->suffix_offsets[P] && !b->suffix_steps)) {
+        set_error(e, "gfe_score_paths_incremental: malformed batch");
+        return GFE_ERR_ARG;
+    }
+    if (P >= (1u << 24)) {
+        set_error(e, "gfe_score_paths_incremental: more than 2^24 paths in one batch");
+        return GFE_ERR_LIMIT;
+    }
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    cudaStream_t st = e->stream;
+    const uint32_t n_bases = b->n_bases, base_total = b->base_offsets[n_bases], suf_total = b->suffix_offsets[P];
+    const uint32_t root = b->base_steps[0] >> 1;
+    // ---- host: per-base node presence, per-item last node / revisit, chunk layout -----------------
+    auto local_of = [&](uint32_t step) -> uint32_t {
+        const uint32_t node = step >> 1;
+        return node < e->n_nodes ? e->node2local[node] : e->L;
+    };
+    for (uint32_t k = 0; k < n_bases; ++k) {
+        if (b->base_offsets[k + 1] <= b->base_offsets[k] || (b->base_steps[b->base_offsets[k]] >> 1) != root) {
+            set_error(e, "gfe_score_paths_incremental: base path %u is empty or does not start at the root node", k);
+            return GFE_ERR_ARG;
+        }
+    }
+    if (local_of(b->base_steps[0]) >= e->L) {
+        set_error(e, "gfe_score_paths_incremental: the root node is outside the universe");
+        return GFE_ERR_ARG;
+    }
+    TRY(ensure_index(e, local_of(b->base_steps[0]), st));
+    const uint32_t words_per_base = (e->L + 31) / 32;
+    std::vector<uint32_t> &present = e->h_present;
+    present.assign((size_t)n_bases * words_per_base, 0u);
+    for (uint32_t k = 0; k < n_bases; ++k)
+        for (uint32_t i = b->base_offsets[k]; i < b->base_offsets[k + 1]; ++i) {
+            const uint32_t l = local_of(b->base_steps[i]);
+            if (l < e->L) present[(size_t)k * words_per_base + (l >> 5)] |= 1u << (l & 31);
+        }
+    using Slot = gfe_engine::IncrSlot;               // parent = 1: the item's parent path (negative copy)
+    std::vector<Slot> &slots = e->h_slots;
+    slots.clear();
+    slots.reserve((size_t)P + P / 8 + 8);
+    uint32_t n_full = 0;
+    for (uint32_t i = 0; i < P; ++i) {
+        const uint32_t kb = b->item_base[i];
+        if (kb >= n_bases || b->suffix_offsets[i + 1] < b->suffix_offsets[i]) {
+            set_error(e, "gfe_score_paths_incremental: item %u is malformed", i);
+            return GFE_ERR_ARG;
+        }
+        const uint32_t s0 = b->suffix_offsets[i], ns = b->suffix_offsets[i + 1] - s0;
+        const uint32_t nb = b->base_offsets[kb + 1] - b->base_offsets[kb];
+        if ((uint64_t)nb + ns > GFE_MAX_STEPS) {
+            set_error(e, "gfe_score_paths_incremental: item %u has %u steps; the reference's MAX_N allows %u", i,
+                      nb + ns, GFE_MAX_STEPS);
+            return GFE_ERR_LIMIT;
+        }
+        if (b->mode[i] == 0) {
+            slots.push_back(Slot{kNoNode, i, 0});
+            ++n_full;
+            continue;
+        }
+        if (nb + ns < (uint32_t)kMaxBucket + 1) {
+            set_error(e, "gfe_score_paths_incremental: item %u: delta mode needs a parent of >= %d steps", i, kMaxBucket);
+            return GFE_ERR_ARG;
+        }
+        const uint32_t last = ns ? b->suffix_steps[s0 + ns - 1] : b->base_steps[b->base_offsets[kb + 1] - 1];
+        const uint32_t v = local_of(last);
+        if (v >= e->L) {
+            set_error(e, "gfe_score_paths_incremental: item %u ends in a node outside the universe", i);
+            return GFE_ERR_ARG;
+        }
+        // does the parent (the path without its last step) already visit v?
+        bool revisit = false;
+        if (ns) {
+            revisit = (present[(size_t)kb * words_per_base + (v >> 5)] >> (v & 31)) & 1u;
+            for (uint32_t j = 0; j + 1 < ns && !revisit; ++j) revisit = local_of(b->suffix_steps[s0 + j]) == v;
+        } else {
+            for (uint32_t j = b->base_offsets[kb]; j + 1 < b->base_offsets[kb + 1] && !revisit; ++j)
+                revisit = local_of(b->base_steps[j]) == v;
+        }
+        slots.push_back(Slot{v, i, 0});
+        if (revisit) slots.push_back(Slot{v, i, 1});
+    }
+    std::stable_sort(slots.begin(), slots.end(), [](const Slot &x, const Slot &y) { return x.key < y.key; });
+    // chunks of 32 slots, never mixing keys; device path d = 32 * chunk + position
+    std::vector<uint32_t> &chunk_node = e->h_chunk_node;
+    std::vector<uint32_t> &slot_dev = e->h_slot_dev;
+    chunk_node.clear();
+    slot_dev.assign(slots.size(), 0);
+    {
+        uint32_t in_chunk = 32, cur_key = 0;
+        for (size_t k = 0; k < slots.size(); ++k) {
+            if (in_chunk == 32 || slots[k].key != cur_key) {
+                chunk_node.push_back(slots[k].key);
+                cur_key = slots[k].key;
+                in_chunk = 0;
+            }
+            slot_dev[k] = (uint32_t)(chunk_node.size() - 1) * 32u + in_chunk++;
+        }
+    }
+    const uint32_t chunks = (uint32_t)chunk_node.size(), P_dev = chunks * 32u;
+    // ---- staging: [base_off][base_steps][suffix_steps][desc inc][poff inc][chunk_node][desc full][poff full]
+    const size_t o_boff = 0, o_bst = align16(o_boff + ((size_t)n_bases + 1) * 4);
+    const size_t o_suf = align16(o_bst + (size_t)base_total * 4);
+    const size_t o_desc = align16(o_suf + (size_t)suf_total * 4);
+    const size_t o_poff = align16(o_desc + (size_t)P_dev * 16);
+    const size_t o_cn = align16(o_poff + ((size_t)P_dev + 1) * 4);
+    const size_t o_fdesc = align16(o_cn + (size_t)chunks * 4);
+    const size_t o_fpoff = align16(o_fdesc + (size_t)n_full * 16);
+    const size_t bytes = align16(o_fpoff + ((size_t)n_full + 1) * 4);
+    TRY(ensure_pinned(e, e->h_stage, bytes));
+    TRY(ensure_dev(e, e->d_stage, bytes));
+    unsigned char *hs = e->h_stage.ptr;
+    memcpy(hs + o_boff, b->base_offsets, ((size_t)n_bases + 1) * 4);
+    memcpy(hs + o_bst, b->base_steps, (size_t)base_total * 4);
+    if (suf_total) memcpy(hs + o_suf, b->suffix_steps, (size_t)suf_total * 4);
+    uint4 *h_desc = reinterpret_cast<uint4 *>(hs + o_desc);
+    uint32_t *h_poff = reinterpret_cast<uint32_t *>(hs + o_poff);
+    for (uint32_t d = 0; d < P_dev; ++d) h_desc[d] = make_uint4(kNoNode, 0, 0, 0);
+    std::vector<uint32_t> &len_dev = e->h_len_dev;
+    len_dev.assign(P_dev, 0);
+    uint4 *h_fdesc = reinterpret_cast<uint4 *>(hs + o_fdesc);
+    uint32_t *h_fpoff = reinterpret_cast<uint32_t *>(hs + o_fpoff);
+    uint32_t nf = 0, ftotal = 0;
+    std::vector<uint32_t> &full_of_item = e->h_full_of_item;
+    full_of_item.assign(P, kNoNode);
+    for (size_t k = 0; k < slots.size(); ++k) {
+        const Slot &sl = slots[k];
+        const uint32_t i = sl.item, kb = b->item_base[i];
+        const uint32_t s0 = b->suffix_offsets[i], ns = b->suffix_offsets[i + 1] - s0;
+        const uint32_t nb = b->base_offsets[kb + 1] - b->base_offsets[kb];
+        h_desc[slot_dev[k]] = make_uint4(kb, s0, ns, sl.parent);
+        len_dev[slot_dev[k]] = nb + ns - sl.parent;
+        if (sl.key == kNoNode) {
+            full_of_item[i] = nf;
+            h_fdesc[nf] = make_uint4(kb, s0, ns, 0);
+            h_fpoff[nf] = ftotal;
+            ftotal += nb + ns;
+            ++nf;
+        }
+    }
+    h_fpoff[nf] = ftotal;
+    uint32_t dtotal = 0;
+    for (uint32_t d = 0; d < P_dev; ++d) {
+        h_poff[d] = dtotal;
+        dtotal += len_dev[d];
+    }
+    h_poff[P_dev] = dtotal;
+    memcpy(hs + o_cn, chunk_node.data(), (size_t)chunks * 4);
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_stage.ptr, hs, bytes, cudaMemcpyHostToDevice, st));
+    // ---- device buffers ------------------------------------------------------------------------------
+    const size_t res_words = kHdrWords + (size_t)n_full * 2 + (size_t)P_dev * 4;
+    TRY(ensure_pinned(e, e->h_counts, res_words));
+    {
+        const uint32_t *before = e->d_counts.ptr;
+        TRY(ensure_dev(e, e->d_counts, res_words));
+        if (e->d_counts.ptr != before)
+            CUDA_TRY(e, cudaMemsetAsync(e->d_counts.ptr, 0, kHdrWords * sizeof(uint32_t), st));
+    }
+    TRY(ensure_dev(e, e->d_plocal, (size_t)dtotal + ftotal + 16));
+    TRY(ensure_dev(e, e->d_ptab, (size_t)std::max(P_dev, n_full) * e->tab_stride));
+    TRY(ensure_dev(e, e->d_pnext, (size_t)std::max(dtotal, ftotal) + 8));
+    {
+        // second-look / exact lists: the incremental pass touches ~4 % of the rows per path
+        const uint64_t want = std::max<uint64_t>(std::min<uint64_t>((uint64_t)P_dev * e->A / 256, 1ull << 26), 1u << 20);
+        if (want > e->slow_cap) e->slow_cap = (size_t)want;
+        if (want > e->work_cap) e->work_cap = (size_t)want;
+        TRY(ensure_dev(e, e->d_slow, e->slow_cap));
+        TRY(ensure_dev(e, e->d_work, e->work_cap));
+    }
+    MaskGeom mg;
+    mg.W = 1;
+    mg.L = e->L;
+    mg.bt_base = 0;
+    mg.node_base = geom_node_base();
+    mg.lm_base = geom_lm_base(e->L);
+    mg.pair_base = geom_pair_base(e->L);
+    mg.n_pairs = e->n_pairs;
+    mg.entries = (mg.pair_base + 2 * e->n_pairs + 2 + 3) & ~3u;
+    const size_t table_words = (size_t)chunks * mg.entries, fplane_words = (size_t)chunks * 2 * (e->L + 1);
+    if (table_words + fplane_words > 0xFFFFFFFFull) {
+        set_error(e, "gfe_score_paths_incremental: batch too large for the mask tables");
+        return GFE_ERR_LIMIT;
+    }
+    TRY(ensure_dev(e, e->d_masks, table_words + fplane_words));
+    TRY(ensure_dev(e, e->d_unit_ctr, chunks));
+    uint32_t *d_hdr = e->d_counts.ptr, *d_full = d_hdr + kHdrWords, *d_inc = d_full + (size_t)n_full * 2;
+    const unsigned char *ds = e->d_stage.ptr;
+    const uint32_t *d_poff = reinterpret_cast<const uint32_t *>(ds + o_poff);
+    const PairDict pd{e->d_pair_keys.ptr, e->d_pair_ids.ptr, e->d_pair_ctr.ptr};
+    // ---- chain A: the incremental pass over all P_dev slots ------------------------------------------
+    PrologueArgs pro{};
+    pro.zero[0] = d_inc;
+    pro.zero_words[0] = P_dev * 4;
+    pro.zero[1] = d_hdr;
+    pro.zero_words[1] = kWorkCounters;
+    pro.zero[2] = e->d_masks.ptr;
+    pro.zero_words[2] = (uint32_t)(table_words + fplane_words);
+    pro.zero[3] = e->d_unit_ctr.ptr;
+    pro.zero_words[3] = chunks;
+    pro.sticky = d_hdr + kWorkCounters + 1;
+    launch_prologue(pro, e->sm_count, st);
+    AssembleArgs as;
+    as.desc = reinterpret_cast<const uint4 *>(ds + o_desc);
+    as.P = P_dev;
+    as.base_off = reinterpret_cast<const uint32_t *>(ds + o_boff);
+    as.base_steps = reinterpret_cast<const uint32_t *>(ds + o_bst);
+    as.suffix_steps = reinterpret_cast<const uint32_t *>(ds + o_suf);
+    as.poff = d_poff;
+    as.map = e->d_node2local.ptr;
+    as.n_nodes = e->n_nodes;
+    as.L = e->L;
+    as.out = e->d_plocal.ptr;
+    as.err = d_hdr + kWorkCounters;
+    launch_assemble_paths(as, st);
+    launch_build_tables(d_poff, e->d_plocal.ptr, P_dev, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr,
+                        e->d_masks.ptr, e->d_masks.ptr + table_words, mg, pd, st);
+    IncrArgs ia;
+    ia.bk = e->bk;
+    ia.mg = mg;
+    ia.inv = InvIndex{e->d_inv_off.ptr, e->d_inv_rows.ptr};
+    ia.masks = e->d_masks.ptr;
+    ia.fplane = e->d_masks.ptr + table_words;
+    ia.chunk_node = reinterpret_cast<const uint32_t *>(ds + o_cn);
+    ia.chunks = chunks;
+    ia.counts = d_inc;
+    ia.unit_rows = 256;
+    ia.unit_ctr = e->d_unit_ctr.ptr;
+    ia.slow = e->d_slow.ptr;
+    ia.work_count = d_hdr;
+    ia.slow_cap = (uint32_t)std::min<size_t>(e->d_slow.cap, 0xFFFFFFFFu);
+    if (e->timing) {
+        TRY(next_event_pair(e));
+        CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    }
+    launch_score_incr(ia, e->sm_count, st);
+    if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
+    ScoreArgs a;
+    a.bk = e->bk;
+    a.poff = d_poff;
+    a.pstep = e->d_plocal.ptr;
+    a.ptab = e->d_ptab.ptr;
+    a.pnext = e->d_pnext.ptr;
+    a.tab_stride = e->tab_stride;
+    a.P = P_dev;
+    a.chunk = pick_chunk(e, P_dev);
+    a.filter = 1;
+    a.counts = d_inc;
+    a.work = e->d_work.ptr;
+    a.work_count = d_hdr;
+    a.work_cap = (uint32_t)std::min<size_t>(e->d_work.cap, 0xFFFFFFFFu);
+    a.count_stride = 4;
+    a.path_tag = 1u << 30;     // what the long-row kernel queues belongs to the fresh set
+    e->kernel_launches += 4;
+    const uint32_t long_lo = e->bk.tile_start[kLongBucket], long_hi = e->bk.tile_start[kNumBuckets];
+    if (long_hi > long_lo) {   // alignments longer than kMaxBucket steps: scored afresh, set 1
+        launch_score_paths(a, e->sm_count, long_lo, long_hi, false, st);
+        e->kernel_launches += 1;
+    }
+    launch_slow_worklist(a, e->d_slow.ptr, d_hdr + 2, ia.slow_cap, st);
+    launch_exact_worklist(a, st);
+    e->kernel_launches += 2;
+    if (e->max_m > (uint32_t)kExactRegSteps) {
+        launch_exact_worklist_long(a, e->max_m, st);
+        e->kernel_launches += 1;
+    }
+    CUDA_TRY(e, cudaGetLastError());
+    // ---- chain B: the full scan of the mode-0 items -----------------------------------------------------
+    if (n_full) {
+        uint16_t *d_flocal = e->d_plocal.ptr + ((dtotal + 7) & ~7u);
+        AssembleArgs fs = as;
+        fs.desc = reinterpret_cast<const uint4 *>(ds + o_fdesc);
+        fs.P = n_full;
+        fs.poff = reinterpret_cast<const uint32_t *>(ds + o_fpoff);
+        fs.out = d_flocal;
+        launch_assemble_paths(fs, st);
+        e->kernel_launches += 1;
+        TRY(enqueue_score(e, fs.poff, d_flocal, n_full, ftotal, 1, d_full, d_hdr, nullptr, d_hdr + kWorkCounters,
+                          d_hdr + kWorkCounters + 1, st));
+    }
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, res_words * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(e, cudaStreamSynchronize(st));
+    if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
+    e->h2d_bytes += bytes;
+    e->d2h_bytes += res_words * sizeof(uint32_t);
+    const uint32_t *h = e->h_counts.ptr;
+    if (h[kWorkCounters]) {
+        CUDA_TRY(e, cudaMemset(e->d_counts.ptr + kWorkCounters, 0, 2 * sizeof(uint32_t)));
+        set_error(e, "gfe_score_paths_incremental: a step names a node outside the universe");
+        return GFE_ERR_ARG;
+    }
+    if (h[1] || h[3] || h[kWorkCounters + 1]) {
+        // a list overflowed in one of the two chains: grow both lists and redo the batch
+        CUDA_TRY(e, cudaMemset(e->d_counts.ptr + kWorkCounters, 0, 2 * sizeof(uint32_t)));
+        if (++e->incr_retries > 6 || e->d_slow.cap >= ((size_t)1 << 28)) {
+            e->incr_retries = 0;
+            set_error(e, "gfe_score_paths_incremental: work lists still overflow; split the batch");
+            return GFE_ERR_LIMIT;
+        }
+        e->slow_cap = std::min<size_t>(e->d_slow.cap * 4, (size_t)1 << 28);
+        e->work_cap = std::min<size_t>(e->d_work.cap * 4, (size_t)1 << 28);
+        TRY(ensure_dev(e, e->d_slow, e->slow_cap));
+        TRY(ensure_dev(e, e->d_work, e->work_cap));
+        const int rc = score_incremental_impl(e, b, counts);
+        e->incr_retries = 0;
+        return rc;
+    }
+    e->exact_pairs += h[0];
+    e->slow_pairs += h[2] - h[4];
+    // ---- results per item ---------------------------------------------------------------------------------
+    const uint32_t *h_full = h + kHdrWords, *h_inc = h_full + (size_t)n_full * 2;
+    for (uint32_t i = 0; i < P; ++i) counts[4 * (size_t)i] = counts[4 * (size_t)i + 1] = 0;
+    for (size_t k = 0; k < slots.size(); ++k) {
+        const Slot &sl = slots[k];
+        const uint32_t *r = h_inc + 4 * (size_t)slot_dev[k];
+        int32_t *o = counts + 4 * (size_t)sl.item;
+        if (sl.key == kNoNode) {
+            const uint32_t *f = h_full + 2 * (size_t)full_of_item[sl.item];
+            o[0] = (int32_t)f[0];
+            o[1] = (int32_t)f[1];
+            o[2] = (int32_t)r[2];
+            o[3] = (int32_t)r[3];
+        } else if (sl.parent) {
+            o[0] -= (int32_t)r[0];
+            o[1] -= (int32_t)r[1];
+        } else {
+            o[0] += (int32_t)r[0];
+            o[1] += (int32_t)r[1];
+            o[2] = (int32_t)r[2];
+            o[3] = (int32_t)r[3];
+        }
+    }
+    return GFE_OK;
+}
+
+extern "C" {
+
+int gfe_score_paths_incremental(gfe_engine *e, const gfe_path_batch *batch, int32_t *counts) {
+    return score_incremental_impl(e, batch, counts);
 }
 
 int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,

@@ -57,6 +57,18 @@ struct gfe_engine {
     size_t slow_cap = 1u << 20;
     int force_legacy = 0;            // GFE_FORCE_LEGACY=1: A/B runs of the pre-bitset kernel
 
+    // inverted index of the scoring view (incremental search scoring), built lazily per (universe, root)
+    DevBuf<uint32_t> d_inv_off, d_inv_cursor, d_inv_rows, d_chunk_node;
+    DevBuf<uint4> d_desc;
+    uint32_t inv_root = 0xFFFFFFFFu;
+    bool have_index = false;
+    uint64_t inv_entries = 0;
+    int incr_retries = 0;
+    // host scratch of gfe_score_paths_incremental (kept to avoid per-batch allocation)
+    struct IncrSlot { uint32_t key, item, parent; };
+    std::vector<uint32_t> h_present, h_chunk_node, h_slot_dev, h_len_dev, h_full_of_item;
+    std::vector<IncrSlot> h_slots;
+
     // candidate-path staging and results
     PinBuf<unsigned char> h_stage;
     DevBuf<unsigned char> d_stage;
@@ -102,6 +114,7 @@ struct gfe_engine {
         fd(d_edge_ft.ptr); fd(d_edge_counts.ptr); fd(d_edge_table.ptr); fd(d_rowstart.ptr);
         fd(d_pair_keys.ptr); fd(d_pair_ids.ptr); fd(d_pair_ctr.ptr); fd(d_masks.ptr);
         fd(d_unit_ctr.ptr); fd(d_slow.ptr);
+        fd(d_inv_off.ptr); fd(d_inv_cursor.ptr); fd(d_inv_rows.ptr); fd(d_chunk_node.ptr); fd(d_desc.ptr);
         fd(d_tr_path.ptr); fd(d_tr_misc.ptr); fd(d_tr_dirs.ptr); fd(d_tr_len.ptr); fd(d_tr_longb.ptr);
         fd(d_tr_base.ptr); fd(d_tr_first.ptr); fd(d_tr_score.ptr); fd(d_tr_longrows.ptr);
         fd(d_tr_ops.ptr); fd(d_tr_rc.ptr);

@@ -3,6 +3,8 @@
 // DESIGN.md for the per-kernel roofline.
 #include "kernels.cuh"
 
+#include <algorithm>
+
 namespace gfe {
 
 namespace {
@@ -263,6 +265,10 @@ build_tables_kernel(const uint32_t *__restrict__ poff, const uint16_t *__restric
     pdl_trigger();   // the scoring kernel may be scheduled now; it waits for this grid before its first read
     const uint32_t p = blockIdx.x;
     const uint32_t o0 = poff[p], n = poff[p + 1] - o0;
+    if (n == 0) {            // padding slot of an incremental chunk: no bits, an all-absent table row
+        for (uint32_t i = threadIdx.x; i < stride; i += blockDim.x) ptab[(size_t)p * stride + i] = 0;
+        return;
+    }
     const uint16_t *s = pstep + o0;
     for (uint32_t i = threadIdx.x; i <= L; i += blockDim.x) row[i] = 0xFFFFFFFFu;
     __syncthreads();
@@ -661,7 +667,7 @@ __device__ __forceinline__ void settle(const ScoreArgs &a, uint32_t p_glob, cons
         bad = v == kBad;
         if (v == kExact) {
             const uint32_t idx = atomicAdd(a.work_count, 1u);
-            if (idx < a.work_cap) a.work[idx] = make_uint2(p_glob, sorted);
+            if (idx < a.work_cap) a.work[idx] = make_uint2(p_glob | a.path_tag, sorted);
             else atomicOr(a.work_count + 1, 1u);
         }
     }
@@ -804,9 +810,10 @@ score_paths_kernel(const ScoreArgs a, const uint32_t tile_lo, const uint32_t til
     __syncthreads();
     // alignments without steps pass the filter and score 0 against every path: good
     const uint32_t empty_rows = (add_empty && blockIdx.x == 0) ? a.bk.count[0] : 0u;
+    const size_t set_off = ((a.path_tag >> 30) & 1u) << 1;
     for (uint32_t i = threadIdx.x; i < 2 * pc; i += blockDim.x) {
         const uint32_t v = s_cnt[i] + ((i & 1u) ? empty_rows : 0u);
-        if (v) atomicAdd(&a.counts[2 * (size_t)p_base + i], v);
+        if (v) atomicAdd(&a.counts[(size_t)a.count_stride * (p_base + (i >> 1)) + set_off + (i & 1u)], v);
     }
 }
 
@@ -827,23 +834,25 @@ slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
         uint2 w = slow[idx];
         if (w.x == kSlowHole) continue;     // unused tail of a warp's reserved window
         const uint32_t guess = w.x >> 31;   // the bitset kernel already counted this pair good (1) / bad (0)
-        w.x &= 0x7FFFFFFFu;
+        w.x &= 0x7FFFFFFFu;                 // bit 30 (accumulator set) travels on to the exact list
+        const uint32_t p = entry_path(w.x);
+        const size_t cb = entry_count_base(a.count_stride, w.x);
         const RowRef r = locate_row(a.bk, w.y);
         const int m = (int)r.m;
-        const uint32_t po = a.poff[w.x];
-        const int n = (int)(a.poff[w.x + 1] - po);
-        const uint16_t *tab = a.ptab + (size_t)w.x * a.tab_stride;
+        const uint32_t po = a.poff[p];
+        const int n = (int)(a.poff[p + 1] - po);
+        const uint16_t *tab = a.ptab + (size_t)p * a.tab_stride;
         // always walk the visit chain: a pair the bitsets flagged for a twice-visited node needs
         // it, and for a start-overhang suspect it finds nothing at the cost of one table read
         const int v = slow_verdict(a.pstep + po, a.pnext + po, n, tab, r.ptr, m, true);
         if (v == kExact) {
-            atomicSub(&a.counts[2 * (size_t)w.x + guess], 1u);   // the exact DP adds the right one
+            atomicSub(&a.counts[cb + guess], 1u);   // the exact DP adds the right one
             const uint32_t k = atomicAdd(a.work_count, 1u);
             if (k < a.work_cap) a.work[k] = w;
             else atomicOr(a.work_count + 1, 1u);
         } else if ((v == kGood ? 1u : 0u) != guess) {          // correct the rare wrong guess
-            atomicSub(&a.counts[2 * (size_t)w.x + guess], 1u);
-            atomicAdd(&a.counts[2 * (size_t)w.x + (guess ^ 1u)], 1u);
+            atomicSub(&a.counts[cb + guess], 1u);
+            atomicAdd(&a.counts[cb + (guess ^ 1u)], 1u);
         }
     }
 }
@@ -874,7 +883,7 @@ exact_worklist_kernel(const ScoreArgs a) {
             if (idx < cnt) {
                 w[k] = a.work[idx];
                 const uint32_t m = locate_row(a.bk, w[k].y).m;
-                const uint32_t n = a.poff[w[k].x + 1] - a.poff[w[k].x];
+                const uint32_t n = a.poff[entry_path(w[k].x) + 1] - a.poff[entry_path(w[k].x)];
                 const uint32_t tier = m <= 8 ? 0u : (m <= 16 ? 1u : 2u);
                 // long alignments: exact_worklist_long_kernel
                 bin[k] = m > (uint32_t)kExactRegSteps ? (uint32_t)kExactBins - 1u : tier * 8u + min(n >> 5, 7u);
@@ -902,13 +911,14 @@ exact_worklist_kernel(const ScoreArgs a) {
         for (uint32_t j = threadIdx.x; j < todo; j += blockDim.x) {
             const uint2 it = s_item[j];
             const RowRef r = locate_row(a.bk, it.y);
-            const uint32_t po = a.poff[it.x];
-            const int n = (int)(a.poff[it.x + 1] - po);
+            const uint32_t p = entry_path(it.x);
+            const uint32_t po = a.poff[p];
+            const int n = (int)(a.poff[p + 1] - po);
             int tf, tr;
-            exact_both(a.pstep + po, n, a.ptab + (size_t)it.x * a.tab_stride, a.pnext + po, r.ptr, (int)r.m, false,
+            exact_both(a.pstep + po, n, a.ptab + (size_t)p * a.tab_stride, a.pnext + po, r.ptr, (int)r.m, false,
                        &tf, &tr);
             const bool good = (tf == 0) || (tr == 0);
-            atomicAdd(&a.counts[2 * (size_t)it.x + (good ? 1 : 0)], 1u);
+            atomicAdd(&a.counts[entry_count_base(a.count_stride, it.x) + (good ? 1 : 0)], 1u);
         }
         __syncthreads();
     }
@@ -923,8 +933,8 @@ exact_worklist_long_kernel(const ScoreArgs a) {
         const RowRef r = locate_row(a.bk, w.y);
         const int m = (int)r.m;
         if (m <= kExactRegSteps) continue;
-        const uint32_t po = a.poff[w.x];
-        const int n = (int)(a.poff[w.x + 1] - po);
+        const uint32_t po = a.poff[entry_path(w.x)];
+        const int n = (int)(a.poff[entry_path(w.x) + 1] - po);
         int tf = warp_exact_T(a.pstep + po, n, r.ptr, m, false, scratch);
         __syncwarp();
         int tr = -1;
@@ -932,7 +942,7 @@ exact_worklist_long_kernel(const ScoreArgs a) {
         __syncwarp();
         if ((threadIdx.x & 31) == 0) {
             const bool good = (tf == 0) || (tr == 0);
-            atomicAdd(&a.counts[2 * (size_t)w.x + (good ? 1 : 0)], 1u);
+            atomicAdd(&a.counts[entry_count_base(a.count_stride, w.x) + (good ? 1 : 0)], 1u);
         }
     }
 }
@@ -1048,6 +1058,113 @@ pair_exact_long_kernel(const PairArgs a) {
             const int best = tf > tr ? tf : tr;
             atomicAdd(&a.counts[best < 0 ? 0 : 1], 1u);
         }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Inverted index of the bucketed view (see InvIndex, kernels.cuh).  One thread per bucketed row.
+// ------------------------------------------------------------------------------------------------
+template <bool kFill>
+__global__ void __launch_bounds__(kBlock)
+index_rows_kernel(const Buckets bk, const uint32_t L, const uint32_t root, uint32_t *__restrict__ cnt,
+                  uint32_t *__restrict__ rows) {
+    const uint32_t lo = bk.row_start[1], hi = bk.row_start[kLongBucket];
+    for (uint32_t s = lo + blockIdx.x * blockDim.x + threadIdx.x; s < hi; s += gridDim.x * blockDim.x) {
+        int b = 0;
+#pragma unroll
+        for (int k = 1; k < kNumBuckets; ++k) b += (s >= bk.row_start[k]) ? 1 : 0;
+        const uint32_t r = s - bk.row_start[b];
+        const uint16_t *p = bk.bstep + bk.step_base[b] + (size_t)r * row_stride(b);
+        uint32_t node[kMaxBucket];
+        bool outside = false, in_f = false;
+#pragma unroll
+        for (int j = 0; j < kMaxBucket; ++j) {
+            node[j] = j < b ? (uint32_t)(__ldg(p + j) >> 1) : 0xFFFFFFFFu;
+            if (j < b) {
+                outside |= node[j] >= L;
+                in_f |= node[j] == root;
+            }
+        }
+        if (outside) continue;          // filtered out for every path
+        if (in_f) {
+            const uint32_t g = L * kIdxLens + (uint32_t)b;
+            const uint32_t slot = atomicAdd(&cnt[g], 1u);
+            if (kFill) rows[slot] = r;
+            continue;
+        }
+#pragma unroll
+        for (int j = 0; j < kMaxBucket; ++j) {
+            if (j >= b) break;
+            bool seen = false;
+#pragma unroll
+            for (int i = 0; i < kMaxBucket; ++i)
+                if (i < j) seen |= node[i] == node[j];
+            if (seen) continue;
+            const uint32_t g = node[j] * kIdxLens + (uint32_t)b;
+            const uint32_t slot = atomicAdd(&cnt[g], 1u);
+            if (kFill) rows[slot] = r;
+        }
+    }
+}
+
+// exclusive scan of `groups` counters into off[0..groups] (one CTA; a one-off per universe) + cursor copy
+__global__ void __launch_bounds__(1024)
+index_scan_kernel(const uint32_t *__restrict__ cnt, uint32_t groups, uint32_t *__restrict__ off,
+                  uint32_t *__restrict__ cursor) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    for (uint32_t base = 0; base < groups; base += 1024) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < groups ? cnt[i] : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(kFull, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_warp[wid] = incl;
+        __syncthreads();
+        if (wid == 0) {
+            uint32_t w = s_warp[lane], wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(kFull, wi, o);
+                if (lane >= o) wi += t;
+            }
+            s_warp[lane] = wi - w;
+        }
+        __syncthreads();
+        const uint32_t excl = s_carry + s_warp[wid] + incl - v;
+        if (i < groups) {
+            off[i] = excl;
+            cursor[i] = excl;
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) off[groups] = s_carry;
+}
+
+// One warp per candidate path: base path (raw global ids) + suffix -> universe-local 16-bit steps.
+__global__ void __launch_bounds__(256) assemble_paths_kernel(const AssembleArgs a) {
+    const uint32_t p = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (p >= a.P) return;
+    const uint4 d = a.desc[p];
+    if (d.x == 0xFFFFFFFFu) return;                    // padding slot of a chunk: an empty path
+    const uint32_t b0 = a.base_off[d.x], nb = a.base_off[d.x + 1] - b0;
+    const uint32_t total = nb + d.z - d.w;             // d.w steps dropped at the end (the parent of a child)
+    uint16_t *out = a.out + a.poff[p];
+    for (uint32_t i = lane; i < total; i += 32) {
+        const uint32_t s = i < nb ? a.base_steps[b0 + i] : a.suffix_steps[d.y + (i - nb)];
+        const uint32_t node = s >> 1;
+        uint32_t l = node < a.n_nodes ? a.map[node] : a.L;
+        if (l >= a.L) { atomicOr(a.err, 1u); l = a.L; }
+        out[i] = (uint16_t)((l << 1) | (s & 1u));
     }
 }
 
@@ -1186,6 +1303,30 @@ void launch_pair_classify(const PairArgs &a, int sm_count, cudaStream_t st) {
 
 void launch_pair_exact(const PairArgs &a, cudaStream_t st) {
     pair_exact_kernel<<<148 * 4, 128, ((size_t)a.n * 2 + 15) & ~(size_t)15, st>>>(a);
+}
+
+void launch_index_count(const Buckets &bk, uint32_t L, uint32_t root_local, uint32_t *cnt, cudaStream_t st) {
+    const uint32_t n = bk.row_start[kLongBucket] - bk.row_start[1];
+    if (!n) return;
+    index_rows_kernel<false><<<std::min<uint32_t>((n + kBlock - 1) / kBlock, 148 * 16), kBlock, 0, st>>>(
+        bk, L, root_local, cnt, nullptr);
+}
+
+void launch_index_scan(const uint32_t *cnt, uint32_t groups, uint32_t *off, uint32_t *cursor, cudaStream_t st) {
+    index_scan_kernel<<<1, 1024, 0, st>>>(cnt, groups, off, cursor);
+}
+
+void launch_index_fill(const Buckets &bk, uint32_t L, uint32_t root_local, uint32_t *cursor, uint32_t *rows,
+                       cudaStream_t st) {
+    const uint32_t n = bk.row_start[kLongBucket] - bk.row_start[1];
+    if (!n) return;
+    index_rows_kernel<true><<<std::min<uint32_t>((n + kBlock - 1) / kBlock, 148 * 16), kBlock, 0, st>>>(
+        bk, L, root_local, cursor, rows);
+}
+
+void launch_assemble_paths(const AssembleArgs &a, cudaStream_t st) {
+    if (!a.P) return;
+    assemble_paths_kernel<<<(a.P * 32 + 255) / 256, 256, 0, st>>>(a);
 }
 
 void launch_pair_exact_long(const PairArgs &a, uint32_t max_m, cudaStream_t st) {

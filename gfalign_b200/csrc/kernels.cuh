@@ -90,7 +90,16 @@ struct ScoreArgs {
     uint2 *work;              // exact-DP worklist (path, sorted row)
     uint32_t *work_count;     // [0] entries, [1] overflow flag
     uint32_t work_cap;
+    // count record of path p, accumulator set s (list entries carry s in bit 30 of the path field):
+    // counts[count_stride * p + 2 * s + {0: bad, 1: good}]; plain batches: stride 2, one set
+    uint32_t count_stride = 2;
+    uint32_t path_tag = 0;    // OR-ed into the path field of the entries score_paths_kernel queues (set << 30)
 };
+constexpr uint32_t kPathMask = 0x3FFFFFFFu;   // path index inside a list entry's x (bit 31 guess, bit 30 set)
+__host__ __device__ inline uint32_t entry_path(uint32_t x) { return x & kPathMask; }
+__host__ __device__ inline size_t entry_count_base(uint32_t stride, uint32_t x) {
+    return (size_t)stride * (x & kPathMask) + (((x >> 30) & 1u) << 1);
+}
 
 struct PairDict {
     uint32_t *keys;           // kPairHashCap slots, kPairEmpty = free
@@ -123,6 +132,36 @@ struct BitsetArgs {
     uint32_t *unit_ctr;       // per chunk: next unit (dynamic scheduling), zeroed per launch
     uint2 *slow;              // (path, sorted row) pairs the bitsets cannot settle
     uint32_t *work_count;     // [0..1] exact list count/overflow, [2..3] slow list count/overflow
+    uint32_t slow_cap;
+};
+
+// Inverted index of the scoring view (incremental search scoring): for every universe
+// node v and row length m the bucket-local ids of the rows of length m that contain v — except the rows
+// of F = {rows containing the root node (path[0] of every candidate: the only rows that can overhang
+// the path start, SURVEY.md A.3 class iv)}, which form the groups of pseudo-node L.  Rows naming a
+// node outside the universe appear nowhere (the id filter drops them for every path).  Long rows
+// (m > kMaxBucket) are not indexed: they are scored afresh for every path like F.
+constexpr int kIdxLens = kMaxBucket + 1;      // group (v, m) at v * kIdxLens + m, m = 1..kMaxBucket
+struct InvIndex {
+    const uint32_t *off;      // (L + 1) * kIdxLens + 1
+    const uint32_t *rows;     // bucket-local row ids
+};
+
+// Incremental batch: chunks of <= 32 paths (one word, W = 1) that END IN THE SAME NODE v.  Pass 0 scores
+// the rows of list(v) (accumulator set 0), pass 1 the rows of F (set 1).
+struct IncrArgs {
+    Buckets bk;
+    MaskGeom mg;              // W = 1
+    InvIndex inv;
+    const uint32_t *masks;    // [chunks][entries]
+    const uint32_t *fplane;   // [chunks][L+1] x {F+, F-}
+    const uint32_t *chunk_node;   // per chunk: local node of pass 0, 0xFFFFFFFF = no pass 0
+    uint32_t chunks;
+    uint32_t *counts;         // [chunks * 32][4]: {bad, good} of set 0, {bad, good} of set 1
+    uint32_t unit_rows;
+    uint32_t *unit_ctr;       // per chunk, zeroed per launch
+    uint2 *slow;
+    uint32_t *work_count;
     uint32_t slow_cap;
 };
 
@@ -266,6 +305,27 @@ void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P
 void launch_score_paths(const ScoreArgs &a, int sm_count, uint32_t tile_lo, uint32_t tile_hi,
                         bool add_empty, cudaStream_t st);
 void launch_score_bitset(const BitsetArgs &a, int sm_count, cudaStream_t st);
+void launch_score_incr(const IncrArgs &a, int sm_count, cudaStream_t st);
+// inverted index: count -> scan -> fill.  cnt/off have (L + 1) * kIdxLens + 1 words
+void launch_index_count(const Buckets &bk, uint32_t L, uint32_t root_local, uint32_t *cnt, cudaStream_t st);
+void launch_index_scan(const uint32_t *cnt, uint32_t groups, uint32_t *off, uint32_t *cursor, cudaStream_t st);
+void launch_index_fill(const Buckets &bk, uint32_t L, uint32_t root_local, uint32_t *cursor, uint32_t *rows,
+                       cudaStream_t st);
+// candidate paths given as (base path, suffix) pairs -> local 16-bit steps at out[poff[p]..]; desc[p] =
+// {base id or 0xFFFFFFFF, first suffix step, suffix steps, steps to drop at the end}
+struct AssembleArgs {
+    const uint4 *desc;
+    uint32_t P;
+    const uint32_t *base_off;     // raw base paths (global ids)
+    const uint32_t *base_steps;
+    const uint32_t *suffix_steps;
+    const uint32_t *poff;         // P + 1, lengths as the host computed them
+    const uint32_t *map;          // node -> local
+    uint32_t n_nodes, L;
+    uint16_t *out;
+    uint32_t *err;
+};
+void launch_assemble_paths(const AssembleArgs &a, cudaStream_t st);
 void launch_slow_worklist(const ScoreArgs &a, const uint2 *slow, const uint32_t *slow_count,
                           uint32_t slow_cap, cudaStream_t st);
 void launch_exact_worklist(const ScoreArgs &a, cudaStream_t st);

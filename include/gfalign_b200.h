@@ -80,6 +80,37 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe);
 int gfe_score_paths(gfe_engine *e, const uint32_t *path_offsets, const uint32_t *path_steps,
                     uint32_t P, int filter, uint32_t *counts);
 
+/* ---- search scoring, incremental ------------------------------------------------------------------
+ * The search expands a path by ONE step at a time (reference src/eval.cpp:146-163: newPath = u + v,
+ * then evaluatePath(newPath)).  Relative to its parent, a child can change the verdict only of the
+ * alignments that contain the appended node (a new occurrence must end at the new step; a newly
+ * passing alignment must name the new node) and of the alignments that contain the root node
+ * (path[0]; the start-overhang class of the traceback).  The engine keeps an inverted
+ * node -> alignment index of the scoring view and scores exactly those.
+ *
+ * Candidate paths are given as (base path, suffix) pairs so that a batch of siblings / a speculated
+ * subtree shares its long common prefixes: path i = bases[item_base[i]] ++ suffix i.  All paths start
+ * at the same node (the root).  Per path, counts[4i..4i+3] =
+ *   mode 0 (full):   bad, good of evaluatePath(path) over ALL alignments; then bad, good over the
+ *                    alignments of the fresh set F (root-node and > 16-step alignments, empty ones)
+ *   mode 1 (delta):  bad(path) - bad(parent), good(path) - good(parent) over the alignments OUTSIDE
+ *                    F, parent = path minus its last step; then bad, good of the path over F.
+ *                    Requires the parent to have at least 16 steps.
+ * so  counts(child) = [counts(parent) - F(parent)] + delta(child) + F(child), bit-exact.
+ * Only with the id filter (search); returns GFE_ERR_STATE when the universe has no pair dictionary
+ * (the caller then uses gfe_score_paths). */
+typedef struct gfe_path_batch {
+    uint32_t n_bases;
+    const uint32_t *base_offsets;     /* n_bases + 1 */
+    const uint32_t *base_steps;       /* oriented steps, global dense ids */
+    uint32_t P;
+    const uint32_t *item_base;        /* P: index of the item's base path */
+    const uint32_t *suffix_offsets;   /* P + 1 */
+    const uint32_t *suffix_steps;
+    const uint8_t *mode;              /* P: 0 full, 1 delta */
+} gfe_path_batch;
+int gfe_score_paths_incremental(gfe_engine *e, const gfe_path_batch *batch, int32_t *counts /* P x 4 */);
+
 /* Same with every buffer already on the device and no host synchronisation: work is enqueued on
  * `cuda_stream` (a cudaStream_t; NULL = the CUDA default stream).  d_counts (P x 2, uint32) is zeroed
  * and filled by the enqueued work, so a collective (NCCL all-reduce over alignment shards) can
