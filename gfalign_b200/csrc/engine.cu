@@ -134,6 +134,10 @@ int gfe_create(int cuda_device, gfe_engine **out) {
 
 void gfe_destroy(gfe_engine *e) {
     if (!e) return;
+    if (getenv("GFE_DEBUG_TIMING") && e->incr_n[0])
+        fprintf(stderr, "[gfe incremental] %llu batches, %llu paths, %llu chunks, %llu full-scan items; host prep %.3f s, "
+                        "enqueue %.3f s, wait %.3f s\n", (unsigned long long)e->incr_n[0], (unsigned long long)e->incr_n[1],
+                (unsigned long long)e->incr_n[2], (unsigned long long)e->incr_n[3], e->incr_t[0], e->incr_t[1], e->incr_t[2]);
     cudaSetDevice(e->device);
     if (e->stream) cudaStreamSynchronize(e->stream);
     e->free_all();
@@ -804,8 +808,13 @@ constexpr size_t kHdrWords = 16;   // [8 work counters][bad-step flag][sticky ov
 inline size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 }  // namespace
 
+static inline double now_s() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_t *counts) {
     if (!e || !b || !counts) return GFE_ERR_ARG;
+    const double t_begin = now_s();
     if (!e->have_alignments || !e->have_universe) {
         set_error(e, "gfe_score_paths_incremental: alignments and universe must be set first");
         return GFE_ERR_STATE;
@@ -898,7 +907,16 @@ static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_
         slots.push_back(Slot{v, i, 0});
         if (revisit) slots.push_back(Slot{v, i, 1});
     }
-    std::stable_sort(slots.begin(), slots.end(), [](const Slot &x, const Slot &y) { return x.key < y.key; });
+    {   // stable counting sort by key (keys are local node ids; kNoNode sorts last)
+        std::vector<uint32_t> &cnt = e->h_key_count;
+        cnt.assign((size_t)e->L + 2, 0u);
+        for (const Slot &sl : slots) cnt[std::min<uint32_t>(sl.key, e->L) + 1]++;
+        for (size_t k = 1; k < cnt.size(); ++k) cnt[k] += cnt[k - 1];
+        std::vector<Slot> &sorted = e->h_slots2;
+        sorted.resize(slots.size());
+        for (const Slot &sl : slots) sorted[cnt[std::min<uint32_t>(sl.key, e->L)]++] = sl;
+        slots.swap(sorted);
+    }
     // chunks of 32 slots, never mixing keys; device path d = 32 * chunk + position
     std::vector<uint32_t> &chunk_node = e->h_chunk_node;
     std::vector<uint32_t> &slot_dev = e->h_slot_dev;
@@ -964,6 +982,7 @@ static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_
     }
     h_poff[P_dev] = dtotal;
     memcpy(hs + o_cn, chunk_node.data(), (size_t)chunks * 4);
+    const double t_prep = now_s();
     CUDA_TRY(e, cudaMemcpyAsync(e->d_stage.ptr, hs, bytes, cudaMemcpyHostToDevice, st));
     // ---- device buffers ------------------------------------------------------------------------------
     const size_t res_words = kHdrWords + (size_t)n_full * 2 + (size_t)P_dev * 4;
@@ -1096,7 +1115,16 @@ static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_
                           d_hdr + kWorkCounters + 1, st));
     }
     CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, res_words * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    const double t_enq = now_s();
     CUDA_TRY(e, cudaStreamSynchronize(st));
+    const double t_done = now_s();
+    e->incr_t[0] += t_prep - t_begin;
+    e->incr_t[1] += t_enq - t_prep;
+    e->incr_t[2] += t_done - t_enq;
+    e->incr_n[0] += 1;
+    e->incr_n[1] += P;
+    e->incr_n[2] += chunks;
+    e->incr_n[3] += n_full;
     if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
     e->h2d_bytes += bytes;
     e->d2h_bytes += res_words * sizeof(uint32_t);

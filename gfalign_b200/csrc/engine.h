@@ -64,10 +64,13 @@ struct gfe_engine {
     bool have_index = false;
     uint64_t inv_entries = 0;
     int incr_retries = 0;
+    double incr_t[3] = {0, 0, 0};     // GFE_DEBUG_TIMING: host prep / enqueue / wait seconds of the incremental batches
+    uint64_t incr_n[4] = {0, 0, 0, 0};
     // host scratch of gfe_score_paths_incremental (kept to avoid per-batch allocation)
     struct IncrSlot { uint32_t key, item, parent; };
     std::vector<uint32_t> h_present, h_chunk_node, h_slot_dev, h_len_dev, h_full_of_item;
-    std::vector<IncrSlot> h_slots;
+    std::vector<IncrSlot> h_slots, h_slots2;
+    std::vector<uint32_t> h_key_count;
 
     // candidate-path staging and results
     PinBuf<unsigned char> h_stage;

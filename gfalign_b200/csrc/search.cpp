@@ -15,9 +15,13 @@
 // it has not been asked about yet.  On a miss it sends the children of the extracted path plus a
 // breadth-first subtree below them in ONE kernel batch and caches the counts on the path tree.
 #include <chrono>
+#include <climits>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <deque>
+#include <queue>
+#include <utility>
 #include <vector>
 
 #include "../../include/gfalign_b200.h"
@@ -180,6 +184,14 @@ struct PathNode {
     uint32_t child_begin = 0, child_count = 0;
     uint8_t root_or = 0;   // depth-2 nodes: orientation the source is left in (src/eval.cpp:148-149)
     bool scored = false, expanded = false;
+    bool kids_scored = false;        // every child carries its counts (or is in flight in the current batch)
+    // counts over the alignments outside the fresh set F (incremental scoring, gfe_score_paths_incremental)
+    int32_t main_bad = 0, main_good = 0;
+    int32_t key = 0;                 // alt = bad - good - uniques, the path's heap key (src/eval.cpp:163)
+    // speculation priority: the replay reaches a cached path only after every ancestor was extracted,
+    // i.e. not before the largest key on the way down from the heap: eff = max(key, eff(parent))
+    int32_t eff = INT32_MIN;
+    bool extracted = false;
 };
 
 struct Driver {
@@ -209,13 +221,14 @@ struct Driver {
     }
 
     // children of x per src/eval.cpp:136-151; `path` is x's materialised path and occ[] its visits
-    void expand(uint32_t x, const std::vector<uint32_t> &path) {
+    void expand(uint32_t x, const std::vector<uint32_t> &path) { expand(x, path.back(), path[0] >> 1); }
+    // the same from the path's ends: `last` = its last step (== T[x].step), root_node = node of path[0]
+    void expand(uint32_t x, uint32_t last, uint32_t root_node) {
         PathNode &nx = T[x];
         nx.expanded = true;
         const uint32_t begin = (uint32_t)T.size();
-        const uint32_t last = path.back(), node = last >> 1;
-        const bool is_root = path.size() == 1;
-        const uint32_t root_node = path[0] >> 1;
+        const uint32_t node = last >> 1;
+        const bool is_root = T[x].depth == 1;
         uint32_t count = 0;
         for (uint32_t k = g->adj_offsets[node]; k < g->adj_offsets[node + 1]; ++k) {
             if (!is_root && (last & 1u) != g->adj_or0[k]) continue;
@@ -319,6 +332,206 @@ struct Driver {
         return rc;
     }
 
+    // ---- engine-backed scoring: incremental, several speculation roots ------------------------------
+    // evaluatePath(child) differs from evaluatePath(parent) only on the alignments that contain the
+    // appended node or the root node (gfe_score_paths_incremental); the batch therefore carries, for
+    // every candidate, (base path of its speculation root, suffix below it) and asks for the delta.
+    // Roots: the extracted path x (its children are REQUIRED) and the best other frontier paths of the
+    // heap (lowest key first) whose children are not scored yet — the paths the replay will extract next.
+    gfe_engine *eng = nullptr;
+    // (key, node) of every scored, non-final path whose children are not scored yet — in the heap or
+    // still below it in the cached tree: where the replay can miss next, best key first
+    // min-heap with lazy deletion: an entry is live while its node still lacks scored children and its
+    // priority is the node's current eff
+    struct FrontCmp {
+        bool operator()(const std::pair<int32_t, uint32_t> &a, const std::pair<int32_t, uint32_t> &b) const {
+            return a > b;
+        }
+    };
+    std::priority_queue<std::pair<int32_t, uint32_t>, std::vector<std::pair<int32_t, uint32_t>>, FrontCmp> front;
+    std::vector<std::pair<int32_t, uint32_t>> front_keep;
+    // candidates per batch / speculation roots per batch / live front entries examined per batch: measured
+    // optimum on cfg3 (profiles/r02_search_sweep.txt): many roots with a small subtree each
+    uint32_t spec_width = 4096, spec_roots = 256, spec_scan = 4096;
+    std::vector<uint32_t> t_base_off, t_base_steps, t_item_base, t_suf_off, t_suf_steps, t_items, t_parents;
+    std::vector<uint8_t> t_mode;
+    std::vector<int32_t> t_counts;
+    std::vector<uint32_t> root_path, t_kids;
+
+    // The materialised path of ONE tree node at a time (`cur`), with occ[] = its visit counts; moving to
+    // another node costs the tree distance, not the depth: speculation roots are mostly close relatives.
+    uint32_t cur = kNoParent;
+    std::vector<uint32_t> cur_path, chain, climb;   // chain[d-1] = tree node of depth d on the way to cur
+    void move_to(uint32_t r) {
+        climb.clear();
+        uint32_t a = r;
+        while (a != kNoParent && (cur == kNoParent || T[a].depth > cur_path.size() || chain[T[a].depth - 1] != a)) {
+            climb.push_back(a);
+            a = T[a].parent;
+        }
+        const size_t keep = a == kNoParent ? 0 : T[a].depth;
+        while (cur_path.size() > keep) {
+            occ[cur_path.back() >> 1]--;
+            cur_path.pop_back();
+            chain.pop_back();
+        }
+        for (size_t i = climb.size(); i-- > 0;) {
+            const uint32_t y = climb[i];
+            cur_path.push_back(T[y].step);
+            chain.push_back(y);
+            occ[T[y].step >> 1]++;
+        }
+        // the source's orientation is the one its first edge left it in (src/eval.cpp:148-149)
+        if (cur_path.size() >= 2) cur_path[0] = (cur_path[0] & ~1u) | T[chain[1]].root_or;
+        cur = r;
+    }
+    void leave_path() {   // back to the neutral state the full-scan driver expects (occ[] all zero)
+        for (uint32_t s : cur_path) occ[s >> 1]--;
+        cur_path.clear();
+        chain.clear();
+        cur = kNoParent;
+    }
+
+    // BFS below root r (path `rp`, occ[] holds its visits): one item per unscored child.  A node's
+    // children are taken all or none; the walk stops when the next node's children no longer fit
+    // `budget` (the children of r itself are taken regardless when `required`).
+    void speculate_below(uint32_t r, const std::vector<uint32_t> &rp, uint32_t budget, bool required) {
+        const uint32_t base_depth = T[r].depth;
+        const bool base_fixed = rp.size() > 1;     // else r is the search root: orientation per first edge
+        uint32_t kb[2] = {kNoParent, kNoParent};   // base id per root orientation (base_fixed: kb[0] only)
+        auto base_for = [&](uint32_t orient) -> uint32_t {
+            const uint32_t k = base_fixed ? 0u : orient;
+            if (kb[k] == kNoParent) {
+                kb[k] = (uint32_t)t_base_off.size() - 1;
+                const size_t at = t_base_steps.size();
+                t_base_steps.insert(t_base_steps.end(), rp.begin(), rp.end());
+                if (!base_fixed) t_base_steps[at] = (rp[0] & ~1u) | orient;
+                t_base_off.push_back((uint32_t)t_base_steps.size());
+            }
+            return kb[k];
+        };
+        std::deque<uint32_t> frontier;
+        frontier.push_back(r);
+        uint32_t taken = 0, visited = 0;
+        while (!frontier.empty() && visited < 4 * budget + 16) {
+            const uint32_t y = frontier.front();
+            frontier.pop_front();
+            ++visited;
+            if (T[y].depth > GFE_MAX_STEPS - 1) continue;   // children would exceed MAX_N
+            suffix.resize(T[y].depth - base_depth);
+            for (uint32_t cur = y, i = (uint32_t)suffix.size(); cur != r; cur = T[cur].parent)
+                suffix[--i] = T[cur].step;
+            if (!T[y].expanded) {
+                for (uint32_t s : suffix) occ[s >> 1]++;
+                expand(y, T[y].step, rp[0] >> 1);
+                for (uint32_t s : suffix) occ[s >> 1]--;
+            }
+            uint32_t open = 0;
+            for (uint32_t c = 0; c < T[y].child_count; ++c) open += T[T[y].child_begin + c].scored ? 0u : 1u;
+            if (open && !(required && y == r) && taken + open > budget) break;
+            for (uint32_t c = 0; c < T[y].child_count; ++c) {
+                const uint32_t ci = T[y].child_begin + c;
+                if (!T[ci].scored) {
+                    const uint32_t orient = base_fixed ? 0u : T[y == r ? ci : first_below(y, r)].root_or;
+                    t_items.push_back(ci);
+                    t_parents.push_back(y);
+                    t_item_base.push_back(base_for(orient));
+                    t_suf_steps.insert(t_suf_steps.end(), suffix.begin(), suffix.end());
+                    t_suf_steps.push_back(T[ci].step);
+                    t_suf_off.push_back((uint32_t)t_suf_steps.size());
+                    t_mode.push_back(T[y].depth >= 16 ? 1 : 0);   // delta needs a parent of >= 16 steps
+                    ++taken;
+                }
+                if ((T[ci].step >> 1) != prm->destination) frontier.push_back(ci);
+            }
+            t_kids.push_back(y);
+        }
+    }
+
+    int score_children_tree(uint32_t x) {
+        if (T[x].kids_scored && T[x].expanded) {
+            bool ok = true;
+            for (uint32_t c = 0; c < T[x].child_count; ++c) ok = ok && T[T[x].child_begin + c].scored;
+            if (ok) return GFE_OK;
+        }
+        t_base_off.assign(1, 0);
+        t_base_steps.clear(); t_item_base.clear(); t_suf_off.assign(1, 0); t_suf_steps.clear();
+        t_items.clear(); t_parents.clear(); t_mode.clear(); t_kids.clear();
+        const uint32_t width = prm->speculate ? prm->speculate : spec_width;
+        // root 0: the extracted path
+        move_to(x);
+        speculate_below(x, cur_path, std::max<uint32_t>(width / 2, 1), true);
+        // further roots: the best frontier paths of the heap whose children are not scored
+        if (width > 1 && spec_roots > 1) {
+            uint32_t picked = 0, scanned = 0;
+            const uint32_t per_root = std::max<uint32_t>((width - width / 2) / (spec_roots - 1), 1);
+            front_keep.clear();
+            while (!front.empty() && picked + 1 < spec_roots && scanned < spec_scan) {
+                const std::pair<int32_t, uint32_t> top = front.top();
+                front.pop();
+                const uint32_t r = top.second;
+                if (T[r].kids_scored || T[r].eff != top.first) continue;          // stale entry
+                ++scanned;
+                if (r == x || T[r].depth >= GFE_MAX_STEPS) {
+                    front_keep.push_back(top);
+                    continue;
+                }
+                move_to(r);
+                speculate_below(r, cur_path, per_root, false);
+                front_keep.push_back(top);   // dropped below once its children are in the batch
+                ++picked;
+            }
+        }
+        const uint32_t P = (uint32_t)t_items.size();
+        if (P == 0) {
+            T[x].kids_scored = true;
+            for (const auto &k : front_keep)
+                if (!T[k.second].kids_scored) front.push(k);
+            front_keep.clear();
+            return GFE_OK;
+        }
+        t_counts.resize((size_t)P * 4);
+        gfe_path_batch b;
+        b.n_bases = (uint32_t)t_base_off.size() - 1;
+        b.base_offsets = t_base_off.data();
+        b.base_steps = t_base_steps.data();
+        b.P = P;
+        b.item_base = t_item_base.data();
+        b.suffix_offsets = t_suf_off.data();
+        b.suffix_steps = t_suf_steps.data();
+        b.mode = t_mode.data();
+        auto t0 = std::chrono::steady_clock::now();
+        const int rc = gfe_score_paths_incremental(eng, &b, t_counts.data());
+        st.seconds_scoring += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        st.kernel_batches++;
+        st.paths_scored += P;
+        if (rc != GFE_OK) return rc;
+        for (uint32_t i = 0; i < P; ++i) {
+            PathNode &n = T[t_items[i]];
+            const int32_t *c = &t_counts[4 * (size_t)i];
+            if (t_mode[i]) {
+                const PathNode &par = T[t_parents[i]];
+                n.main_bad = par.main_bad + c[0];
+                n.main_good = par.main_good + c[1];
+            } else {
+                n.main_bad = c[0] - c[2];
+                n.main_good = c[1] - c[3];
+            }
+            n.bad = (uint32_t)(n.main_bad + c[2]);
+            n.good = (uint32_t)(n.main_good + c[3]);
+            n.scored = true;
+            n.key = (int32_t)n.bad - (int32_t)n.good - (int32_t)n.uniques;   // src/eval.cpp:163
+            const PathNode &pp = T[t_parents[i]];
+            n.eff = pp.extracted ? n.key : std::max(n.key, pp.eff);
+            if ((n.step >> 1) != prm->destination && n.depth < GFE_MAX_STEPS) front.push({n.eff, t_items[i]});
+        }
+        for (uint32_t y : t_kids) T[y].kids_scored = true;   // their front entries are stale from now on
+        for (const auto &k : front_keep)
+            if (!T[k.second].kids_scored) front.push(k);
+        front_keep.clear();
+        return GFE_OK;
+    }
+
     // the ancestor of y (or y itself) that is a direct child of x
     uint32_t first_below(uint32_t y, uint32_t x) const {
         uint32_t cur = y;
@@ -331,7 +544,7 @@ struct Driver {
 
 static int run_search(gfe_score_fn score, void *score_user, const gfe_graph *g,
                       const gfe_search_params *p, gfe_row_fn emit, void *user,
-                      gfe_search_stats *stats) {
+                      gfe_search_stats *stats, gfe_engine *eng = nullptr) {
     const auto t_begin = std::chrono::steady_clock::now();
     Driver d;
     d.score = score;
@@ -344,6 +557,12 @@ static int run_search(gfe_score_fn score, void *score_user, const gfe_graph *g,
         if (p->budget_nodes[i] >= g->n_nodes) return GFE_ERR_ARG;
         d.budget[p->budget_nodes[i]] = p->budget_counts[i];
     }
+    if (eng) {
+        d.eng = eng;
+        if (const char *v = getenv("GFE_SPEC_WIDTH")) d.spec_width = (uint32_t)std::max(1, atoi(v));
+        if (const char *v = getenv("GFE_SPEC_ROOTS")) d.spec_roots = (uint32_t)std::max(1, atoi(v));
+        if (const char *v = getenv("GFE_SPEC_SCAN")) d.spec_scan = (uint32_t)std::max(1, atoi(v));
+    }
     OrderHeap Q;
     PathNode root;
     root.parent = kNoParent;
@@ -351,6 +570,7 @@ static int run_search(gfe_score_fn score, void *score_user, const gfe_graph *g,
     root.depth = 1;
     root.uniques = 1;
     root.scored = true;
+    d.T.reserve(1u << 20);
     d.T.push_back(root);
     Q.insert(0, 0);
 
@@ -361,16 +581,32 @@ static int run_search(gfe_score_fn score, void *score_user, const gfe_graph *g,
     std::vector<uint32_t> visits(g->n_nodes, 0);
     int rc = GFE_OK;
 
+    const bool dbg = getenv("GFE_DEBUG_TIMING") != nullptr;
+    double t_heap = 0, t_score = 0, t_kids = 0;
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     while (Q.size() > 0 && steps < p->max_steps) {
+        const double t0 = dbg ? now() : 0;
         const uint32_t x = Q.extract_min();
+        const double t1 = dbg ? now() : 0;
+        t_heap += t1 - t0;
+        d.T[x].extracted = true;
         if (d.T[x].depth < GFE_MAX_STEPS) {
-            rc = d.score_children(x);
+            rc = eng ? d.score_children_tree(x) : d.score_children(x);
+            if (rc == GFE_ERR_STATE && eng) {
+                // no pair dictionary for this universe: the incremental path is off, use full scans
+                eng = nullptr;
+                d.eng = nullptr;
+                d.leave_path();
+                rc = d.score_children(x);
+            }
             if (rc != GFE_OK) break;
         } else {
             // the reference's dp[MAX_N][MAX_N] cannot hold a longer path (include/alignments.h:246)
             d.T[x].expanded = true;
             d.T[x].child_count = 0;
         }
+        const double t2 = dbg ? now() : 0;
+        t_score += t2 - t1;
         for (uint32_t c = 0; c < d.T[x].child_count; ++c) {
             const uint32_t ci = d.T[x].child_begin + c;
             const PathNode &n = d.T[ci];
@@ -382,6 +618,11 @@ static int run_search(gfe_score_fn score, void *score_user, const gfe_graph *g,
                     break;
                 }
                 Q.insert(ci, alt);
+                if (eng && d.T[ci].eff != alt) {      // now in the heap: reachable at its own key
+                    d.T[ci].eff = alt;
+                    if (!d.T[ci].kids_scored) d.front.push({alt, ci});
+                }
+
             } else {
                 ++path_counter;
                 d.materialise(ci, row_path);
@@ -415,9 +656,13 @@ static int run_search(gfe_score_fn score, void *score_user, const gfe_graph *g,
                 }
             }
         }
+        if (dbg) t_kids += now() - t2;
         if (rc != GFE_OK) break;
         ++steps;
     }
+    if (dbg)
+        fprintf(stderr, "[gfe search] extract_min %.3f s, score_children (incl. GPU %.3f s) %.3f s, insert/emit %.3f s, "
+                        "tree nodes %zu\n", t_heap, d.st.seconds_scoring, t_score, t_kids, d.T.size());
     d.st.extractions = steps;
     d.st.reached_max_steps = steps >= p->max_steps ? 1 : 0;
     d.st.seconds_total =
@@ -458,7 +703,9 @@ extern "C" int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_pa
     search_universe(g, p, uni);
     rc = gfe_set_universe(e, uni.data(), (uint32_t)uni.size());
     if (rc != GFE_OK) return rc;
-    return run_search(engine_scorer, e, g, p, emit, user, stats);
+    // GFE_SEARCH_FULLSCAN=1: every candidate through gfe_score_paths (the checker of the incremental path)
+    const char *fs = getenv("GFE_SEARCH_FULLSCAN");
+    return run_search(engine_scorer, e, g, p, emit, user, stats, (fs && fs[0] == '1') ? nullptr : e);
 }
 
 namespace {

@@ -118,3 +118,28 @@ def test_incremental_cfg5_shape_and_wide_batch(engine, oracle):
     rng = np.random.default_rng(4)
     n_delta = _check_batch(engine, oracle, w.offsets, w.steps, t.n_nodes, nodes, paths, rng, os.cpu_count() or 1)
     assert n_delta > 400
+
+
+def test_search_rows_incremental_equal_full_scan(engine):
+    """gfe_search with incremental scoring (default) emits the rows of the same search scored by full
+    scans (GFE_SEARCH_FULLSCAN=1), for several speculation widths; paths here reach ~100 steps."""
+    w = synth.make_workload("cfg3", A=40000)
+    t = w.tangle
+    nodes, counts, node_count = synth.node_table(t)
+    engine.set_alignments(w.offsets, w.steps, t.n_nodes)
+
+    def run(**kw):
+        rows, stats = engine.search(t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source, t.destination,
+                                    nodes, counts, node_count, max_steps=3000, return_all_paths=True, **kw)
+        return [r.columns(t.names) for r in rows], stats
+
+    os.environ["GFE_SEARCH_FULLSCAN"] = "1"
+    try:
+        want, st_full = run()
+    finally:
+        del os.environ["GFE_SEARCH_FULLSCAN"]
+    assert len(want) > 3
+    for spec in (0, 1, 64, 4096):
+        got, st = run(speculate=spec)
+        assert got == want, spec
+        assert st["evaluations"] == st_full["evaluations"]
