@@ -543,7 +543,7 @@ def main():
             try:
                 from gfalign_b200.sharded import PeerExchange
                 px = PeerExchange(P * 2, dev)
-                px_e2e = PeerExchange(max(P, 4096) * 2 + 1, dev)
+                px_e2e = PeerExchange(1 << 18, dev)     # also carries the search's incremental batches
                 exchange = "peer-memory sum kernel (NVLink P2P loads)"
             except Exception as ex:   # no peer access between the GPUs of this box
                 sys.stderr.write(f"[bench] peer exchange unavailable ({ex!r}); using NCCL\n")

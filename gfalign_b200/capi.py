@@ -86,7 +86,7 @@ EXPORTS = [
     "gfe_text_open", "gfe_text_close", "gfe_text_get", "gfe_text_node_name", "gfe_text_node_id",
     "gfe_text_qname", "gfe_peer_sum_u32", "gfe_device_status_to",
     "gfe_exchange_create", "gfe_exchange_destroy", "gfe_score_paths_sharded", "gfe_search_sharded",
-    "gfe_score_paths_incremental",
+    "gfe_score_paths_incremental", "gfe_score_paths_incremental_sharded",
 ]
 
 PEER_MAX = 16      # GFE_PEER_MAX
@@ -162,6 +162,7 @@ def load_library() -> C.CDLL:
     lib.gfe_peer_sum_u32.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_int, C.c_uint32, C.c_uint32,
                                      C.c_uint32, C.c_void_p, C.c_void_p]
     lib.gfe_score_paths_incremental.argtypes = [C.c_void_p, C.POINTER(_PathBatch), _i32p]
+    lib.gfe_score_paths_incremental_sharded.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(_PathBatch), _i32p]
     lib.gfe_exchange_create.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_int, C.c_uint32,
                                         C.POINTER(C.c_void_p)]
     lib.gfe_exchange_destroy.argtypes = [C.c_void_p]

@@ -812,7 +812,7 @@ static inline double now_s() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
-static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_t *counts) {
+static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path_batch *b, int32_t *counts) {
     if (!e || !b || !counts) return GFE_ERR_ARG;
     const double t_begin = now_s();
     if (!e->have_alignments || !e->have_universe) {
@@ -985,7 +985,7 @@ static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_
     const double t_prep = now_s();
     CUDA_TRY(e, cudaMemcpyAsync(e->d_stage.ptr, hs, bytes, cudaMemcpyHostToDevice, st));
     // ---- device buffers ------------------------------------------------------------------------------
-    const size_t res_words = kHdrWords + (size_t)n_full * 2 + (size_t)P_dev * 4;
+    const size_t res_words = kHdrWords + (size_t)n_full * 2 + (size_t)P_dev * 4 + 1;   // + the summed flags (sharded)
     TRY(ensure_pinned(e, e->h_counts, res_words));
     {
         const uint32_t *before = e->d_counts.ptr;
@@ -1021,6 +1021,19 @@ static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_
     TRY(ensure_dev(e, e->d_masks, table_words + fplane_words));
     TRY(ensure_dev(e, e->d_unit_ctr, chunks));
     uint32_t *d_hdr = e->d_counts.ptr, *d_full = d_hdr + kHdrWords, *d_inc = d_full + (size_t)n_full * 2;
+    uint32_t *d_sum = d_full;                 // where the host reads the (summed) records
+    const size_t rec_words = (size_t)n_full * 2 + (size_t)P_dev * 4;
+    if (x) {
+        // sharded: this rank's records accumulate in its half of the exchange buffer, one more slot carries
+        // its flags; the peer kernel sums all shards into the result block
+        if (rec_words + 1 > x->n_cap) {
+            set_error(e, "gfe_score_paths_incremental_sharded: batch needs %zu exchange slots, the buffer has %u",
+                      rec_words + 1, x->n_cap);
+            return GFE_ERR_LIMIT;
+        }
+        d_full = reinterpret_cast<uint32_t *>(x->bases[x->rank]) + (size_t)x->n_cap * ((x->epoch + 1) & 1u);
+        d_inc = d_full + (size_t)n_full * 2;
+    }
     const unsigned char *ds = e->d_stage.ptr;
     const uint32_t *d_poff = reinterpret_cast<const uint32_t *>(ds + o_poff);
     const PairDict pd{e->d_pair_keys.ptr, e->d_pair_ids.ptr, e->d_pair_ctr.ptr};
@@ -1114,6 +1127,17 @@ static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_
         TRY(enqueue_score(e, fs.poff, d_flocal, n_full, ftotal, 1, d_full, d_hdr, nullptr, d_hdr + kWorkCounters,
                           d_hdr + kWorkCounters + 1, st));
     }
+    if (x) {
+        launch_flag_word(d_hdr + kWorkCounters, d_hdr, d_full + rec_words, st);   // bad step | overflow of the last chain
+        launch_flag_or(d_hdr + kWorkCounters + 1, d_full + rec_words, st);        // | overflow of the first chain
+        e->kernel_launches += 3;
+        x->epoch += 1;
+        const int prc = gfe_peer_sum_u32(x->bases, x->world, x->rank, x->n_cap, (uint32_t)rec_words + 1, x->epoch, d_sum, st);
+        if (prc != GFE_OK) {
+            set_error(e, "gfe_score_paths_incremental_sharded: peer sum launch failed");
+            return prc;
+        }
+    }
     CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, res_words * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     const double t_enq = now_s();
     CUDA_TRY(e, cudaStreamSynchronize(st));
@@ -1129,12 +1153,17 @@ static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_
     e->h2d_bytes += bytes;
     e->d2h_bytes += res_words * sizeof(uint32_t);
     const uint32_t *h = e->h_counts.ptr;
+    const uint32_t any_flags = x ? h[kHdrWords + rec_words] : 0u;     // summed over the ranks
+    if (x && any_flags == GFE_PEER_TIMEOUT) {
+        set_error(e, "gfe_score_paths_incremental_sharded: a peer never reached epoch %u (GFE_PEER_TIMEOUT_MS)", x->epoch);
+        return GFE_ERR_CUDA;
+    }
     if (h[kWorkCounters]) {
         CUDA_TRY(e, cudaMemset(e->d_counts.ptr + kWorkCounters, 0, 2 * sizeof(uint32_t)));
         set_error(e, "gfe_score_paths_incremental: a step names a node outside the universe");
         return GFE_ERR_ARG;
     }
-    if (h[1] || h[3] || h[kWorkCounters + 1]) {
+    if (h[1] || h[3] || h[kWorkCounters + 1] || any_flags) {   // sharded: every rank repeats the batch together
         // a list overflowed in one of the two chains: grow both lists and redo the batch
         CUDA_TRY(e, cudaMemset(e->d_counts.ptr + kWorkCounters, 0, 2 * sizeof(uint32_t)));
         if (++e->incr_retries > 6 || e->d_slow.cap >= ((size_t)1 << 28)) {
@@ -1146,7 +1175,7 @@ static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_
         e->work_cap = std::min<size_t>(e->d_work.cap * 4, (size_t)1 << 28);
         TRY(ensure_dev(e, e->d_slow, e->slow_cap));
         TRY(ensure_dev(e, e->d_work, e->work_cap));
-        const int rc = score_incremental_impl(e, b, counts);
+        const int rc = score_incremental_impl(e, x, b, counts);
         e->incr_retries = 0;
         return rc;
     }
@@ -1181,7 +1210,13 @@ static int score_incremental_impl(gfe_engine *e, const gfe_path_batch *b, int32_
 extern "C" {
 
 int gfe_score_paths_incremental(gfe_engine *e, const gfe_path_batch *batch, int32_t *counts) {
-    return score_incremental_impl(e, batch, counts);
+    return score_incremental_impl(e, nullptr, batch, counts);
+}
+
+int gfe_score_paths_incremental_sharded(gfe_engine *e, gfe_exchange *x, const gfe_path_batch *batch,
+                                        int32_t *counts) {
+    if (!x) return GFE_ERR_ARG;
+    return score_incremental_impl(e, x, batch, counts);
 }
 
 int gfe_score_paths_device(gfe_engine *e, const uint32_t *d_path_offsets,

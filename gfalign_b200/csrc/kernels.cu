@@ -1235,6 +1235,14 @@ __global__ void flag_word_kernel(const uint32_t *err, const uint32_t *wc, uint32
     *out = (*err ? 1u : 0u) | ((wc[1] || wc[3]) ? 2u : 0u);
 }
 
+__global__ void flag_or_kernel(const uint32_t *sticky, uint32_t *out) {
+    if (*sticky) *out |= 2u;
+}
+
+void launch_flag_or(const uint32_t *sticky, uint32_t *out, cudaStream_t st) {
+    flag_or_kernel<<<1, 1, 0, st>>>(sticky, out);
+}
+
 void launch_flag_word(const uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st) {
     flag_word_kernel<<<1, 1, 0, st>>>(err, wc, out);
 }

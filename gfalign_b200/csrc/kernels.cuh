@@ -297,6 +297,8 @@ void launch_prologue(const PrologueArgs &a, int sm_count, cudaStream_t st);
 void launch_status_flag(uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st);
 // the same word without clearing anything (the host API reads the header itself afterwards)
 void launch_flag_word(const uint32_t *err, const uint32_t *wc, uint32_t *out, cudaStream_t st);
+// *out |= (*sticky ? 2 : 0)
+void launch_flag_or(const uint32_t *sticky, uint32_t *out, cudaStream_t st);
 // masks == nullptr: tables only (legacy kernel); else also ORs path p into the batch's bitsets
 void launch_build_tables(const uint32_t *poff, const uint16_t *pstep, uint32_t P, uint32_t L,
                          uint32_t tab_stride, uint16_t *ptab, uint16_t *pnext, uint32_t *masks,

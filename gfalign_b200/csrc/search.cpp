@@ -339,6 +339,7 @@ struct Driver {
     // Roots: the extracted path x (its children are REQUIRED) and the best other frontier paths of the
     // heap (lowest key first) whose children are not scored yet — the paths the replay will extract next.
     gfe_engine *eng = nullptr;
+    gfe_exchange *xch = nullptr;      // alignment shards: the same batches on every rank, records summed over the box
     // (key, node) of every scored, non-final path whose children are not scored yet — in the heap or
     // still below it in the cached tree: where the replay can miss next, best key first
     // min-heap with lazy deletion: an entry is live while its node still lacks scored children and its
@@ -501,7 +502,8 @@ struct Driver {
         b.suffix_steps = t_suf_steps.data();
         b.mode = t_mode.data();
         auto t0 = std::chrono::steady_clock::now();
-        const int rc = gfe_score_paths_incremental(eng, &b, t_counts.data());
+        const int rc = xch ? gfe_score_paths_incremental_sharded(eng, xch, &b, t_counts.data())
+                           : gfe_score_paths_incremental(eng, &b, t_counts.data());
         st.seconds_scoring += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         st.kernel_batches++;
         st.paths_scored += P;
@@ -544,7 +546,7 @@ struct Driver {
 
 static int run_search(gfe_score_fn score, void *score_user, const gfe_graph *g,
                       const gfe_search_params *p, gfe_row_fn emit, void *user,
-                      gfe_search_stats *stats, gfe_engine *eng = nullptr) {
+                      gfe_search_stats *stats, gfe_engine *eng = nullptr, gfe_exchange *xch = nullptr) {
     const auto t_begin = std::chrono::steady_clock::now();
     Driver d;
     d.score = score;
@@ -559,6 +561,7 @@ static int run_search(gfe_score_fn score, void *score_user, const gfe_graph *g,
     }
     if (eng) {
         d.eng = eng;
+        d.xch = xch;
         if (const char *v = getenv("GFE_SPEC_WIDTH")) d.spec_width = (uint32_t)std::max(1, atoi(v));
         if (const char *v = getenv("GFE_SPEC_ROOTS")) d.spec_roots = (uint32_t)std::max(1, atoi(v));
         if (const char *v = getenv("GFE_SPEC_SCAN")) d.spec_scan = (uint32_t)std::max(1, atoi(v));
@@ -731,7 +734,9 @@ extern "C" int gfe_search_sharded(gfe_engine *e, gfe_exchange *x, const gfe_grap
     rc = gfe_set_universe(e, uni.data(), (uint32_t)uni.size());
     if (rc != GFE_OK) return rc;
     ShardedUser u{e, x};
-    return run_search(sharded_scorer, &u, g, p, emit, user, stats);
+    const char *fs = getenv("GFE_SEARCH_FULLSCAN");
+    const bool full = fs && fs[0] == '1';
+    return run_search(sharded_scorer, &u, g, p, emit, user, stats, full ? nullptr : e, full ? nullptr : x);
 }
 
 extern "C" int gfe_search_with_scorer(gfe_score_fn score, void *score_user, const gfe_graph *g,

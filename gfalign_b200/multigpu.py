@@ -129,7 +129,7 @@ def main(argv=None):
             scorer = sharded.ShardedScorer(local_score, device=device)      # counts over NCCL
             if os.environ.get("GFE_EXCHANGE", "peer") == "peer":
                 try:      # counts stay on the device, summed by the peer-memory kernel (csrc/peer.cu)
-                    px = sharded.PeerExchange(2 * 4096 + 1, device)
+                    px = sharded.PeerExchange(1 << 18, device)     # 4 slots per candidate of a 4096-wide batch + padding
                 except Exception as ex:
                     sys.stderr.write(f"[multigpu] peer exchange unavailable ({ex!r}); using NCCL\n")
         if px is not None:

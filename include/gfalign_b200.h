@@ -248,6 +248,13 @@ int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_params *p, gf
 /* gfe_search over alignment shards: every rank calls it with its own engine (holding its shard) and the
  * box's exchange buffer; evaluatePath is answered by gfe_score_paths_sharded, so all ranks emit the
  * same rows. */
+/* gfe_score_paths_incremental over alignment shards: deltas and fresh-set counts are sums over
+ * alignments, so every rank scores the same batch against its shard (its own inverted index) and the
+ * raw records are summed by the peer kernel before the per-path composition.  n_cap of the exchange
+ * buffer must cover 4 slots per candidate plus padding (2^18 slots serve batches of 4096 paths). */
+int gfe_score_paths_incremental_sharded(gfe_engine *e, gfe_exchange *x, const gfe_path_batch *batch,
+                                        int32_t *counts /* P x 4 */);
+
 int gfe_search_sharded(gfe_engine *e, gfe_exchange *x, const gfe_graph *g, const gfe_search_params *p,
                        gfe_row_fn emit, void *user, gfe_search_stats *stats);
 

@@ -404,7 +404,7 @@ def test_sharded_entry_world1_scores_and_search_rows(engine, oracle):
     multi-GPU run takes: accumulate into the exchange buffer, status slot, peer sum, one copy back):
     counts == oracle, search rows == the reference CLI's on every golden search case."""
     from test_oracle import _search_inputs, search_rows_text
-    buf, x = _world1_exchange(2 * 4096 + 1)
+    buf, x = _world1_exchange(1 << 18)
     w = synth.make_workload("cfg3", A=30000)
     t = w.tangle
     nodes, _, _ = synth.node_table(t)
@@ -427,6 +427,16 @@ def test_sharded_entry_world1_scores_and_search_rows(engine, oracle):
         assert search_rows_text(rows, stats, tt.names, kw) == c["stdout"].splitlines(), c["name"]
         seen += 1
     assert seen >= 13
+    # deep paths (deltas through the sharded incremental entry): same rows as the single-engine search
+    nd, cn, node_count = synth.node_table(t)
+    engine.set_alignments(w.offsets, w.steps, t.n_nodes)
+    kw = dict(max_steps=2500, return_all_paths=True)
+    rows_s, st_s = engine.search_sharded(x, t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source,
+                                         t.destination, nd, cn, node_count, **kw)
+    rows_1, st_1 = engine.search(t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source, t.destination,
+                                 nd, cn, node_count, **kw)
+    assert [r.columns(t.names) for r in rows_s] == [r.columns(t.names) for r in rows_1] and len(rows_1) > 2
+    assert st_s["evaluations"] == st_1["evaluations"]
     x.close()
 
 
