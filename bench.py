@@ -788,6 +788,32 @@ def main():
         if not rows_agree:
             raise SystemExit("search rows differ between ranks")
         line["search"] = srch
+        if cx is not None:
+            # strong scaling of the N = 1 search (the cfg3 table of rank 0, replicated): candidate-batch sharding
+            off0, steps0 = (off, steps) if rank == 0 else synth.random_walk_alignments(
+                t.n_nodes, t.edge_from, t.edge_to, A, *synth.HIFI_LENGTHS, seed=11)
+            with gfalign_b200.Engine(local) as e3:
+                e3.set_alignments(off0, steps0, t.n_nodes)
+                cx.set_batch_sharding(True)
+                barrier()
+                rows3, st3 = e3.search_sharded(cx, t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source,
+                                               t.destination, nodes, counts, node_count, max_steps=args.search_steps)
+                cx.set_batch_sharding(False)
+            ts3 = torch.tensor([st3["seconds_total"]], dtype=torch.float64, device=dev)
+            sig3 = torch.tensor([len(rows3), sum(r.bad * 31 + r.good for r in rows3) % (1 << 31)], dtype=torch.int64, device=dev)
+            lo, hi = sig3.clone(), sig3.clone()
+            dist.all_reduce(ts3, op=dist.ReduceOp.MAX)
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            if not torch.equal(lo, hi):
+                raise SystemExit("batch-sharded search rows differ between ranks")
+            line["search_strong_cfg3"] = {
+                "sharding": "candidate batches (speculation subtrees dealt over the ranks), table replicated",
+                "max_steps": args.search_steps, "alignments": A, "seconds_search_loop": float(ts3.item()),
+                "evaluatePath_calls": st3["evaluations"], "paths_per_s": st3["evaluations"] / float(ts3.item()),
+                "kernel_batches": st3["kernel_batches"], "paths_scored": st3["paths_scored"], "rows": len(rows3),
+                "seconds_scoring": st3["seconds_scoring"], "rows_identical_on_all_ranks": True,
+                "note": "same table and search as the N = 1 line's `search` block"}
 
     # ---- BASELINE configs[4]: cfg5, 50 M alignments split over the ranks -------------------------------
     eng.close()

@@ -86,7 +86,7 @@ EXPORTS = [
     "gfe_text_open", "gfe_text_close", "gfe_text_get", "gfe_text_node_name", "gfe_text_node_id",
     "gfe_text_qname", "gfe_peer_sum_u32", "gfe_device_status_to",
     "gfe_exchange_create", "gfe_exchange_destroy", "gfe_score_paths_sharded", "gfe_search_sharded",
-    "gfe_score_paths_incremental", "gfe_score_paths_incremental_sharded",
+    "gfe_score_paths_incremental", "gfe_score_paths_incremental_sharded", "gfe_exchange_set_batch_sharding",
 ]
 
 PEER_MAX = 16      # GFE_PEER_MAX
@@ -116,6 +116,10 @@ class Exchange:
         if rc != 0:
             raise GfeError(rc, "gfe_exchange_create: bad arguments")
         self.handle, self._lib, self.n_cap = h, lib, n_cap
+
+    def set_batch_sharding(self, on: bool = True):
+        """Replicated tables: deal the candidates of a batch over the ranks instead of the alignments."""
+        self._lib.gfe_exchange_set_batch_sharding(self.handle, int(on))
 
     def close(self):
         if getattr(self, "handle", None):
@@ -165,6 +169,7 @@ def load_library() -> C.CDLL:
     lib.gfe_score_paths_incremental_sharded.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(_PathBatch), _i32p]
     lib.gfe_exchange_create.argtypes = [C.POINTER(C.c_uint64), C.c_int, C.c_int, C.c_uint32,
                                         C.POINTER(C.c_void_p)]
+    lib.gfe_exchange_set_batch_sharding.argtypes = [C.c_void_p, C.c_int]
     lib.gfe_exchange_destroy.argtypes = [C.c_void_p]
     lib.gfe_exchange_destroy.restype = None
     lib.gfe_score_paths_sharded.argtypes = [C.c_void_p, C.c_void_p, _u32p, _u32p, C.c_uint32, C.c_int, _u32p]

@@ -590,6 +590,10 @@ struct gfe_exchange {
     uint64_t bases[GFE_PEER_MAX];
     int world = 1, rank = 0;
     uint32_t n_cap = 0, epoch = 0;
+    // false: every rank holds an alignment SHARD and scores every candidate (records are summed);
+    // true:  every rank holds the WHOLE table and scores its share of the candidates — the speculation
+    //        subtrees are dealt round-robin — and the sum of the records is an all-gather
+    bool batch_shard = false;
 };
 
 // gfe_score_paths, and with `x` its sharded form: the kernels accumulate this rank's records
@@ -598,6 +602,7 @@ struct gfe_exchange {
 static int score_paths_impl(gfe_engine *e, gfe_exchange *x, const uint32_t *path_offsets,
                             const uint32_t *path_steps, uint32_t P, int filter, uint32_t *counts) {
     if (!e || !path_offsets || !counts) return GFE_ERR_ARG;
+    if (x && x->batch_shard) x = nullptr;   // replicated table: the full scan is local (same result on every rank)
     if (!e->have_alignments || !e->have_universe) {
         set_error(e, "gfe_score_paths: alignments and universe must be set first");
         return GFE_ERR_STATE;
@@ -769,6 +774,12 @@ int gfe_exchange_create(const uint64_t *peer_bases, int world, int rank, uint32_
 
 void gfe_exchange_destroy(gfe_exchange *x) { delete x; }
 
+int gfe_exchange_set_batch_sharding(gfe_exchange *x, int on) {
+    if (!x) return GFE_ERR_ARG;
+    x->batch_shard = on != 0;
+    return GFE_OK;
+}
+
 int gfe_score_paths_sharded(gfe_engine *e, gfe_exchange *x, const uint32_t *path_offsets,
                             const uint32_t *path_steps, uint32_t P, int filter, uint32_t *counts) {
     if (!x) return GFE_ERR_ARG;
@@ -867,12 +878,14 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
     slots.clear();
     slots.reserve((size_t)P + P / 8 + 8);
     uint32_t n_full = 0;
+    const bool deal = x && x->batch_shard;     // candidate-batch sharding: this rank scores its subtrees only
     for (uint32_t i = 0; i < P; ++i) {
         const uint32_t kb = b->item_base[i];
         if (kb >= n_bases || b->suffix_offsets[i + 1] < b->suffix_offsets[i]) {
             set_error(e, "gfe_score_paths_incremental: item %u is malformed", i);
             return GFE_ERR_ARG;
         }
+        if (deal && (int)(kb % (uint32_t)x->world) != x->rank) continue;
         const uint32_t s0 = b->suffix_offsets[i], ns = b->suffix_offsets[i + 1] - s0;
         const uint32_t nb = b->base_offsets[kb + 1] - b->base_offsets[kb];
         if ((uint64_t)nb + ns > GFE_MAX_STEPS) {
@@ -942,7 +955,9 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
     const size_t o_cn = align16(o_poff + ((size_t)P_dev + 1) * 4);
     const size_t o_fdesc = align16(o_cn + (size_t)chunks * 4);
     const size_t o_fpoff = align16(o_fdesc + (size_t)n_full * 16);
-    const size_t bytes = align16(o_fpoff + ((size_t)n_full + 1) * 4);
+    const size_t o_sitem = align16(o_fpoff + ((size_t)n_full + 1) * 4);          // batch sharding: slot -> item
+    const size_t o_saux = align16(o_sitem + (deal ? (size_t)P_dev * 4 : 0));
+    const size_t bytes = align16(o_saux + (deal ? (size_t)P_dev * 4 : 0));
     TRY(ensure_pinned(e, e->h_stage, bytes));
     TRY(ensure_dev(e, e->d_stage, bytes));
     unsigned char *hs = e->h_stage.ptr;
@@ -975,6 +990,16 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
         }
     }
     h_fpoff[nf] = ftotal;
+    if (deal) {
+        uint32_t *h_sitem = reinterpret_cast<uint32_t *>(hs + o_sitem), *h_saux = reinterpret_cast<uint32_t *>(hs + o_saux);
+        for (uint32_t d = 0; d < P_dev; ++d) h_sitem[d] = h_saux[d] = kNoNode;
+        for (size_t k = 0; k < slots.size(); ++k) {
+            const Slot &sl = slots[k];
+            const uint32_t kind = sl.key == kNoNode ? 2u : (sl.parent ? 1u : 0u);
+            h_sitem[slot_dev[k]] = sl.item | (kind << 30);
+            h_saux[slot_dev[k]] = kind == 2u ? full_of_item[sl.item] : 0u;
+        }
+    }
     uint32_t dtotal = 0;
     for (uint32_t d = 0; d < P_dev; ++d) {
         h_poff[d] = dtotal;
@@ -985,7 +1010,8 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
     const double t_prep = now_s();
     CUDA_TRY(e, cudaMemcpyAsync(e->d_stage.ptr, hs, bytes, cudaMemcpyHostToDevice, st));
     // ---- device buffers ------------------------------------------------------------------------------
-    const size_t res_words = kHdrWords + (size_t)n_full * 2 + (size_t)P_dev * 4 + 1;   // + the summed flags (sharded)
+    // + the summed flags (sharded) / + the gathered per-item records and flags (batch sharding)
+    const size_t res_words = kHdrWords + (size_t)n_full * 2 + (size_t)P_dev * 4 + 1 + (deal ? (size_t)P * 4 + 1 : 0);
     TRY(ensure_pinned(e, e->h_counts, res_words));
     {
         const uint32_t *before = e->d_counts.ptr;
@@ -1023,7 +1049,16 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
     uint32_t *d_hdr = e->d_counts.ptr, *d_full = d_hdr + kHdrWords, *d_inc = d_full + (size_t)n_full * 2;
     uint32_t *d_sum = d_full;                 // where the host reads the (summed) records
     const size_t rec_words = (size_t)n_full * 2 + (size_t)P_dev * 4;
-    if (x) {
+    uint32_t *d_items = nullptr;             // batch sharding: per-item records in the exchange buffer
+    if (deal) {
+        if ((size_t)P * 4 + 1 > x->n_cap) {
+            set_error(e, "gfe_score_paths_incremental_sharded: batch needs %zu exchange slots, the buffer has %u",
+                      (size_t)P * 4 + 1, x->n_cap);
+            return GFE_ERR_LIMIT;
+        }
+        d_items = reinterpret_cast<uint32_t *>(x->bases[x->rank]) + (size_t)x->n_cap * ((x->epoch + 1) & 1u);
+        CUDA_TRY(e, cudaMemsetAsync(d_items, 0, ((size_t)P * 4 + 1) * 4, st));
+    } else if (x) {
         // sharded: this rank's records accumulate in its half of the exchange buffer, one more slot carries
         // its flags; the peer kernel sums all shards into the result block
         if (rec_words + 1 > x->n_cap) {
@@ -1127,7 +1162,22 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
         TRY(enqueue_score(e, fs.poff, d_flocal, n_full, ftotal, 1, d_full, d_hdr, nullptr, d_hdr + kWorkCounters,
                           d_hdr + kWorkCounters + 1, st));
     }
-    if (x) {
+    if (deal) {
+        // this rank's share of the candidates, composed per item on the device; the sum over the ranks
+        // (everybody else wrote zeros for them) is the all-gather
+        launch_compose_items(reinterpret_cast<const uint32_t *>(ds + o_sitem), reinterpret_cast<const uint32_t *>(ds + o_saux),
+                             P_dev, d_inc, d_full, reinterpret_cast<int32_t *>(d_items), st);
+        launch_flag_word(d_hdr + kWorkCounters, d_hdr, d_items + (size_t)P * 4, st);
+        launch_flag_or(d_hdr + kWorkCounters + 1, d_items + (size_t)P * 4, st);
+        e->kernel_launches += 4;
+        x->epoch += 1;
+        const int prc = gfe_peer_sum_u32(x->bases, x->world, x->rank, x->n_cap, P * 4 + 1, x->epoch,
+                                         d_hdr + kHdrWords + rec_words + 1, st);
+        if (prc != GFE_OK) {
+            set_error(e, "gfe_score_paths_incremental_sharded: peer sum launch failed");
+            return prc;
+        }
+    } else if (x) {
         launch_flag_word(d_hdr + kWorkCounters, d_hdr, d_full + rec_words, st);   // bad step | overflow of the last chain
         launch_flag_or(d_hdr + kWorkCounters + 1, d_full + rec_words, st);        // | overflow of the first chain
         e->kernel_launches += 3;
@@ -1153,7 +1203,8 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
     e->h2d_bytes += bytes;
     e->d2h_bytes += res_words * sizeof(uint32_t);
     const uint32_t *h = e->h_counts.ptr;
-    const uint32_t any_flags = x ? h[kHdrWords + rec_words] : 0u;     // summed over the ranks
+    const uint32_t any_flags = deal ? h[kHdrWords + rec_words + 1 + (size_t)P * 4]
+                                    : (x ? h[kHdrWords + rec_words] : 0u);     // summed over the ranks
     if (x && any_flags == GFE_PEER_TIMEOUT) {
         set_error(e, "gfe_score_paths_incremental_sharded: a peer never reached epoch %u (GFE_PEER_TIMEOUT_MS)", x->epoch);
         return GFE_ERR_CUDA;
@@ -1182,6 +1233,10 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
     e->exact_pairs += h[0];
     e->slow_pairs += h[2] - h[4];
     // ---- results per item ---------------------------------------------------------------------------------
+    if (deal) {
+        memcpy(counts, h + kHdrWords + rec_words + 1, (size_t)P * 4 * sizeof(int32_t));
+        return GFE_OK;
+    }
     const uint32_t *h_full = h + kHdrWords, *h_inc = h_full + (size_t)n_full * 2;
     for (uint32_t i = 0; i < P; ++i) counts[4 * (size_t)i] = counts[4 * (size_t)i + 1] = 0;
     for (size_t k = 0; k < slots.size(); ++k) {

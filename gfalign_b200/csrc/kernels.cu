@@ -1168,6 +1168,33 @@ __global__ void __launch_bounds__(256) assemble_paths_kernel(const AssembleArgs 
     }
 }
 
+__global__ void __launch_bounds__(256)
+compose_items_kernel(const uint32_t *__restrict__ slot_item, const uint32_t *__restrict__ slot_aux, uint32_t P_dev,
+                     const uint32_t *__restrict__ inc, const uint32_t *__restrict__ full, int32_t *__restrict__ out) {
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= P_dev) return;
+    const uint32_t si = slot_item[k];
+    if (si == 0xFFFFFFFFu) return;
+    const uint32_t kind = si >> 30;
+    const uint32_t *r = inc + 4 * (size_t)k;
+    int32_t *o = out + 4 * (size_t)(si & kPathMask);
+    if (kind == 0u) {            // the candidate itself: + its counts on the rows of its last node, its fresh set
+        atomicAdd(o, (int32_t)r[0]);
+        atomicAdd(o + 1, (int32_t)r[1]);
+        o[2] = (int32_t)r[2];
+        o[3] = (int32_t)r[3];
+    } else if (kind == 1u) {     // its parent on the same rows (the last node was visited before)
+        atomicAdd(o, -(int32_t)r[0]);
+        atomicAdd(o + 1, -(int32_t)r[1]);
+    } else {                     // full scan
+        const uint32_t *f = full + 2 * (size_t)slot_aux[k];
+        o[0] = (int32_t)f[0];
+        o[1] = (int32_t)f[1];
+        o[2] = (int32_t)r[2];
+        o[3] = (int32_t)r[3];
+    }
+}
+
 constexpr size_t kMaxDynSmem = 200 * 1024;
 
 size_t score_smem_bytes(const ScoreArgs &a) {
@@ -1330,6 +1357,12 @@ void launch_index_fill(const Buckets &bk, uint32_t L, uint32_t root_local, uint3
     if (!n) return;
     index_rows_kernel<true><<<std::min<uint32_t>((n + kBlock - 1) / kBlock, 148 * 16), kBlock, 0, st>>>(
         bk, L, root_local, cursor, rows);
+}
+
+void launch_compose_items(const uint32_t *slot_item, const uint32_t *slot_aux, uint32_t P_dev, const uint32_t *inc,
+                          const uint32_t *full, int32_t *out, cudaStream_t st) {
+    if (!P_dev) return;
+    compose_items_kernel<<<(P_dev + 255) / 256, 256, 0, st>>>(slot_item, slot_aux, P_dev, inc, full, out);
 }
 
 void launch_assemble_paths(const AssembleArgs &a, cudaStream_t st) {

@@ -328,6 +328,10 @@ struct AssembleArgs {
     uint32_t *err;
 };
 void launch_assemble_paths(const AssembleArgs &a, cudaStream_t st);
+// candidate-batch sharding: raw slot records -> per-item records {d bad, d good, fresh bad, fresh good}; slot_item[k] =
+// item | kind << 30 (0 child, 1 parent copy, 2 full scan; 0xFFFFFFFF padding), slot_aux[k] = index into `full` (kind 2)
+void launch_compose_items(const uint32_t *slot_item, const uint32_t *slot_aux, uint32_t P_dev, const uint32_t *inc,
+                          const uint32_t *full, int32_t *out, cudaStream_t st);
 void launch_slow_worklist(const ScoreArgs &a, const uint2 *slow, const uint32_t *slow_count,
                           uint32_t slow_cap, cudaStream_t st);
 void launch_exact_worklist(const ScoreArgs &a, cudaStream_t st);

@@ -36,6 +36,9 @@ def _args(argv):
     ap.add_argument("--min-nodes", type=int, default=0)
     ap.add_argument("--return-all-paths", action="store_true")
     ap.add_argument("--speculate", type=int, default=0)
+    ap.add_argument("--shard", choices=["alignments", "batch", "auto"], default="auto",
+                    help="search: shard the alignment table over the GPUs, or replicate it and deal each batch's "
+                         "speculation subtrees (small tables); auto = batch up to 4 M alignments")
     return ap.parse_args(argv)
 
 
@@ -100,8 +103,12 @@ def main(argv=None):
         dist.init_process_group("nccl", device_id=device)
 
     tp = capi.TextPack(a.gfa, a.gaf, threads=a.threads)
-    cuts = sharded.shard_bounds(tp.offsets, world)
-    off, st = sharded.take_shard(tp.offsets, tp.steps, int(cuts[rank]), int(cuts[rank + 1]))
+    batch_shard = a.tool == "search" and (a.shard == "batch" or (a.shard == "auto" and tp.A <= 4_000_000))
+    if batch_shard:
+        off, st = tp.offsets, tp.steps                 # every rank keeps the whole table
+    else:
+        cuts = sharded.shard_bounds(tp.offsets, world)
+        off, st = sharded.take_shard(tp.offsets, tp.steps, int(cuts[rank]), int(cuts[rank + 1]))
     eng = capi.Engine(local)
     eng.set_alignments(off, st, tp.n_nodes)
 
@@ -112,6 +119,9 @@ def main(argv=None):
         eng.set_universe(nodes)
 
         def local_score(po, ps):
+            return eng.score_paths(po, ps, filter=True)
+
+        def local_replicated(po, ps):      # batch sharding without the peer kernel: every rank scores everything
             return eng.score_paths(po, ps, filter=True)
 
         out = sys.stdout
@@ -126,21 +136,24 @@ def main(argv=None):
         px = None
         scorer = local_score
         if world > 1:
-            scorer = sharded.ShardedScorer(local_score, device=device)      # counts over NCCL
+            scorer = local_replicated if batch_shard else sharded.ShardedScorer(local_score, device=device)
             if os.environ.get("GFE_EXCHANGE", "peer") == "peer":
                 try:      # counts stay on the device, summed by the peer-memory kernel (csrc/peer.cu)
                     px = sharded.PeerExchange(1 << 18, device)     # 4 slots per candidate of a 4096-wide batch + padding
                 except Exception as ex:
                     sys.stderr.write(f"[multigpu] peer exchange unavailable ({ex!r}); using NCCL\n")
         if px is not None:
-            # the whole loop in C: gfe_search_sharded -> gfe_score_paths_sharded per batch
+            # the whole loop in C: gfe_search_sharded -> gfe_score_paths_incremental_sharded per batch
+            if batch_shard:
+                px.c_exchange().set_batch_sharding(True)
             rows, stats = eng.search_sharded(px.c_exchange(), tp.adj_offsets, tp.adj_target, tp.adj_or0,
                                              tp.adj_or1, src, dst, nodes, counts, node_count, **kw)
         else:
             rows, stats = capi.search_with_scorer(scorer, tp.adj_offsets, tp.adj_target, tp.adj_or0,
                                                   tp.adj_or1, src, dst, nodes, counts, node_count, **kw)
         if rank == 0 and os.environ.get("GFE_DEBUG_TIMING"):
-            sys.stderr.write(f"[multigpu] exchange {'peer kernel (C loop)' if px is not None else type(scorer).__name__}, "
+            sys.stderr.write(f"[multigpu] {'candidate-batch' if batch_shard else 'alignment'} sharding, "
+                             f"exchange {'peer kernel (C loop)' if px is not None else getattr(scorer, '__name__', type(scorer).__name__)}, "
                              f"{stats['kernel_batches']} batches, scoring {stats['seconds_scoring']:.3f} s\n")
         if rank == 0 and stats["extractions"] >= a.max_steps:
             out.write(f"Reached maximum number of steps ({stats['extractions']})\n")

@@ -196,6 +196,13 @@ typedef struct gfe_exchange gfe_exchange;
 int gfe_exchange_create(const uint64_t *peer_bases, int world, int rank, uint32_t n_cap,
                         gfe_exchange **out);
 void gfe_exchange_destroy(gfe_exchange *x);
+/* Candidate-batch sharding for tables too small to fill N GPUs (SURVEY.md 8e "alternative when A is
+ * small"; north_star: "sharding DFS subtrees"): every rank holds the WHOLE alignment table, the
+ * speculation subtrees of a batch (its base paths) are dealt round-robin over the ranks, each rank scores
+ * its share with gfe_score_paths_incremental_sharded, and the sum of the per-candidate records — zeros
+ * from the ranks that did not score a candidate — is the all-gather.  gfe_score_paths_sharded then
+ * needs no exchange (every rank scores the batch itself). */
+int gfe_exchange_set_batch_sharding(gfe_exchange *x, int on);
 int gfe_score_paths_sharded(gfe_engine *e, gfe_exchange *x, const uint32_t *path_offsets,
                             const uint32_t *path_steps, uint32_t P, int filter, uint32_t *counts);
 

@@ -437,6 +437,12 @@ def test_sharded_entry_world1_scores_and_search_rows(engine, oracle):
                                  nd, cn, node_count, **kw)
     assert [r.columns(t.names) for r in rows_s] == [r.columns(t.names) for r in rows_1] and len(rows_1) > 2
     assert st_s["evaluations"] == st_1["evaluations"]
+    # candidate-batch sharding with one rank (it owns every subtree): device-side composition per item
+    x.set_batch_sharding(True)
+    rows_b, st_b = engine.search_sharded(x, t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source,
+                                         t.destination, nd, cn, node_count, **kw)
+    assert [r.columns(t.names) for r in rows_b] == [r.columns(t.names) for r in rows_1]
+    assert np.array_equal(engine.score_paths_sharded(x, po, ps, filter=True), engine.score_paths(po, ps, filter=True))
     x.close()
 
 

@@ -34,10 +34,12 @@ def test_two_gpu_search_and_evalgfa_match_reference(tmp_path):
         for fn, txt in c["files"].items():
             with open(os.path.join(d, fn), "w") as f:
                 f.write(txt)
-        p = _torchrun(2, list(c["args"]), d, port)
-        port += 1
-        assert p.returncode == 0, p.stderr[-2000:]
-        assert p.stdout == c["stdout"], c["name"]
+        modes = (["--shard", "alignments"], ["--shard", "batch"]) if "_search" in c["name"] else ([],)
+        for extra in modes:      # alignment shards and candidate-batch shards must print the same rows
+            p = _torchrun(2, list(c["args"]) + extra, d, port)
+            port += 1
+            assert p.returncode == 0, p.stderr[-2000:]
+            assert p.stdout == c["stdout"], (c["name"], extra)
         if "-o" in c["args"]:
             out = open(os.path.join(d, c["args"][c["args"].index("-o") + 1])).read()
             assert out == c["out_text"], c["name"]
