@@ -217,9 +217,10 @@ def run_cfg4(device_index: int = 0, A: int = 20_000_000, reps: int = 5, cpu: boo
     c1 = eng.counters()
     exact = int(c1["exact_pairs"] - c0["exact_pairs"])
     k_ms, call_s = timed(lambda: eng.score_pairs(path, filter=False, want_scores=False))
+    exact_ms = eng.last_aux_kernel_ms()
     view_bytes = 2.0 * (S + A) + 8.0 * A
     sec = {"kernel": "pair_classify_kernel (+ pair_exact_kernel for rows touching the path)", "path_steps": n,
-           "classify_kernel_ms": k_ms, "call_seconds_totals_only": call_s, "pairs_per_s": A / call_s,
+           "classify_kernel_ms": k_ms, "exact_dp_kernel_ms": exact_ms, "call_seconds_totals_only": call_s, "pairs_per_s": A / call_s,
            "exact_dp_pairs": exact, "dp_cells_dense_equivalent": 2.0 * n * mbar * exact, "bad": int(bad),
            "good": int(good),
            "roofline": roof(view_bytes, k_ms, "classify pass streams the 16-bit view (2(m+1) B) + 8 B of scores "

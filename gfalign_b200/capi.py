@@ -87,6 +87,7 @@ EXPORTS = [
     "gfe_text_qname", "gfe_peer_sum_u32", "gfe_device_status_to",
     "gfe_exchange_create", "gfe_exchange_destroy", "gfe_score_paths_sharded", "gfe_search_sharded",
     "gfe_score_paths_incremental", "gfe_score_paths_incremental_sharded", "gfe_exchange_set_batch_sharding",
+    "gfe_last_aux_kernel_ms",
 ]
 
 PEER_MAX = 16      # GFE_PEER_MAX
@@ -184,6 +185,8 @@ def load_library() -> C.CDLL:
     lib.gfe_set_timing.argtypes = [C.c_void_p, C.c_int]
     lib.gfe_last_kernel_ms.argtypes = [C.c_void_p]
     lib.gfe_last_kernel_ms.restype = C.c_float
+    lib.gfe_last_aux_kernel_ms.argtypes = [C.c_void_p]
+    lib.gfe_last_aux_kernel_ms.restype = C.c_float
     lib.gfe_device_status.argtypes = [C.c_void_p, _u32p]
     lib.gfe_kernel_time_stats.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_uint32)]
     lib.gfe_trace_pairs.argtypes = [C.c_void_p, _u32p, C.c_uint32, C.c_uint64, C.c_uint32, _u8p, _u8p,
@@ -415,6 +418,9 @@ class Engine:
 
     def last_kernel_ms(self) -> float:
         return float(self._lib.gfe_last_kernel_ms(self._h))
+
+    def last_aux_kernel_ms(self) -> float:
+        return float(self._lib.gfe_last_aux_kernel_ms(self._h))
 
     def device_status(self) -> int:
         """Sticky flags of the *_device calls (bit0 path outside universe, bit1 worklist overflow)."""

@@ -142,6 +142,7 @@ void gfe_destroy(gfe_engine *e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     e->free_all();
     for (cudaEvent_t ev : e->ev_ring) cudaEventDestroy(ev);
+    if (e->ev_aux) cudaEventDestroy(e->ev_aux);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -153,6 +154,7 @@ int gfe_set_timing(gfe_engine *e, int enabled) {
 }
 
 float gfe_last_kernel_ms(const gfe_engine *e) { return e ? e->last_kernel_ms : 0.f; }
+float gfe_last_aux_kernel_ms(const gfe_engine *e) { return e ? e->last_aux_ms : 0.f; }
 
 int gfe_kernel_time_stats(gfe_engine *e, double *total_ms, uint32_t *launches) {
     if (!e || !total_ms || !launches) return GFE_ERR_ARG;
@@ -333,7 +335,10 @@ int gfe_set_alignments_device(gfe_engine *e, const uint32_t *d_offsets, const ui
     return build_bucket_geometry(e);   // also finds the longest alignment
 }
 
-int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) {
+}  // extern "C"
+
+// with_dict = false: evalPath's view (position-table kernels only): no pair dictionary pass over the table
+static int set_universe_impl(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe, bool with_dict) {
     if (!e || (n_universe && !nodes)) return GFE_ERR_ARG;
     if (!e->have_alignments) {
         set_error(e, "gfe_set_universe: call gfe_set_alignments first");
@@ -379,7 +384,7 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) 
         const int64_t word_budget = (int64_t)(kBitsetSmemBudget / 4) - 64 - 8;
         int64_t max_pairs = (word_budget - 2 * ((int64_t)e->L + 1) - (kMaxBucket + 2) - 2 - 3 - 2 * (int64_t)kBloom) / 2;
         max_pairs = std::min<int64_t>(max_pairs, 32766);
-        if (max_pairs >= 1 && !e->force_legacy) {
+        if (max_pairs >= 1 && !e->force_legacy && with_dict) {
             TRY(ensure_dev(e, e->d_pair_keys, kPairHashCap));
             TRY(ensure_dev(e, e->d_pair_ids, kPairHashCap));
             TRY(ensure_dev(e, e->d_pair_ctr, 4));
@@ -412,6 +417,12 @@ int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) 
     e->have_universe = true;
     e->have_index = false;
     return GFE_OK;
+}
+
+extern "C" {
+
+int gfe_set_universe(gfe_engine *e, const uint32_t *nodes, uint32_t n_universe) {
+    return set_universe_impl(e, nodes, n_universe, true);
 }
 
 // ---- search scoring -----------------------------------------------------------------------------
@@ -1328,7 +1339,7 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
             if (seen.emplace(node, (uint32_t)uni.size()).second) uni.push_back(node);
         }
     }
-    TRY(gfe_set_universe(e, uni.data(), (uint32_t)uni.size()));
+    TRY(set_universe_impl(e, uni.data(), (uint32_t)uni.size(), false));
     const size_t off_bytes = 16;
     const size_t bytes = off_bytes + (size_t)n * 2;
     TRY(ensure_pinned(e, e->h_stage, bytes));
@@ -1391,6 +1402,10 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
             e->kernel_launches += 1;
         }
     }
+    if (e->timing) {       // the exact DP behind the classify pass: ev1 .. aux
+        if (!e->ev_aux) CUDA_TRY(e, cudaEventCreate(&e->ev_aux));
+        CUDA_TRY(e, cudaEventRecord(e->ev_aux, st));
+    }
     CUDA_TRY(e, cudaGetLastError());
     CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr, e->d_counts.ptr, 2 * sizeof(uint32_t),
                                 cudaMemcpyDeviceToHost, st));
@@ -1404,6 +1419,7 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
                                     cudaMemcpyDeviceToHost, st));
     CUDA_TRY(e, cudaStreamSynchronize(st));
     if (e->timing && e->ev0) cudaEventElapsedTime(&e->last_kernel_ms, e->ev0, e->ev1);
+    if (e->timing && e->ev_aux) cudaEventElapsedTime(&e->last_aux_ms, e->ev1, e->ev_aux);
     e->exact_pairs += e->h_wc[0];
     e->h2d_bytes += bytes;
     e->d2h_bytes += 16 + ((t_fw ? 1 : 0) + (t_rc ? 1 : 0)) * e->A * sizeof(int32_t);
@@ -1465,12 +1481,28 @@ int edge_count_on_device(gfe_engine *e, const uint32_t *edge_from, const uint32_
         CUDA_TRY(e, cudaMemcpyAsync(e->d_edge_ft.ptr, edge_from, (size_t)E * 4, cudaMemcpyHostToDevice, st));
         CUDA_TRY(e, cudaMemcpyAsync(e->d_edge_ft.ptr + E, edge_to, (size_t)E * 4, cudaMemcpyHostToDevice, st));
     }
-    launch_edge_build(e->d_edge_ft.ptr, e->d_edge_ft.ptr + E, E, e->d_edge_table.ptr, e->edge_cap, st);
+    const uint32_t steps2 = 2 * e->n_nodes;
+    TRY(ensure_dev(e, e->d_edge_adj, std::max<size_t>(steps2, 1)));
+    TRY(ensure_dev(e, e->d_edge_deg, (size_t)steps2 + 1));
+    TRY(ensure_dev(e, e->d_edge_cnt, (size_t)E * 2 + 1));
+    EdgeBuild eb;
+    eb.table = e->d_edge_table.ptr;
+    eb.cap = e->edge_cap;
+    eb.deg = e->d_edge_deg.ptr;
+    eb.adj = e->d_edge_adj.ptr;
+    eb.steps2 = steps2;
+    eb.cursor = e->d_edge_deg.ptr + steps2;
+    launch_edge_build(e->d_edge_ft.ptr, e->d_edge_ft.ptr + E, E, eb, st);
+    CUDA_TRY(e, cudaMemsetAsync(e->d_edge_cnt.ptr, 0, ((size_t)E * 2 + 1) * 4, st));
     EdgeStreamArgs a;
     TRY(ensure_rowstart(e, st));
     a.steps = e->d_steps;
     a.rowstart = e->d_rowstart.ptr;
     a.S = e->S;
+    a.adj = e->d_edge_adj.ptr;
+    a.cnt = e->d_edge_cnt.ptr;
+    a.steps2 = steps2;
+    a.n_arcs = 2 * E;
     a.table = e->d_edge_table.ptr;
     a.cap = e->edge_cap;
     if (e->timing) {
@@ -1479,7 +1511,7 @@ int edge_count_on_device(gfe_engine *e, const uint32_t *edge_from, const uint32_
     }
     if (E) launch_edge_stream(a, e->sm_count, st);
     if (e->timing) CUDA_TRY(e, cudaEventRecord(e->ev1, st));
-    e->kernel_launches += (E ? 1 : 0) + ((E && e->A) ? 1 : 0) + 1;
+    e->kernel_launches += (E ? 3 : 0) + ((E && e->S >= 2) ? 1 : 0) + 1;
     e->h2d_bytes += (uint64_t)E * 8;
     CUDA_TRY(e, cudaGetLastError());
     return GFE_OK;
@@ -1497,7 +1529,7 @@ int gfe_edge_traversals_device(gfe_engine *e, const uint32_t *edge_from, const u
     cudaStream_t st = (cudaStream_t)cuda_stream;   // NULL = the CUDA default stream
     TRY(edge_count_on_device(e, edge_from, edge_to, E, st));
     CUDA_TRY(e, cudaMemsetAsync(d_counts, 0, (size_t)E * 2 * sizeof(uint32_t), st));
-    launch_edge_scatter(e->d_edge_table.ptr, e->edge_cap, d_counts, st);
+    launch_edge_scatter(e->d_edge_table.ptr, e->edge_cap, e->d_edge_cnt.ptr, d_counts, st);
     e->kernel_launches += 1;
     CUDA_TRY(e, cudaGetLastError());
     // the caller's host arrays may go away after the call
@@ -1535,7 +1567,7 @@ int gfe_edge_support(gfe_engine *e, const uint32_t *edge_from, const uint32_t *e
     if (E) {
         TRY(ensure_dev(e, e->d_edge_counts, E));
         launch_edge_weights(e->d_edge_ft.ptr, e->d_edge_ft.ptr + E, E, e->d_edge_table.ptr, e->edge_cap,
-                            e->d_edge_counts.ptr, st);
+                            e->d_edge_cnt.ptr, e->d_edge_counts.ptr, st);
         e->kernel_launches += 1;
         CUDA_TRY(e, cudaGetLastError());
         CUDA_TRY(e, cudaMemcpyAsync(weights, e->d_edge_counts.ptr, (size_t)E * 4, cudaMemcpyDeviceToHost, st));

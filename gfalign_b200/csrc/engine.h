@@ -28,7 +28,8 @@ struct gfe_engine {
     std::vector<cudaEvent_t> ev_ring;           // pairs recorded since the last gfe_kernel_time_stats
     size_t ev_used = 0;
     bool timing = false;
-    float last_kernel_ms = 0.f;
+    float last_kernel_ms = 0.f, last_aux_ms = 0.f;
+    cudaEvent_t ev_aux = nullptr;
     char error[512] = "";
 
     // alignment table (owned copies, or adopted device pointers)
@@ -100,6 +101,8 @@ struct gfe_engine {
     // edge support
     DevBuf<uint32_t> d_edge_ft, d_edge_counts;     // link records (from | to), per-record weights
     DevBuf<gfe::EdgeSlot> d_edge_table;
+    DevBuf<uint4> d_edge_adj;                      // dense adjacency records, one per oriented step
+    DevBuf<uint32_t> d_edge_deg, d_edge_cnt;       // arcs per step (+ the counter cursor), one counter per arc
     uint32_t edge_cap = 0;
     DevBuf<uint32_t> d_rowstart;                   // bit s: step s starts an alignment
     bool have_rowstart = false;
@@ -115,6 +118,7 @@ struct gfe_engine {
         fd(d_stage.ptr); fd(d_ptab.ptr); fd(d_plocal.ptr); fd(d_pnext.ptr); fd(d_counts.ptr); fd(d_err.ptr);
         fd(d_work.ptr); fd(d_work_count.ptr); fd(d_pair_work.ptr); fd(d_tfw.ptr); fd(d_trc.ptr);
         fd(d_edge_ft.ptr); fd(d_edge_counts.ptr); fd(d_edge_table.ptr); fd(d_rowstart.ptr);
+        fd(d_edge_adj.ptr); fd(d_edge_deg.ptr); fd(d_edge_cnt.ptr);
         fd(d_pair_keys.ptr); fd(d_pair_ids.ptr); fd(d_pair_ctr.ptr); fd(d_masks.ptr);
         fd(d_unit_ctr.ptr); fd(d_slow.ptr);
         fd(d_inv_off.ptr); fd(d_inv_cursor.ptr); fd(d_inv_rows.ptr); fd(d_chunk_node.ptr); fd(d_desc.ptr);

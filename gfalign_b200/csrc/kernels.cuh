@@ -180,17 +180,30 @@ struct PairArgs {             // evalPath: one path against every alignment
     uint32_t work_cap;
 };
 
-struct __align__(16) EdgeSlot {   // evalGFA: one directed link pair of the graph (edges.cu)
+struct __align__(16) EdgeSlot {   // evalGFA: one directed arc of the graph (edges.cu)
     unsigned long long key;       // from_step << 32 | to_step; ~0 = empty
-    uint32_t count;               // traversal events equal to this pair
+    uint32_t count;               // index of the arc's counter
     uint32_t rep;                 // lowest slot (2i = record i, 2i+1 = its reverse complement) carrying it
+};
+
+struct EdgeBuild {                // evalGFA: what launch_edge_build fills from the link records
+    EdgeSlot *table;
+    uint32_t cap;
+    uint32_t *deg;                // arcs per oriented step (2 * n_nodes)
+    uint4 *adj;                   // dense adjacency records {to_0, to_1, to_2, first counter}
+    uint32_t steps2;              // 2 * n_nodes
+    uint32_t *cursor;             // one word: counters handed out
 };
 
 struct EdgeStreamArgs {
     const uint32_t *steps;
     const uint32_t *rowstart;     // bitmap over steps: bit s = step s starts an alignment
     uint64_t S;                   // total steps
-    EdgeSlot *table;
+    const uint4 *adj;
+    uint32_t *cnt;                // one counter per directed arc (zeroed by the caller)
+    uint32_t steps2;
+    uint32_t n_arcs;              // counters (upper bound 2 E)
+    const EdgeSlot *table;        // arcs of crowded steps (more than three per step)
     uint32_t cap;
 };
 
@@ -341,12 +354,11 @@ void launch_pair_exact(const PairArgs &a, cudaStream_t st);
 void launch_pair_exact_long(const PairArgs &a, uint32_t max_m, cudaStream_t st);
 uint32_t edge_table_capacity(uint32_t E);
 void launch_rowstart(const uint32_t *off, uint64_t A, uint32_t *rowstart, cudaStream_t st);
-void launch_edge_build(const uint32_t *d_ef, const uint32_t *d_et, uint32_t E, EdgeSlot *table,
-                       uint32_t cap, cudaStream_t st);
+void launch_edge_build(const uint32_t *d_ef, const uint32_t *d_et, uint32_t E, const EdgeBuild &b, cudaStream_t st);
 void launch_edge_stream(const EdgeStreamArgs &a, int sm_count, cudaStream_t st);
-void launch_edge_scatter(const EdgeSlot *table, uint32_t cap, uint32_t *counts, cudaStream_t st);
+void launch_edge_scatter(const EdgeSlot *table, uint32_t cap, const uint32_t *cnt, uint32_t *counts, cudaStream_t st);
 void launch_edge_weights(const uint32_t *d_ef, const uint32_t *d_et, uint32_t E, const EdgeSlot *table,
-                         uint32_t cap, uint32_t *weights, cudaStream_t st);
+                         uint32_t cap, const uint32_t *cnt, uint32_t *weights, cudaStream_t st);
 int configure_edge_kernels();
 int configure_bitset_kernels();
 void launch_max_len(const uint32_t *off, uint64_t first, uint32_t count, uint32_t *out,

@@ -161,10 +161,9 @@ int gfe_edge_support(gfe_engine *e, const uint32_t *edge_from, const uint32_t *e
 
 /* Device-side half of the above for sharded alignments: raw traversal counters, to be summed across
  * shards (all-reduce) before gfe_edge_weights_from_counts.  d_counts has 2*E uint32 slots (slot 2i =
- * record i as written, 2i+1 = its reverse complement).  A pair and its reverse complement are
- * counted together: their events are reported at the lowest slot carrying the canonical
- * orientation and the other slots stay 0, so only sums over both orientations of a record are
- * defined — which is all gfe_edge_weights_from_counts uses. */
+ * record i as written, 2i+1 = its reverse complement).  Every directed arc is counted once, at the
+ * LOWEST slot that carries it (duplicate records and records that are each other's reverse
+ * complement share arcs); the other slots stay 0.  gfe_edge_weights_from_counts resolves that. */
 int gfe_edge_traversals_device(gfe_engine *e, const uint32_t *edge_from, const uint32_t *edge_to,
                                uint32_t E, uint32_t *d_counts, void *cuda_stream);
 int gfe_edge_weights_from_counts(const uint32_t *edge_from, const uint32_t *edge_to, uint32_t E,
@@ -323,6 +322,8 @@ int gfe_device_status_to(gfe_engine *e, uint32_t *d_flags, void *cuda_stream);
  * the engine's stream); 0 if timing was not enabled with gfe_set_timing(e, 1). */
 int gfe_set_timing(gfe_engine *e, int enabled);
 float gfe_last_kernel_ms(const gfe_engine *e);
+/* gfe_score_pairs: milliseconds of the exact-DP kernels behind the classify pass (0 without timing). */
+float gfe_last_aux_kernel_ms(const gfe_engine *e);
 /* Synchronises the device, sums the CUDA-event durations of every dominant-kernel launch timed
  * since the previous call (any stream the launches were enqueued on) and resets the record. */
 int gfe_kernel_time_stats(gfe_engine *e, double *total_ms, uint32_t *launches);
