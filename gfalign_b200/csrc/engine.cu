@@ -185,7 +185,7 @@ int gfe_device_status(gfe_engine *e, uint32_t *flags) {
         CUDA_TRY(e, cudaMemcpy(wc, e->d_work_count.ptr, sizeof(wc), cudaMemcpyDeviceToHost));
     // err[1]: overflow bits of every batch since the last report (the prologue of the next batch
     // folds them in before it clears the counters); wc: the batch still in the counters
-    *flags = (err[0] ? 1u : 0u) | ((wc[1] || wc[3] || err[1]) ? 2u : 0u);
+    *flags = ((err[0] & 1u) ? 1u : 0u) | ((wc[1] || wc[3] || err[1]) ? 2u : 0u) | (err[0] & 4u);
     return GFE_OK;
 }
 
@@ -227,11 +227,9 @@ static int validate_csr_host(gfe_engine *e, const uint32_t *offsets, const uint3
             return GFE_ERR_ARG;
         }
         uint32_t m = offsets[a + 1] - offsets[a];
-        if (m > GFE_MAX_STEPS) {
-            set_error(e, "alignment %llu has %u steps; the reference's MAX_N allows %u",
-                      (unsigned long long)a, m, GFE_MAX_STEPS);
-            return GFE_ERR_LIMIT;
-        }
+        // rows longer than GFE_MAX_STEPS are accepted here: with the id filter the reference drops such a row
+        // before its DP unless every node of it is on the candidate path (src/eval.cpp:81-91); only then, and
+        // in every unfiltered call, its dp[MAX_N][MAX_N] cannot hold the row -> GFE_ERR_LIMIT at score time
         mx = std::max(mx, m);
     }
     const uint64_t S = offsets[A];
@@ -276,11 +274,6 @@ static int build_bucket_geometry(gfe_engine *e) {
     }
     e->bstep_elems = base + 8;
     e->max_m = hist[kNumBuckets];
-    if (e->max_m > GFE_MAX_STEPS) {
-        set_error(e, "an alignment has %u steps; the reference's MAX_N allows %u", e->max_m,
-                  GFE_MAX_STEPS);
-        return GFE_ERR_LIMIT;
-    }
     return GFE_OK;
 }
 
@@ -481,6 +474,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     a.work = e->d_work.ptr;
     a.work_count = d_work_count;
     a.work_cap = (uint32_t)std::min<size_t>(e->d_work.cap, 0xFFFFFFFFu);
+    a.err = d_bad_step;
     const PairDict pd{e->d_pair_keys.ptr, e->d_pair_ids.ptr, e->d_pair_ctr.ptr};
     const uint32_t long_lo = e->bk.tile_start[kLongBucket], long_hi = e->bk.tile_start[kNumBuckets];
     if (e->have_dict && !e->force_legacy) {
@@ -586,7 +580,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         launch_exact_worklist(a, st);
         e->kernel_launches += 1;
         if (e->max_m > (uint32_t)kExactRegSteps) {
-            launch_exact_worklist_long(a, e->max_m, st);
+            launch_exact_worklist_long(a, std::min<uint32_t>(e->max_m, GFE_MAX_STEPS), st);
             e->kernel_launches += 1;
         }
     }
@@ -622,6 +616,11 @@ static int score_paths_impl(gfe_engine *e, gfe_exchange *x, const uint32_t *path
     if (!path_steps || path_offsets[0] != 0) {
         set_error(e, "gfe_score_paths: malformed path CSR");
         return GFE_ERR_ARG;
+    }
+    if (!filter && e->max_m > GFE_MAX_STEPS) {
+        set_error(e, "gfe_score_paths: an alignment has %u steps; the reference's MAX_N allows %u (unfiltered scoring)",
+                  e->max_m, GFE_MAX_STEPS);
+        return GFE_ERR_LIMIT;
     }
     const uint32_t total = path_offsets[P];
     for (uint32_t p = 0; p < P; ++p) {
@@ -718,6 +717,12 @@ static int score_paths_impl(gfe_engine *e, gfe_exchange *x, const uint32_t *path
         const int rc = score_paths_impl(e, x, path_offsets, path_steps, P, filter, counts);
         e->shard_retries = 0;
         return rc;
+    }
+    if (e->h_counts.ptr[kWorkCounters] & 4u) {
+        CUDA_TRY(e, cudaMemset(e->d_counts.ptr + kWorkCounters, 0, sizeof(uint32_t)));
+        set_error(e, "gfe_score_paths: an alignment of more than %u steps passes the id filter of a candidate path; "
+                     "the reference's dp[MAX_N][MAX_N] cannot hold it", GFE_MAX_STEPS);
+        return GFE_ERR_LIMIT;
     }
     if (e->h_counts.ptr[kWorkCounters]) {
         // a step outside the universe: name it the way the host check did, and clear the flag
@@ -1146,6 +1151,7 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
     a.work_cap = (uint32_t)std::min<size_t>(e->d_work.cap, 0xFFFFFFFFu);
     a.count_stride = 4;
     a.path_tag = 1u << 30;     // what the long-row kernel queues belongs to the fresh set
+    a.err = d_hdr + kWorkCounters;
     e->kernel_launches += 4;
     const uint32_t long_lo = e->bk.tile_start[kLongBucket], long_hi = e->bk.tile_start[kNumBuckets];
     if (long_hi > long_lo) {   // alignments longer than kMaxBucket steps: scored afresh, set 1
@@ -1156,7 +1162,7 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
     launch_exact_worklist(a, st);
     e->kernel_launches += 2;
     if (e->max_m > (uint32_t)kExactRegSteps) {
-        launch_exact_worklist_long(a, e->max_m, st);
+        launch_exact_worklist_long(a, std::min<uint32_t>(e->max_m, GFE_MAX_STEPS), st);
         e->kernel_launches += 1;
     }
     CUDA_TRY(e, cudaGetLastError());
@@ -1222,6 +1228,11 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
     }
     if (h[kWorkCounters]) {
         CUDA_TRY(e, cudaMemset(e->d_counts.ptr + kWorkCounters, 0, 2 * sizeof(uint32_t)));
+        if (h[kWorkCounters] & 4u) {
+            set_error(e, "gfe_score_paths_incremental: an alignment of more than %u steps passes the id filter of a "
+                         "candidate path; the reference's dp[MAX_N][MAX_N] cannot hold it", GFE_MAX_STEPS);
+            return GFE_ERR_LIMIT;
+        }
         set_error(e, "gfe_score_paths_incremental: a step names a node outside the universe");
         return GFE_ERR_ARG;
     }
@@ -1324,6 +1335,10 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
         set_error(e, "gfe_score_pairs: path has %u steps; allowed 1..%u", n, GFE_MAX_STEPS);
         return n == 0 ? GFE_ERR_ARG : GFE_ERR_LIMIT;
     }
+    if (e->max_m > GFE_MAX_STEPS) {
+        set_error(e, "gfe_score_pairs: an alignment has %u steps; the reference's MAX_N allows %u", e->max_m, GFE_MAX_STEPS);
+        return GFE_ERR_LIMIT;
+    }
     // universe = the distinct nodes of the path, in first-visit order
     std::vector<uint32_t> uni;
     uni.reserve(n);
@@ -1398,7 +1413,7 @@ int gfe_score_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, int f
         launch_pair_exact(a, st);
         e->kernel_launches += 1;
         if (e->max_m > (uint32_t)kExactRegSteps) {
-            launch_pair_exact_long(a, e->max_m, st);
+            launch_pair_exact_long(a, std::min<uint32_t>(e->max_m, GFE_MAX_STEPS), st);
             e->kernel_launches += 1;
         }
     }
@@ -1591,6 +1606,10 @@ int gfe_trace_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, uint6
     if (n == 0 || n > GFE_MAX_STEPS) {
         set_error(e, "gfe_trace_pairs: path has %u steps; allowed 1..%u", n, GFE_MAX_STEPS);
         return n == 0 ? GFE_ERR_ARG : GFE_ERR_LIMIT;
+    }
+    if (e->max_m > GFE_MAX_STEPS) {
+        set_error(e, "gfe_trace_pairs: an alignment has %u steps; the reference's MAX_N allows %u", e->max_m, GFE_MAX_STEPS);
+        return GFE_ERR_LIMIT;
     }
     if (first > e->A || count > e->A - first) {
         set_error(e, "gfe_trace_pairs: alignments [%llu, +%u) out of range (A = %llu)",

@@ -658,6 +658,7 @@ __device__ __forceinline__ void settle(const ScoreArgs &a, uint32_t p_glob, cons
     const bool twice = orall & 1u;
     const bool special = twice || ((kFilter ? mn : mn_present) >> 2) == 1u;
     const bool in = valid && (kFilter ? pass : true);
+    if (in && m > GFE_MAX_STEPS_DEV && a.err) atomicOr(a.err, 4u);   // the reference's dp[][] cannot hold this row
     good = in && (gt || occ);
     bad = in && !gt && !occ && !special;
     if (in && !gt && !occ && special) {
@@ -1254,7 +1255,8 @@ void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uin
 }
 
 __global__ void status_flag_kernel(uint32_t *err, const uint32_t *wc, uint32_t *out) {
-    *out = ((err && err[0]) ? 1u : 0u) | (((wc && (wc[1] || wc[3])) || (err && err[1])) ? 2u : 0u);
+    *out = ((err && (err[0] & 1u)) ? 1u : 0u) | (((wc && (wc[1] || wc[3])) || (err && err[1])) ? 2u : 0u) |
+           (err ? (err[0] & 4u) : 0u);
     if (err) err[0] = err[1] = 0;   // reported: a later batch starts clean
 }
 

@@ -93,6 +93,7 @@ struct ScoreArgs {
     // count record of path p, accumulator set s (list entries carry s in bit 30 of the path field):
     // counts[count_stride * p + 2 * s + {0: bad, 1: good}]; plain batches: stride 2, one set
     uint32_t count_stride = 2;
+    uint32_t *err = nullptr;  // bit 2: a row of more than GFE_MAX_STEPS steps passed the id filter (reference: UB)
     uint32_t path_tag = 0;    // OR-ed into the path field of the entries score_paths_kernel queues (set << 30)
 };
 constexpr uint32_t kPathMask = 0x3FFFFFFFu;   // path index inside a list entry's x (bit 31 guess, bit 30 set)

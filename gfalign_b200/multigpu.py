@@ -167,10 +167,22 @@ def main(argv=None):
             sys.stdout.flush()
         E = int(tp.edge_from.size)
         d = torch.zeros(max(2 * E, 1), dtype=torch.int32, device=device)
-        eng.edge_traversals_device(tp.edge_from, tp.edge_to, d.data_ptr())
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.all_reduce(d)                       # integer sum over the alignment shards
+        px = None
+        if world > 1 and E and os.environ.get("GFE_EXCHANGE", "peer") == "peer":
+            try:      # the 2E-slot record summed by the same peer-memory kernel as the search records
+                px = sharded.PeerExchange(2 * E, device)
+            except Exception as ex:
+                sys.stderr.write(f"[multigpu] peer exchange unavailable ({ex!r}); using NCCL\n")
+        if px is not None:
+            stream = torch.cuda.current_stream(device).cuda_stream
+            eng.edge_traversals_device(tp.edge_from, tp.edge_to, px.half_ptr(), stream)
+            px.sum_into(d.data_ptr(), 2 * E, stream)
+            torch.cuda.synchronize()
+        else:
+            eng.edge_traversals_device(tp.edge_from, tp.edge_to, d.data_ptr())
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.all_reduce(d)                   # integer sum over the alignment shards
         if rank == 0 and a.out:
             w = capi.Engine.edge_weights_from_counts(tp.edge_from, tp.edge_to,
                                                      d[:2 * E].cpu().numpy().astype(np.uint32))

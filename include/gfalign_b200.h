@@ -21,7 +21,10 @@
  *     `std::vector<Path> alignmentPaths` (reference src/eval.cpp:121, src/alignments.cpp:451-457).
  *   - reference limits are kept: a candidate path and an alignment have at most GFE_MAX_STEPS steps
  *     (reference MAX_N = 1001, include/alignments.h:246: longer inputs are undefined there; here
- *     they are rejected with GFE_ERR_LIMIT).
+ *     they are rejected with GFE_ERR_LIMIT).  A longer ALIGNMENT is accepted into the table: under the
+ *     id filter of search scoring the reference drops it before its DP unless all its nodes are on the
+ *     candidate path (src/eval.cpp:81-91); GFE_ERR_LIMIT is raised only when one does pass the filter,
+ *     and by every unfiltered call (evalPath, filter = 0).
  */
 #ifndef GFALIGN_B200_H
 #define GFALIGN_B200_H
@@ -312,7 +315,8 @@ int gfe_get_counters(const gfe_engine *e, gfe_counters *out);
  * flags of ALL batches enqueued since the previous report (they are sticky across batches and are
  * cleared by the report) — bit0: a candidate path named a node outside the universe, bit1: a
  * worklist overflowed (results of that batch are incomplete; re-run it through gfe_score_paths,
- * which grows the list and retries by itself). */
+ * which grows the list and retries by itself), bit2: an alignment of more than GFE_MAX_STEPS steps
+ * passed the id filter of a path (the reference cannot score it; gfe_score_paths: GFE_ERR_LIMIT). */
 int gfe_device_status(gfe_engine *e, uint32_t *flags);
 /* The same flags written to a device word, stream-ordered behind the *_device calls on `cuda_stream`
  * (no synchronisation): sharded callers add the word to the exchanged record so that every rank

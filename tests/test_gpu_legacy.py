@@ -41,3 +41,43 @@ def test_pair_dictionary_overflow_falls_back_and_matches_oracle(engine, oracle):
     assert int(got.sum()) > 0
     got = engine.score_paths(po, ps, filter=False)
     assert np.array_equal(got, oracle.evaluate_paths(po, ps, off, st, False, os.cpu_count() or 1))
+
+
+def test_overlong_alignment_is_dropped_by_the_filter_and_flagged_when_it_passes(engine, oracle):
+    """An alignment longer than the reference's MAX_N: in search mode the reference drops it at the id
+    filter whenever a node of it is missing from the candidate path (src/eval.cpp:81-91), so the table
+    is accepted and scored; only a path on which it passes the filter (undefined in the reference:
+    dp[1001][1001]) and the unfiltered entry points raise GFE_ERR_LIMIT."""
+    import gfalign_b200
+    w = synth.make_workload("cfg3", A=20000)
+    t = w.tangle
+    nodes, _, _ = synth.node_table(t)
+    po, ps = synth.candidate_paths(t, 40, seed=5)
+    missing = sorted(set(range(t.n_nodes)) - set((ps >> 1).tolist()))
+    a, b = int(ps[po[3]]) >> 1, int(ps[po[3] + 1]) >> 1      # two nodes of candidate 3
+    # long row 1: names a node no candidate visits -> filtered for every candidate
+    assert missing
+    long1 = np.array(([a << 1, b << 1] * 700)[:1399] + [missing[0] << 1], dtype=np.uint32)
+    off = np.concatenate([w.offsets, [w.offsets[-1] + long1.size]]).astype(np.uint32)
+    st = np.concatenate([w.steps, long1]).astype(np.uint32)
+    engine.set_alignments(off, st, t.n_nodes)
+    engine.set_universe(nodes)
+    got = engine.score_paths(po, ps, filter=True)
+    assert np.array_equal(got, oracle.evaluate_paths(po, ps, w.offsets, w.steps, True, 4))   # as if the row were absent
+    with pytest.raises(gfalign_b200.GfeError) as ex:
+        engine.score_paths(po, ps, filter=False)
+    assert ex.value.status == -3
+    with pytest.raises(gfalign_b200.GfeError):
+        engine.score_pairs(ps[po[0]:po[1]])
+    # long row 2: only nodes a, b -> passes the filter of candidate 3: reference behaviour undefined -> LIMIT
+    long2 = np.array(([a << 1, b << 1] * 700)[:1300], dtype=np.uint32)
+    off = np.concatenate([w.offsets, [w.offsets[-1] + long2.size]]).astype(np.uint32)
+    st = np.concatenate([w.steps, long2]).astype(np.uint32)
+    engine.set_alignments(off, st, t.n_nodes)
+    engine.set_universe(nodes)
+    with pytest.raises(gfalign_b200.GfeError) as ex:
+        engine.score_paths(po, ps, filter=True)
+    assert ex.value.status == -3
+    engine.set_alignments(w.offsets, w.steps, t.n_nodes)      # and the engine is usable afterwards
+    engine.set_universe(nodes)
+    assert np.array_equal(engine.score_paths(po, ps, filter=True), got)

@@ -199,8 +199,14 @@ def test_limits_rejected(engine):
     long_path = np.zeros(1001, np.uint32)
     with pytest.raises(gfalign_b200.GfeError):
         engine.score_paths(np.array([0, 1001], np.uint32), long_path)
+    # an over-long alignment is accepted into the table (the id filter may drop it, test_gpu_legacy.py) but
+    # every unfiltered entry point refuses it: the reference's dp[MAX_N][MAX_N] cannot hold it
+    engine.set_alignments(np.array([0, 1001], np.uint32), np.zeros(1001, np.uint32), 2)
     with pytest.raises(gfalign_b200.GfeError):
-        engine.set_alignments(np.array([0, 1001], np.uint32), np.zeros(1001, np.uint32), 2)
+        engine.score_pairs(np.array([0, 2], np.uint32))
+    engine.set_universe(np.arange(2, dtype=np.uint32))
+    with pytest.raises(gfalign_b200.GfeError):
+        engine.score_paths(np.array([0, 2], np.uint32), np.array([0, 2], np.uint32), filter=False)
     with pytest.raises(gfalign_b200.GfeError):   # node outside the universe
         engine.set_alignments(np.array([0, 1], np.uint32), np.array([0], np.uint32), 4)
         engine.set_universe(np.array([0, 1], np.uint32))
