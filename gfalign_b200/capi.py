@@ -87,7 +87,7 @@ EXPORTS = [
     "gfe_text_qname", "gfe_peer_sum_u32", "gfe_device_status_to",
     "gfe_exchange_create", "gfe_exchange_destroy", "gfe_score_paths_sharded", "gfe_search_sharded",
     "gfe_score_paths_incremental", "gfe_score_paths_incremental_sharded", "gfe_exchange_set_batch_sharding",
-    "gfe_last_aux_kernel_ms",
+    "gfe_last_aux_kernel_ms", "gfe_set_dedup", "gfe_get_dedup_stats",
 ]
 
 PEER_MAX = 16      # GFE_PEER_MAX
@@ -183,6 +183,9 @@ def load_library() -> C.CDLL:
                                            C.POINTER(_SearchStats)]
     lib.gfe_get_counters.argtypes = [C.c_void_p, C.POINTER(_Counters)]
     lib.gfe_set_timing.argtypes = [C.c_void_p, C.c_int]
+    lib.gfe_set_dedup.argtypes = [C.c_void_p, C.c_int]
+    lib.gfe_get_dedup_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                        C.POINTER(C.c_uint64), C.POINTER(C.c_int)]
     lib.gfe_last_kernel_ms.argtypes = [C.c_void_p]
     lib.gfe_last_kernel_ms.restype = C.c_float
     lib.gfe_last_aux_kernel_ms.argtypes = [C.c_void_p]
@@ -412,6 +415,15 @@ class Engine:
         c = _Counters()
         self._check(self._lib.gfe_get_counters(self._h, C.byref(c)))
         return {f: getattr(c, f) for f, _ in _Counters._fields_}
+
+    def set_dedup(self, on: bool):
+        """Multiplicity compression of the scoring view for full scans; applies at the next set_universe."""
+        self._check(self._lib.gfe_set_dedup(self._h, int(on)))
+
+    def dedup_stats(self) -> dict:
+        r, d, v, u = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_int()
+        self._check(self._lib.gfe_get_dedup_stats(self._h, C.byref(r), C.byref(d), C.byref(v), C.byref(u)))
+        return {"rows": r.value, "distinct_walks": d.value, "view_rows": v.value, "in_use": bool(u.value)}
 
     def set_timing(self, on: bool):
         self._check(self._lib.gfe_set_timing(self._h, int(on)))

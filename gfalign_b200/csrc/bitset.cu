@@ -113,22 +113,38 @@ struct Planes {
     }
 };
 
-// Bucket (row length) of a unit: lane k compares with the first unit of bucket k (s_ustart: a
-// shared copy of unit_start, 0xFFFFFFFF beyond kMaxBucket), one vote counts the buckets passed.
-__device__ __forceinline__ int unit_bucket(const uint32_t *s_ustart, uint32_t unit, int lane) {
-    return __popc(__ballot_sync(0xFFFFFFFFu, unit >= s_ustart[lane])) - 1;   // entries 0 and 1 are 0
+// Group of a unit: the last group whose first unit is <= unit (s_gstart: shared copy of the groups'
+// unit_start, ascending).  Warp-uniform.
+__device__ __forceinline__ uint32_t unit_group(const uint32_t *s_gstart, uint32_t n_groups, uint32_t unit) {
+    uint32_t lo = 0, hi = n_groups;           // invariant: s_gstart[lo] <= unit < s_gstart[hi] (hi == n: +inf)
+    while (hi - lo > 1) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (s_gstart[mid] <= unit) lo = mid;
+        else hi = mid;
+    }
+    return lo;
 }
 
 // first row / row count / bytes of a unit; used to prefetch the next unit's rows into L1
-__device__ __forceinline__ void prefetch_unit(const BitsetArgs &a, uint32_t unit, int b, int lane) {
-    if (unit >= a.unit_start[kMaxBucket + 1]) return;
-    const uint32_t row0 = (unit - a.unit_start[b]) * a.unit_rows;
-    const uint32_t nrows = min(a.unit_rows, a.bk.count[b] - row0);
-    const uint32_t rs = row_stride(b);
-    const char *p = reinterpret_cast<const char *>(a.bk.bstep + a.bk.step_base[b] + (size_t)row0 * rs);
+__device__ __forceinline__ void prefetch_unit(const BitsetArgs &a, uint32_t unit, const UnitGroup &g, int lane) {
+    const uint32_t row0 = g.row0 + (unit - g.unit_start) * a.unit_rows;
+    const uint32_t nrows = min(a.unit_rows, g.row0 + g.nrows - row0);
+    const uint32_t rs = row_stride(g.m);
+    const char *p = reinterpret_cast<const char *>(a.bk.bstep + a.bk.step_base[g.m] + (size_t)row0 * rs);
     const uint32_t bytes = nrows * rs * 2u;
     for (uint32_t o = (uint32_t)lane * 128u; o < bytes + 127u; o += 32u * 128u)
         asm volatile("prefetch.global.L1 [%0];" ::"l"(p + min(o, bytes - 1u)));
+}
+
+__device__ __forceinline__ UnitGroup load_group(const UnitGroup *g) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(g));
+    UnitGroup r;
+    r.unit_start = v.x;
+    r.row0 = v.y;
+    r.nrows = v.z;
+    r.m = (uint16_t)(v.w & 0xFFFFu);
+    r.shift = (uint16_t)(v.w >> 16);
+    return r;
 }
 
 // Push the set bits of the eight masks of one warp step (paths word_base .. word_base+31, rows
@@ -434,9 +450,9 @@ score_bitset_kernel(const BitsetArgs a) {
     const uint32_t chunk = blockIdx.y;
     const uint32_t p_base = chunk * 32u * W;
     const int lane = threadIdx.x & 31;
-    __shared__ uint32_t s_ustart[32];
+    __shared__ uint32_t s_gstart[kMaxGroups];
     if (threadIdx.x == 0) mbar_init(s_bar, 1);
-    if (threadIdx.x < 32) s_ustart[threadIdx.x] = threadIdx.x <= kMaxBucket ? a.unit_start[threadIdx.x] : 0xFFFFFFFFu;
+    for (uint32_t i = threadIdx.x; i < a.n_groups; i += blockDim.x) s_gstart[i] = a.groups[i].unit_start;
     for (uint32_t i = threadIdx.x; i < 64u * W; i += blockDim.x) s_cnt[i] = 0;
     __syncthreads();
     pdl_wait();      // build_tables' mask tables (everything above only touched this CTA's shared memory)
@@ -464,7 +480,8 @@ score_bitset_kernel(const BitsetArgs a) {
     B.clear();
     uint32_t rows_acc = 0;
     uint2 slow_win = make_uint2(0u, 0u);   // this warp's reserved window of the second-look list
-    const uint32_t n_units = a.unit_start[kMaxBucket + 1];
+    const uint32_t n_units = a.n_units;
+    uint32_t cur_shift = 0;                // the counters hold rows of weight 2^cur_shift
     UnitCtx ctx;
     ctx.nt = nt;
     ctx.nf = nf;
@@ -489,8 +506,8 @@ score_bitset_kernel(const BitsetArgs a) {
                 const uint32_t g = ((gl >> (8 * j)) & 0xFFu) | (((gh >> (8 * j)) & 0xFFu) << 8);
                 const uint32_t b = ((bl >> (8 * j)) & 0xFFu) | (((bh >> (8 * j)) & 0xFFu) << 8);
                 const uint32_t col = 32 * w + c + 8 * j;
-                if (b) atomicAdd(&s_cnt[2 * col], b);
-                if (g) atomicAdd(&s_cnt[2 * col + 1], g);
+                if (b) atomicAdd(&s_cnt[2 * col], b << cur_shift);
+                if (g) atomicAdd(&s_cnt[2 * col + 1], g << cur_shift);
             }
         }
         G.clear();
@@ -508,20 +525,25 @@ score_bitset_kernel(const BitsetArgs a) {
         pending = atomicAdd(a.unit_ctr + chunk, 1u);
     }
     next = __shfl_sync(0xFFFFFFFFu, next, 0);
-    int next_b = unit_bucket(s_ustart, n_units - 1u - min(next, n_units - 1u), lane);
+    UnitGroup next_g = load_group(a.groups + unit_group(s_gstart, a.n_groups, n_units - 1u - min(next, n_units - 1u)));
     for (;;) {
         if (next >= n_units) break;
         const uint32_t unit = n_units - 1u - next;
-        const int b = next_b;
+        const UnitGroup gr = next_g;
+        const int b = gr.m;
         next = __shfl_sync(0xFFFFFFFFu, pending, 0);
         if (lane == 0) pending = atomicAdd(a.unit_ctr + chunk, 1u);
         if (next < n_units) {
-            next_b = unit_bucket(s_ustart, n_units - 1u - next, lane);
-            prefetch_unit(a, n_units - 1u - next, next_b, lane);
+            next_g = load_group(a.groups + unit_group(s_gstart, a.n_groups, n_units - 1u - next));
+            prefetch_unit(a, n_units - 1u - next, next_g, lane);
+        }
+        if (gr.shift != cur_shift) {       // another multiplicity class: settle the counters first
+            flush();
+            cur_shift = gr.shift;
         }
         // rows [row0, row0 + unrows) of bucket b's dense matrix
-        const uint32_t row0 = (unit - a.unit_start[b]) * a.unit_rows;
-        const uint32_t unrows = min(a.unit_rows, a.bk.count[b] - row0);
+        const uint32_t row0 = gr.row0 + (unit - gr.unit_start) * a.unit_rows;
+        const uint32_t unrows = min(a.unit_rows, gr.row0 + gr.nrows - row0);
         const uint16_t *ubase = a.bk.bstep + a.bk.step_base[b] + (size_t)row0 * row_stride(b);
         const uint32_t usorted = a.bk.row_start[b] + row0;
         const uint32_t ulm = tab[(a.mg.lm_base + b) * W];
@@ -695,7 +717,7 @@ void launch_w(const BitsetArgs &a, int sm_count, cudaStream_t st) {
     const uint32_t chunks = (a.P + 32 * W - 1) / (32 * W);
     uint32_t gx = (uint32_t)sm_count / chunks;
     if (gx < 1) gx = 1;
-    const uint32_t n_units = a.unit_start[kMaxBucket + 1];
+    const uint32_t n_units = a.n_units;
     const uint32_t max_gx = (n_units + (kBitThreads / 32) - 1) / (kBitThreads / 32);
     if (gx > max_gx) gx = max_gx ? max_gx : 1;
     launch_pdl(1, score_bitset_kernel<W>, dim3(gx, chunks), dim3(kBitThreads), smem, st, a);

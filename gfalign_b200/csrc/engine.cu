@@ -105,6 +105,8 @@ int gfe_create(int cuda_device, gfe_engine **out) {
     {
         const char *fl = getenv("GFE_FORCE_LEGACY");
         e->force_legacy = (fl && fl[0] == '1') ? 1 : 0;
+        const char *dd = getenv("GFE_DEDUP");
+        e->dedup_enabled = !(dd && dd[0] == '0');
     }
     const bool dbg = getenv("GFE_DEBUG_TIMING") != nullptr;
     auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
@@ -198,6 +200,21 @@ int gfe_device_status_to(gfe_engine *e, uint32_t *d_flags, void *cuda_stream) {
     return GFE_OK;
 }
 
+int gfe_set_dedup(gfe_engine *e, int enabled) {
+    if (!e) return GFE_ERR_ARG;
+    e->dedup_enabled = enabled != 0;
+    return GFE_OK;
+}
+
+int gfe_get_dedup_stats(const gfe_engine *e, uint64_t *rows, uint64_t *distinct, uint64_t *view_rows, int *in_use) {
+    if (!e) return GFE_ERR_ARG;
+    if (rows) *rows = e->dedup_rows;
+    if (distinct) *distinct = e->dedup_distinct;
+    if (view_rows) *view_rows = e->dedup_view_rows;
+    if (in_use) *in_use = (e->have_dedup && e->dedup_enabled) ? 1 : 0;
+    return GFE_OK;
+}
+
 int gfe_get_counters(const gfe_engine *e, gfe_counters *out) {
     if (!e || !out) return GFE_ERR_ARG;
     out->kernel_launches = e->kernel_launches;
@@ -243,16 +260,8 @@ static int validate_csr_host(gfe_engine *e, const uint32_t *offsets, const uint3
     return GFE_OK;
 }
 
-// Length histogram of the alignment table on the device -> bucket geometry (host copy in e->bk).
-static int build_bucket_geometry(gfe_engine *e) {
-    TRY(ensure_dev(e, e->d_hist, kNumBuckets + 2));
-    CUDA_TRY(e, cudaMemsetAsync(e->d_hist.ptr, 0, (kNumBuckets + 2) * sizeof(uint32_t), e->stream));
-    launch_length_histogram(e->d_off, e->A, e->d_hist.ptr, e->stream);
-    e->kernel_launches += e->A ? 1 : 0;
-    uint32_t hist[kNumBuckets + 2];
-    CUDA_TRY(e, cudaMemcpyAsync(hist, e->d_hist.ptr, sizeof(hist), cudaMemcpyDeviceToHost, e->stream));
-    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-    Buckets &bk = e->bk;
+// rows per bucket (hist[0..kNumBuckets-1]; hist[kNumBuckets + 1] = steps of the long rows) -> geometry
+static void layout_buckets(const uint32_t *hist, Buckets &bk, uint64_t *elems) {
     uint64_t row = 0, tile = 0, base = 0;
     for (int b = 0; b < kNumBuckets; ++b) {
         bk.count[b] = hist[b];
@@ -267,12 +276,138 @@ static int build_bucket_geometry(gfe_engine *e) {
     }
     bk.row_start[kNumBuckets] = (uint32_t)row;
     bk.tile_start[kNumBuckets] = (uint32_t)tile;
+    *elems = base + 8;
+}
 
-    if (base + 8 >= 0xFFFFFFFFull) {
+// Scheduling groups of the bitset kernel for one view: gcount[m * 32 + k] rows in class k of bucket m
+// (plain view: everything in class 0).  One table per W.
+static int build_group_tables(gfe_engine *e, int view, const uint32_t *gcount, uint64_t rows_total) {
+    std::vector<UnitGroup> host((size_t)6 * kMaxGroups);
+    for (int wi = 0; wi < 6; ++wi) {
+        const uint32_t W = 1u << wi;
+        const uint32_t step = 4u * (32u / W);
+        const uint64_t warps = (uint64_t)e->sm_count * (kBitThreads / 32);
+        const uint64_t want = rows_total / (8 * warps) / step * step;
+        const uint32_t ur = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(want, step), 8 * step);
+        uint32_t unit = 0, ng = 0;
+        for (int m = 1; m <= kMaxBucket; ++m) {
+            uint32_t row0 = 0;
+            for (int k = 0; k < 32; ++k) {
+                const uint32_t n = gcount[m * 32 + k];
+                if (!n) continue;
+                UnitGroup g;
+                g.unit_start = unit;
+                g.row0 = row0;
+                g.nrows = n;
+                g.m = (uint16_t)m;
+                g.shift = (uint16_t)k;
+                host[(size_t)wi * kMaxGroups + ng++] = g;
+                unit += (n + ur - 1) / ur;
+                row0 += n;
+            }
+        }
+        e->n_groups[view][wi] = ng;
+        e->n_units[view][wi] = unit;
+        e->unit_rows[view][wi] = ur;
+    }
+    TRY(ensure_dev(e, e->d_groups[view], host.size()));
+    CUDA_TRY(e, cudaMemcpyAsync(e->d_groups[view].ptr, host.data(), host.size() * sizeof(UnitGroup),
+                                cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));   // `host` goes out of scope
+    return GFE_OK;
+}
+
+// Multiplicity-compressed copy of the scoring view (see kernels.cu); kept only when it shrinks the
+// bucketed rows by at least a quarter.
+static int build_dedup_view(gfe_engine *e, const PairDict &pd) {
+    e->have_dedup = false;
+    const uint64_t short_rows = (uint64_t)e->bk.row_start[kLongBucket] - e->bk.row_start[1];
+    if (!e->dedup_enabled || !e->have_dict || short_rows < 1024) return GFE_OK;
+    cudaStream_t st = e->stream;
+    uint32_t cap = 1024;
+    while ((uint64_t)cap < 2 * short_rows && cap < (1u << 31)) cap <<= 1;
+    TRY(ensure_dev(e, e->d_dedup, cap));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_dedup.ptr, 0xFF, (size_t)cap * sizeof(DedupSlot), st));
+    launch_dedup_insert(e->d_off, e->d_steps, e->d_node2local.ptr, e->A, e->d_dedup.ptr, cap, st);
+    const size_t misc_words = (size_t)3 * (kDedupStats + 2);
+    TRY(ensure_dev(e, e->d_dedup_misc, misc_words));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_dedup_misc.ptr, 0, misc_words * 4, st));
+    uint32_t *d_gcount = e->d_dedup_misc.ptr, *d_cbase = d_gcount + (kDedupStats + 2), *d_cur = d_cbase + (kDedupStats + 2);
+    launch_dedup_count(e->d_dedup.ptr, cap, e->d_off, d_gcount, st);
+    std::vector<uint32_t> gcount(kDedupStats + 2);
+    CUDA_TRY(e, cudaMemcpyAsync(gcount.data(), d_gcount, gcount.size() * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(e, cudaStreamSynchronize(st));
+    e->kernel_launches += 3;
+    uint64_t view_rows = 0;
+    for (uint32_t i = 32; i < kDedupStats; ++i) view_rows += gcount[i];
+    e->dedup_rows = short_rows;
+    e->dedup_view_rows = view_rows;
+    e->dedup_distinct = gcount[kDedupStats];
+    if (gcount[kDedupStats + 1] != short_rows) {
+        set_error(e, "internal: multiplicity table holds %u of %llu rows", gcount[kDedupStats + 1],
+                  (unsigned long long)short_rows);
+        return GFE_ERR_CUDA;
+    }
+    if (view_rows * 4 > short_rows * 3) return GFE_OK;        // not worth a second copy of the view
+    // geometry of the compressed view: the same empty and long rows, class-sorted short rows
+    uint32_t hist[kNumBuckets + 2] = {};
+    hist[0] = e->bk.count[0];
+    hist[kLongBucket] = e->bk.count[kLongBucket];
+    std::vector<uint32_t> cbase(kDedupStats + 2, 0);
+    for (int m = 1; m <= kMaxBucket; ++m) {
+        uint32_t row = 0;
+        for (int k = 0; k < 32; ++k) {
+            cbase[m * 32 + k] = row;
+            row += gcount[m * 32 + k];
+        }
+        hist[m] = row;
+    }
+    // steps of the long rows: what the plain view holds between its long base and its end
+    hist[kNumBuckets + 1] = (uint32_t)(e->bstep_elems - 8 - e->bk.step_base[kLongBucket]);
+    uint64_t elems = 0;
+    layout_buckets(hist, e->bk2, &elems);
+    TRY(ensure_dev(e, e->d_bstep2, elems));
+    TRY(ensure_dev(e, e->d_ldesc2, std::max<uint32_t>(hist[kLongBucket], 1)));
+    TRY(ensure_dev(e, e->d_rshift2, (size_t)e->bk2.row_start[kNumBuckets] + 1));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_rshift2.ptr, 0, (size_t)e->bk2.row_start[kNumBuckets] + 1, st));
+    CUDA_TRY(e, cudaMemcpyAsync(d_cbase, cbase.data(), cbase.size() * 4, cudaMemcpyHostToDevice, st));
+    e->bk2.bstep = e->d_bstep2.ptr;
+    e->bk2.ldesc = e->d_ldesc2.ptr;
+    e->bk2.perm = nullptr;                 // the search kernels never ask which alignment a row was
+    const uint32_t np = e->n_pairs, bias = geom_pair_base(e->L);
+    launch_dedup_scatter(e->d_dedup.ptr, cap, e->d_off, e->d_steps, e->d_node2local.ptr, e->bk2, e->d_bstep2.ptr, d_cbase,
+                         d_cur, e->d_rshift2.ptr, pd, np, bias, st);
+    if (hist[kLongBucket]) {               // long rows: copied as they are
+        TRY(ensure_dev(e, e->d_cursors, kNumBuckets + 1));
+        CUDA_TRY(e, cudaMemsetAsync(e->d_cursors.ptr, 0, (kNumBuckets + 1) * sizeof(uint32_t), st));
+        launch_bucket_scatter(e->d_off, e->d_steps, e->d_node2local.ptr, e->A, e->bk2, e->d_bstep2.ptr, e->d_ldesc2.ptr,
+                              nullptr, e->d_cursors.ptr, pd, np, bias, st, true);
+        e->kernel_launches += 1;
+    }
+    e->kernel_launches += 1;
+    CUDA_TRY(e, cudaGetLastError());
+    CUDA_TRY(e, cudaStreamSynchronize(st));    // cbase goes out of scope
+    TRY(build_group_tables(e, 1, gcount.data(), view_rows));
+    e->have_dedup = true;
+    return GFE_OK;
+}
+
+// Length histogram of the alignment table on the device -> bucket geometry (host copy in e->bk).
+static int build_bucket_geometry(gfe_engine *e) {
+    TRY(ensure_dev(e, e->d_hist, kNumBuckets + 2));
+    CUDA_TRY(e, cudaMemsetAsync(e->d_hist.ptr, 0, (kNumBuckets + 2) * sizeof(uint32_t), e->stream));
+    launch_length_histogram(e->d_off, e->A, e->d_hist.ptr, e->stream);
+    e->kernel_launches += e->A ? 1 : 0;
+    uint32_t hist[kNumBuckets + 2];
+    CUDA_TRY(e, cudaMemcpyAsync(hist, e->d_hist.ptr, sizeof(hist), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    uint64_t elems = 0;
+    layout_buckets(hist, e->bk, &elems);
+    if (elems >= 0xFFFFFFFFull) {
         set_error(e, "alignment shard has too many steps for 32-bit element offsets; shard it");
         return GFE_ERR_LIMIT;
     }
-    e->bstep_elems = base + 8;
+    e->bstep_elems = elems;
     e->max_m = hist[kNumBuckets];
     return GFE_OK;
 }
@@ -407,6 +542,13 @@ static int set_universe_impl(gfe_engine *e, const uint32_t *nodes, uint32_t n_un
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));
     e->h2d_bytes += (size_t)e->n_nodes * sizeof(uint32_t);
     e->tab_stride = ((e->L + 1 + 7) / 8) * 8;
+    e->have_dedup = false;
+    if (e->have_dict) {
+        std::vector<uint32_t> gcount(kDedupStats + 2, 0);
+        for (int m = 1; m <= kMaxBucket; ++m) gcount[m * 32] = e->bk.count[m];
+        TRY(build_group_tables(e, 0, gcount.data(), e->A));
+        TRY(build_dedup_view(e, pd));
+    }
     e->have_universe = true;
     e->have_index = false;
     return GFE_OK;
@@ -460,8 +602,12 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     pro.total = total_steps;
     pro.err = d_bad_step;
     pro.sticky = d_sticky;
+    // full scans read the multiplicity-compressed view when the universe has one
+    const int view = (e->have_dedup && e->dedup_enabled && e->have_dict && !e->force_legacy) ? 1 : 0;
+    const Buckets &vbk = view ? e->bk2 : e->bk;
     ScoreArgs a;
-    a.bk = e->bk;
+    a.bk = vbk;
+    a.rshift = view ? e->d_rshift2.ptr : nullptr;
     a.poff = d_poff;
     a.pstep = d_pstep;
     a.ptab = e->d_ptab.ptr;
@@ -476,7 +622,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
     a.work_cap = (uint32_t)std::min<size_t>(e->d_work.cap, 0xFFFFFFFFu);
     a.err = d_bad_step;
     const PairDict pd{e->d_pair_keys.ptr, e->d_pair_ids.ptr, e->d_pair_ctr.ptr};
-    const uint32_t long_lo = e->bk.tile_start[kLongBucket], long_hi = e->bk.tile_start[kNumBuckets];
+    const uint32_t long_lo = vbk.tile_start[kLongBucket], long_hi = vbk.tile_start[kNumBuckets];
     if (e->have_dict && !e->force_legacy) {
         // ---- bitset kernel: 32*W paths per CTA pass, mask table in shared memory ----------------
         MaskGeom mg;
@@ -519,7 +665,7 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         launch_build_tables(d_poff, d_pstep, P, e->L, e->tab_stride, e->d_ptab.ptr, e->d_pnext.ptr,
                             e->d_masks.ptr, e->d_masks.ptr + table_words, mg, pd, st);
         BitsetArgs b;
-        b.bk = e->bk;
+        b.bk = vbk;
         b.mg = mg;
         b.masks = e->d_masks.ptr;
         b.fplane = e->d_masks.ptr + table_words;
@@ -530,23 +676,15 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
         b.slow = e->d_slow.ptr;
         b.work_count = d_work_count;
         b.slow_cap = (uint32_t)std::min<size_t>(e->d_slow.cap, 0xFFFFFFFFu);
-        // scheduling units: eight warp steps of 32/W rows, at least 16 rows (short tail)
-        // scheduling units: a multiple of four warp steps (32/W rows each); small enough that every
-        // warp of the grid gets several units, large enough to amortise the fetch
+        // scheduling units: a multiple of four warp steps (32/W rows each), small enough that every warp
+        // of the grid gets several units; the group tables were built with the universe (build_group_tables)
         {
-            const uint32_t step = 4u * (32u / W);
-            const uint64_t warps = (uint64_t)e->sm_count * (kBitThreads / 32);
-            uint64_t want = e->A / (8 * warps) / step * step;
-            b.unit_rows = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(want, step), 8 * step);
-        }
-        {
-            uint32_t unit = 0;
-            b.unit_start[0] = 0;
-            for (int k = 1; k <= kMaxBucket; ++k) {
-                b.unit_start[k] = unit;
-                unit += (e->bk.count[k] + b.unit_rows - 1) / b.unit_rows;
-            }
-            b.unit_start[kMaxBucket + 1] = unit;
+            int wi = 0;
+            while ((1u << wi) < W) ++wi;
+            b.unit_rows = e->unit_rows[view][wi];
+            b.groups = e->d_groups[view].ptr + (size_t)wi * kMaxGroups;
+            b.n_groups = e->n_groups[view][wi];
+            b.n_units = e->n_units[view][wi];
         }
         if (e->timing) {
             TRY(next_event_pair(e));

@@ -50,6 +50,21 @@ struct gfe_engine {
     uint32_t L = 0, tab_stride = 8;
     bool have_universe = false;
 
+    // scheduling groups of the bitset kernel, one table per W in {1,2,4,8,16,32} (index log2 W), for
+    // the plain view [0] and the deduplicated view [1]; built with the universe
+    DevBuf<gfe::UnitGroup> d_groups[2];
+    uint32_t n_groups[2][6] = {}, n_units[2][6] = {}, unit_rows[2][6] = {};
+    // multiplicity-compressed view (K1 full scans): distinct rows up to reverse complement, class k =
+    // bit k of the multiplicity (kernels.cu dedup_*); built with the universe when it pays
+    DevBuf<gfe::DedupSlot> d_dedup;
+    DevBuf<uint16_t> d_bstep2;
+    DevBuf<uint2> d_ldesc2;
+    DevBuf<uint8_t> d_rshift2;
+    DevBuf<uint32_t> d_dedup_misc;       // class histogram / class bases / cursors
+    gfe::Buckets bk2{};
+    bool have_dedup = false, dedup_enabled = true;
+    uint64_t dedup_rows = 0, dedup_view_rows = 0, dedup_distinct = 0;
+
     // pair dictionary of the universe-local view + per-batch bitsets (bitset kernel)
     DevBuf<uint32_t> d_pair_keys, d_pair_ids, d_pair_ctr, d_masks, d_unit_ctr;
     DevBuf<uint2> d_slow;
@@ -121,6 +136,8 @@ struct gfe_engine {
         fd(d_edge_adj.ptr); fd(d_edge_deg.ptr); fd(d_edge_cnt.ptr);
         fd(d_pair_keys.ptr); fd(d_pair_ids.ptr); fd(d_pair_ctr.ptr); fd(d_masks.ptr);
         fd(d_unit_ctr.ptr); fd(d_slow.ptr);
+        fd(d_groups[0].ptr); fd(d_groups[1].ptr); fd(d_dedup.ptr); fd(d_bstep2.ptr); fd(d_ldesc2.ptr);
+        fd(d_rshift2.ptr); fd(d_dedup_misc.ptr);
         fd(d_inv_off.ptr); fd(d_inv_cursor.ptr); fd(d_inv_rows.ptr); fd(d_chunk_node.ptr); fd(d_desc.ptr);
         fd(d_tr_path.ptr); fd(d_tr_misc.ptr); fd(d_tr_dirs.ptr); fd(d_tr_len.ptr); fd(d_tr_longb.ptr);
         fd(d_tr_base.ptr); fd(d_tr_first.ptr); fd(d_tr_score.ptr); fd(d_tr_longrows.ptr);

@@ -104,6 +104,37 @@ __global__ void pair_assign_kernel(const PairDict pd) {
     if (h < kPairHashCap && pd.keys[h] != kPairEmpty) pd.ids[h] = atomicAdd(pd.counter + 1, 1u);
 }
 
+// One row of the scoring view at element offset dst: m local steps, then (bucketed rows only) m-1 pair
+// entries, m-2 triple-slot bytes and zero padding (layout: kernels.cuh row_stride).
+__device__ __forceinline__ void write_view_row(uint16_t *__restrict__ bstep, uint32_t dst,
+                                               const uint32_t *__restrict__ src, uint32_t m, bool is_long,
+                                               const uint32_t *__restrict__ map, const PairDict &pd,
+                                               uint32_t n_pairs, uint32_t pair_bias) {
+    uint32_t prev = 0, prev_pid = 0;
+    unsigned char *slots = reinterpret_cast<unsigned char *>(bstep + dst + 2 * m - 1);
+    for (uint32_t j = 0; j < m; ++j) {
+        const uint32_t s = __ldg(src + j);
+        const uint32_t l = (__ldg(map + (s >> 1)) << 1) | (s & 1u);
+        bstep[dst + j] = (uint16_t)l;
+        if (!is_long && j > 0) {
+            uint32_t pid = 2u * n_pairs;   // pair with a node outside the universe
+            if (n_pairs != 0xFFFFFFFFu) {
+                uint32_t flip;
+                const uint32_t key = pair_canonical(prev, l, &flip);
+                const uint32_t h = pair_find(pd, key);
+                if (h != kPairEmpty) pid = 2u * pd.ids[h] + flip;
+            }
+            bstep[dst + m + j - 1] = (uint16_t)(pid + pair_bias);   // absolute table entry
+            if (j >= 2) slots[j - 2] = (unsigned char)triple_slot(prev_pid, pid);
+            prev_pid = pid;
+        }
+        prev = l;
+    }
+    if (!is_long)   // zero the padding behind the slot bytes
+        for (uint32_t j = 2 * (2 * m - 1) + (m > 2 ? m - 2 : 0); j < 2 * row_stride((int)m); ++j)
+            reinterpret_cast<unsigned char *>(bstep + dst)[j] = 0;
+}
+
 // K0b: scatter every alignment into its length bucket, translating steps to universe-local 16-bit
 // ids on the way (node2local gathered through L2).  Row order inside a bucket is arbitrary; perm
 // remembers the original index.  Slots are handed out per CTA (shared-memory ranks + one global
@@ -113,7 +144,7 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
                       const uint32_t *__restrict__ map, uint64_t A, const Buckets bk,
                       uint16_t *__restrict__ bstep, uint2 *__restrict__ ldesc,
                       uint32_t *__restrict__ perm, uint32_t *__restrict__ cursors,
-                      const PairDict pd, uint32_t n_pairs, uint32_t pair_bias) {
+                      const PairDict pd, uint32_t n_pairs, uint32_t pair_bias, const bool only_long) {
     __shared__ uint32_t s_cnt[kNumBuckets + 1], s_base[kNumBuckets + 1];
     const uint64_t n_tiles = (A + kBlock - 1) / kBlock;
     for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -121,11 +152,14 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
         __syncthreads();
         const uint64_t a = tile * kBlock + threadIdx.x;
         uint32_t o0 = 0, m = 0, b = 0, rank = 0, lrank = 0;
-        const bool valid = a < A;
+        bool valid = a < A;
         if (valid) {
             o0 = __ldg(off + a);
             m = __ldg(off + a + 1) - o0;
             b = m <= (uint32_t)kMaxBucket ? m : (uint32_t)kLongBucket;
+            if (only_long && b != (uint32_t)kLongBucket) valid = false;   // the deduplicated view: short rows come from the table
+        }
+        if (valid) {
             rank = atomicAdd(&s_cnt[b], 1u);
             if (b == (uint32_t)kLongBucket) lrank = atomicAdd(&s_cnt[kNumBuckets], m);
         }
@@ -135,7 +169,7 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
         __syncthreads();
         if (valid) {
             const uint32_t slot = s_base[b] + rank;
-            perm[bk.row_start[b] + slot] = (uint32_t)a;
+            if (perm) perm[bk.row_start[b] + slot] = (uint32_t)a;
             uint32_t dst;
             if (b == (uint32_t)kLongBucket) {
                 dst = bk.step_base[b] + s_base[kNumBuckets] + lrank;
@@ -143,31 +177,150 @@ bucket_scatter_kernel(const uint32_t *__restrict__ off, const uint32_t *__restri
             } else {
                 dst = bk.step_base[b] + slot * row_stride((int)m);
             }
-            uint32_t prev = 0, prev_pid = 0;
-            unsigned char *slots = reinterpret_cast<unsigned char *>(bstep + dst + 2 * m - 1);
-            for (uint32_t j = 0; j < m; ++j) {
-                const uint32_t s = __ldg(steps + o0 + j);
-                const uint32_t l = (__ldg(map + (s >> 1)) << 1) | (s & 1u);
-                bstep[dst + j] = (uint16_t)l;
-                if (b != (uint32_t)kLongBucket && j > 0) {
-                    uint32_t pid = 2u * n_pairs;   // pair with a node outside the universe
-                    if (n_pairs != 0xFFFFFFFFu) {
-                        uint32_t flip;
-                        const uint32_t key = pair_canonical(prev, l, &flip);
-                        const uint32_t h = pair_find(pd, key);
-                        if (h != kPairEmpty) pid = 2u * pd.ids[h] + flip;
-                    }
-                    bstep[dst + m + j - 1] = (uint16_t)(pid + pair_bias);   // absolute table entry
-                    if (j >= 2) slots[j - 2] = (unsigned char)triple_slot(prev_pid, pid);
-                    prev_pid = pid;
-                }
-                prev = l;
-            }
-            if (b != (uint32_t)kLongBucket)   // zero the padding behind the slot bytes
-                for (uint32_t j = 2 * (2 * m - 1) + (m > 2 ? m - 2 : 0); j < 2 * row_stride((int)m); ++j)
-                    reinterpret_cast<unsigned char *>(bstep + dst)[j] = 0;
+            write_view_row(bstep, dst, steps + o0, m, b == (uint32_t)kLongBucket, map, pd, n_pairs, pair_bias);
         }
         __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Multiplicity compression of the scoring view.  The verdict of (path, alignment) depends only on the
+// alignment's universe-local content, and it is the same for an alignment and its reverse complement
+// (good <=> T_fw == 0 or T_rc == 0, src/eval.cpp:92-98).  Rows of 1..kMaxBucket steps are therefore
+// merged up to reverse complement in a hash table; a distinct row with multiplicity w is written once
+// per set bit k of w into class k of its length bucket, and the rows of class k count 2^k alignments
+// each (the kernels flush their counters shifted by k).  Real read sets repeat walks at coverage x.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool load_local_row(const uint32_t *__restrict__ off, const uint32_t *__restrict__ steps,
+                                               const uint32_t *__restrict__ map, uint32_t a, uint32_t (&loc)[kMaxBucket],
+                                               uint32_t *m_out) {
+    const uint32_t o0 = __ldg(off + a), m = __ldg(off + a + 1) - o0;
+    *m_out = m;
+    if (m < 1 || m > (uint32_t)kMaxBucket) return false;
+#pragma unroll
+    for (int j = 0; j < kMaxBucket; ++j) {
+        uint32_t l = 0xFFFFFFFFu;
+        if ((uint32_t)j < m) {
+            const uint32_t s = __ldg(steps + o0 + j);
+            l = (__ldg(map + (s >> 1)) << 1) | (s & 1u);
+        }
+        loc[j] = l;
+    }
+    return true;
+}
+// element j of the reverse complement of a row held in registers (static indexing only)
+__device__ __forceinline__ uint32_t rc_elem(const uint32_t (&loc)[kMaxBucket], uint32_t m, int j) {
+    uint32_t v = 0;
+#pragma unroll
+    for (int i = 0; i < kMaxBucket; ++i)
+        if ((uint32_t)i == m - 1u - (uint32_t)j) v = loc[i] ^ 1u;
+    return v;
+}
+
+__global__ void __launch_bounds__(kBlock)
+dedup_insert_kernel(const uint32_t *__restrict__ off, const uint32_t *__restrict__ steps,
+                    const uint32_t *__restrict__ map, uint64_t A, DedupSlot *__restrict__ slots, uint32_t mask) {
+    for (uint64_t a64 = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; a64 < A; a64 += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t a = (uint32_t)a64;
+        uint32_t loc[kMaxBucket], m;
+        if (!load_local_row(off, steps, map, a, loc, &m)) continue;
+        // canonical orientation: the lexicographically smaller of the row and its reverse complement
+        uint32_t rc[kMaxBucket];
+        int cmp = 0;
+#pragma unroll
+        for (int j = 0; j < kMaxBucket; ++j) {
+            rc[j] = (uint32_t)j < m ? rc_elem(loc, m, j) : 0xFFFFFFFFu;
+            if (cmp == 0 && (uint32_t)j < m) cmp = loc[j] < rc[j] ? -1 : (loc[j] > rc[j] ? 1 : 0);
+        }
+        uint32_t h = 0x811C9DC5u ^ m;
+#pragma unroll
+        for (int j = 0; j < kMaxBucket; ++j)
+            if ((uint32_t)j < m) h = (h ^ (cmp <= 0 ? loc[j] : rc[j])) * 0x01000193u;
+        h ^= h >> 15;
+        h *= 0x2C1B3C6Du;
+        h ^= h >> 12;
+        const uint32_t fp = h * 0x9E3779B1u;
+        uint32_t p = h & mask;
+        for (;;) {
+            unsigned long long cur = slots[p].key;
+            if (cur == ~0ull) {
+                const unsigned long long mine = ((unsigned long long)fp << 32) | a;
+                cur = atomicCAS(&slots[p].key, ~0ull, mine);
+                if (cur == ~0ull) cur = mine;
+            }
+            if ((uint32_t)(cur >> 32) == fp) {
+                const uint32_t rep = (uint32_t)cur;
+                bool same = rep == a;
+                if (!same) {
+                    uint32_t other[kMaxBucket], m2;
+                    if (load_local_row(off, steps, map, rep, other, &m2) && m2 == m) {
+                        bool eq_fw = true, eq_rc = true;   // the two rows are equal up to reverse complement
+#pragma unroll
+                        for (int j = 0; j < kMaxBucket; ++j)
+                            if ((uint32_t)j < m) {
+                                eq_fw = eq_fw && other[j] == loc[j];
+                                eq_rc = eq_rc && other[j] == rc[j];
+                            }
+                        same = eq_fw || eq_rc;
+                    }
+                }
+                if (same) {
+                    atomicAdd(&slots[p].w, 1u);
+                    break;
+                }
+            }
+            p = (p + 1) & mask;
+        }
+    }
+}
+
+// class histogram: gcount[m * 32 + k] = distinct rows of length m whose multiplicity has bit k set;
+// gcount[kDedupStats] = distinct rows, [kDedupStats + 1] = rows merged
+__global__ void __launch_bounds__(kBlock)
+dedup_count_kernel(const DedupSlot *__restrict__ slots, uint32_t cap, const uint32_t *__restrict__ off,
+                   uint32_t *__restrict__ gcount) {
+    __shared__ uint32_t s_h[kDedupStats + 2];
+    for (uint32_t i = threadIdx.x; i < kDedupStats + 2; i += blockDim.x) s_h[i] = 0;
+    __syncthreads();
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += gridDim.x * blockDim.x) {
+        const unsigned long long key = slots[i].key;
+        if (key == ~0ull) continue;
+        const uint32_t rep = (uint32_t)key, m = __ldg(off + rep + 1) - __ldg(off + rep);
+        uint32_t w = slots[i].w + 1u;          // the weight word starts at ~0 (memset) and counts inserts
+        atomicAdd(&s_h[kDedupStats], 1u);
+        atomicAdd(&s_h[kDedupStats + 1], w);
+        while (w) {
+            const uint32_t k = (uint32_t)__ffs(w) - 1u;
+            w &= w - 1u;
+            atomicAdd(&s_h[m * 32u + k], 1u);
+        }
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < kDedupStats + 2; i += blockDim.x)
+        if (s_h[i]) atomicAdd(&gcount[i], s_h[i]);
+}
+
+// one view row per (distinct row, set bit k of its multiplicity), class k of bucket m at rows
+// [class_base[m * 32 + k], ...); rshift[sorted row] = k
+__global__ void __launch_bounds__(kBlock)
+dedup_scatter_kernel(const DedupSlot *__restrict__ slots, uint32_t cap, const uint32_t *__restrict__ off,
+                     const uint32_t *__restrict__ steps, const uint32_t *__restrict__ map, const Buckets bk,
+                     uint16_t *__restrict__ bstep, const uint32_t *__restrict__ class_base,
+                     uint32_t *__restrict__ cursors, uint8_t *__restrict__ rshift, const PairDict pd,
+                     uint32_t n_pairs, uint32_t pair_bias) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += gridDim.x * blockDim.x) {
+        const unsigned long long key = slots[i].key;
+        if (key == ~0ull) continue;
+        const uint32_t rep = (uint32_t)key, o0 = __ldg(off + rep), m = __ldg(off + rep + 1) - o0;
+        uint32_t w = slots[i].w + 1u;
+        while (w) {
+            const uint32_t k = (uint32_t)__ffs(w) - 1u;
+            w &= w - 1u;
+            const uint32_t row = class_base[m * 32u + k] + atomicAdd(&cursors[m * 32u + k], 1u);
+            write_view_row(bstep, bk.step_base[m] + row * row_stride((int)m), steps + o0, m, false, map, pd, n_pairs,
+                           pair_bias);
+            rshift[bk.row_start[m] + row] = (uint8_t)k;
+        }
     }
 }
 
@@ -838,6 +991,7 @@ slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
         w.x &= 0x7FFFFFFFu;                 // bit 30 (accumulator set) travels on to the exact list
         const uint32_t p = entry_path(w.x);
         const size_t cb = entry_count_base(a.count_stride, w.x);
+        const uint32_t wt = a.rshift ? 1u << a.rshift[w.y] : 1u;   // alignments this view row stands for
         const RowRef r = locate_row(a.bk, w.y);
         const int m = (int)r.m;
         const uint32_t po = a.poff[p];
@@ -847,13 +1001,13 @@ slow_worklist_kernel(const ScoreArgs a, const uint2 *__restrict__ slow,
         // it, and for a start-overhang suspect it finds nothing at the cost of one table read
         const int v = slow_verdict(a.pstep + po, a.pnext + po, n, tab, r.ptr, m, true);
         if (v == kExact) {
-            atomicSub(&a.counts[cb + guess], 1u);   // the exact DP adds the right one
+            atomicSub(&a.counts[cb + guess], wt);   // the exact DP adds the right one
             const uint32_t k = atomicAdd(a.work_count, 1u);
             if (k < a.work_cap) a.work[k] = w;
             else atomicOr(a.work_count + 1, 1u);
         } else if ((v == kGood ? 1u : 0u) != guess) {          // correct the rare wrong guess
-            atomicSub(&a.counts[cb + guess], 1u);
-            atomicAdd(&a.counts[cb + (guess ^ 1u)], 1u);
+            atomicSub(&a.counts[cb + guess], wt);
+            atomicAdd(&a.counts[cb + (guess ^ 1u)], wt);
         }
     }
 }
@@ -919,7 +1073,8 @@ exact_worklist_kernel(const ScoreArgs a) {
             exact_both(a.pstep + po, n, a.ptab + (size_t)p * a.tab_stride, a.pnext + po, r.ptr, (int)r.m, false,
                        &tf, &tr);
             const bool good = (tf == 0) || (tr == 0);
-            atomicAdd(&a.counts[entry_count_base(a.count_stride, it.x) + (good ? 1 : 0)], 1u);
+            atomicAdd(&a.counts[entry_count_base(a.count_stride, it.x) + (good ? 1 : 0)],
+                      a.rshift ? 1u << a.rshift[it.y] : 1u);
         }
         __syncthreads();
     }
@@ -1246,12 +1401,32 @@ void launch_pair_assign(const PairDict &pd, cudaStream_t st) {
 void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local,
                            uint64_t A, const Buckets &bk, uint16_t *bstep, uint2 *ldesc,
                            uint32_t *perm, uint32_t *cursors, const PairDict &pd, uint32_t n_pairs,
-                           uint32_t pair_bias, cudaStream_t st) {
+                           uint32_t pair_bias, cudaStream_t st, bool only_long) {
     if (A == 0) return;
     uint64_t blocks = (A + kBlock - 1) / kBlock;
     if (blocks > 148 * 8) blocks = 148 * 8;
     bucket_scatter_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(off, steps, node2local, A, bk, bstep,
-                                                               ldesc, perm, cursors, pd, n_pairs, pair_bias);
+                                                               ldesc, perm, cursors, pd, n_pairs, pair_bias, only_long);
+}
+
+void launch_dedup_insert(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local, uint64_t A,
+                         DedupSlot *slots, uint32_t cap, cudaStream_t st) {
+    if (A == 0) return;
+    uint64_t blocks = (A + kBlock - 1) / kBlock;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    dedup_insert_kernel<<<(unsigned)blocks, kBlock, 0, st>>>(off, steps, node2local, A, slots, cap - 1);
+}
+
+void launch_dedup_count(const DedupSlot *slots, uint32_t cap, const uint32_t *off, uint32_t *gcount, cudaStream_t st) {
+    dedup_count_kernel<<<std::min<uint32_t>((cap + kBlock - 1) / kBlock, 148 * 8), kBlock, 0, st>>>(slots, cap, off, gcount);
+}
+
+void launch_dedup_scatter(const DedupSlot *slots, uint32_t cap, const uint32_t *off, const uint32_t *steps,
+                          const uint32_t *node2local, const Buckets &bk, uint16_t *bstep, const uint32_t *class_base,
+                          uint32_t *cursors, uint8_t *rshift, const PairDict &pd, uint32_t n_pairs, uint32_t pair_bias,
+                          cudaStream_t st) {
+    dedup_scatter_kernel<<<std::min<uint32_t>((cap + kBlock - 1) / kBlock, 148 * 16), kBlock, 0, st>>>(
+        slots, cap, off, steps, node2local, bk, bstep, class_base, cursors, rshift, pd, n_pairs, pair_bias);
 }
 
 __global__ void status_flag_kernel(uint32_t *err, const uint32_t *wc, uint32_t *out) {

@@ -93,6 +93,7 @@ struct ScoreArgs {
     // count record of path p, accumulator set s (list entries carry s in bit 30 of the path field):
     // counts[count_stride * p + 2 * s + {0: bad, 1: good}]; plain batches: stride 2, one set
     uint32_t count_stride = 2;
+    const uint8_t *rshift = nullptr;   // deduplicated view: sorted row -> k, the row counts 2^k alignments
     uint32_t *err = nullptr;  // bit 2: a row of more than GFE_MAX_STEPS steps passed the id filter (reference: UB)
     uint32_t path_tag = 0;    // OR-ed into the path field of the entries score_paths_kernel queues (set << 30)
 };
@@ -120,6 +121,14 @@ struct MaskGeom {
     uint32_t n_pairs;         // C
 };
 
+// Units [unit_start, next group's unit_start) score rows [row0, row0 + nrows) of the matrix of bucket m;
+// every row of the group counts 2^shift alignments (shift > 0 only in the deduplicated view).
+constexpr int kMaxGroups = 512;
+struct __align__(16) UnitGroup {
+    uint32_t unit_start, row0, nrows;
+    uint16_t m, shift;
+};
+
 struct BitsetArgs {
     Buckets bk;
     MaskGeom mg;
@@ -129,7 +138,8 @@ struct BitsetArgs {
     int filter;
     uint32_t *counts;         // P x {bad, good}
     uint32_t unit_rows;       // rows per scheduling unit (multiple of 8 * 32/W, set per launch)
-    uint32_t unit_start[kMaxBucket + 2];   // first unit of buckets 1..kMaxBucket; [kMaxBucket+1] = total
+    const UnitGroup *groups;  // scheduling groups in ascending unit order (one per length, or per length and class)
+    uint32_t n_groups, n_units;
     uint32_t *unit_ctr;       // per chunk: next unit (dynamic scheduling), zeroed per launch
     uint2 *slow;              // (path, sorted row) pairs the bitsets cannot settle
     uint32_t *work_count;     // [0..1] exact list count/overflow, [2..3] slow list count/overflow
@@ -252,7 +262,21 @@ void launch_pair_assign(const PairDict &pd, cudaStream_t st);
 void launch_bucket_scatter(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local,
                            uint64_t A, const Buckets &bk, uint16_t *bstep, uint2 *ldesc,
                            uint32_t *perm, uint32_t *cursors, const PairDict &pd, uint32_t n_pairs,
-                           uint32_t pair_bias, cudaStream_t st);
+                           uint32_t pair_bias, cudaStream_t st, bool only_long = false);
+// multiplicity compression (kernels.cu): distinct rows up to reverse complement, class k = bit k of the
+// multiplicity; gcount has kDedupStats + 2 words (zeroed by the caller)
+struct DedupSlot {
+    unsigned long long key;   // fingerprint << 32 | representative alignment; ~0 = empty
+    uint32_t w, pad;          // multiplicity
+};
+constexpr uint32_t kDedupStats = (kMaxBucket + 1) * 32;
+void launch_dedup_insert(const uint32_t *off, const uint32_t *steps, const uint32_t *node2local, uint64_t A,
+                         DedupSlot *slots, uint32_t cap /* power of two */, cudaStream_t st);
+void launch_dedup_count(const DedupSlot *slots, uint32_t cap, const uint32_t *off, uint32_t *gcount, cudaStream_t st);
+void launch_dedup_scatter(const DedupSlot *slots, uint32_t cap, const uint32_t *off, const uint32_t *steps,
+                          const uint32_t *node2local, const Buckets &bk, uint16_t *bstep, const uint32_t *class_base,
+                          uint32_t *cursors, uint8_t *rshift, const PairDict &pd, uint32_t n_pairs, uint32_t pair_bias,
+                          cudaStream_t st);
 
 // mask-table geometry as a function of the universe size L (entries of W words): BT first (so its
 // byte offsets need no base), then the node plane, LM, and the pair masks on an even entry

@@ -311,6 +311,15 @@ typedef struct gfe_counters {
     uint64_t slow_pairs;          // pairs the bitset kernel handed to the second-look kernel
 } gfe_counters;
 int gfe_get_counters(const gfe_engine *e, gfe_counters *out);
+/* Multiplicity compression of the scoring view (on by default; GFE_DEDUP=0 or enabled = 0 turns it off;
+ * takes effect at the next gfe_set_universe).  The verdict of evaluatePath's inner loop
+ * (reference src/eval.cpp:80-99) depends only on the alignment's oriented node list and is the same
+ * for an alignment and its reverse complement, so alignments with equal walks are scored once and
+ * counted with their multiplicity — counts stay bit-exact.  stats: rows of 1..16 steps, distinct
+ * walks among them, rows of the compressed view (one per set bit of each multiplicity), and whether
+ * full scans (gfe_score_paths*) currently read it (kept only when it saves a quarter of the rows). */
+int gfe_set_dedup(gfe_engine *e, int enabled);
+int gfe_get_dedup_stats(const gfe_engine *e, uint64_t *rows, uint64_t *distinct, uint64_t *view_rows, int *in_use);
 /* After the *_device entry points (which do not synchronise): waits for the device and reports the
  * flags of ALL batches enqueued since the previous report (they are sticky across batches and are
  * cleared by the report) — bit0: a candidate path named a node outside the universe, bit1: a

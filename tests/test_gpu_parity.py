@@ -476,3 +476,51 @@ def test_device_status_is_sticky_across_batches_and_cleared_by_the_report(engine
     engine.score_paths_device(d_po.data_ptr(), d_ps.data_ptr(), 8, int(ps.size), d_counts.data_ptr(), filter=True)
     assert engine.device_status() == 0
     assert np.array_equal(d_counts.cpu().numpy().view(np.uint32).reshape(8, 2), engine.score_paths(po, ps, True))
+
+
+def test_multiplicity_compressed_view_equals_plain_view(engine, oracle):
+    """Full scans read the deduplicated view (distinct walks up to reverse complement, weights 2^k) by
+    default; the counts equal those of the plain view and of the oracle, with and without the filter,
+    incl. a table where one walk repeats 70 000 times (classes up to k = 16) and the second-look /
+    exact lists (tiny alphabet: heavy multiplicities meet the exact DP)."""
+    w = synth.make_workload("cfg3", A=200000)
+    t = w.tangle
+    nodes, _, _ = synth.node_table(t)
+    po, ps = synth.candidate_paths(t, 300, seed=12)
+    rep = np.tile(w.steps[w.offsets[5]:w.offsets[6]], 70000)
+    m5 = int(w.offsets[6] - w.offsets[5])
+    off = np.concatenate([w.offsets.astype(np.int64), w.offsets[-1] + m5 * np.arange(1, 70001)]).astype(np.uint32)
+    st = np.concatenate([w.steps, rep]).astype(np.uint32)
+    engine.set_alignments(off, st, t.n_nodes)
+    res = {}
+    for on in (True, False):
+        engine.set_dedup(on)
+        engine.set_universe(nodes)
+        s = engine.dedup_stats()
+        assert s["in_use"] == on
+        if on:
+            assert s["rows"] == off.size - 1 and s["distinct_walks"] < s["rows"] // 3 and s["view_rows"] < s["rows"] // 2
+        res[on] = [engine.score_paths(po, ps, filter=f) for f in (True, False)]
+    engine.set_dedup(True)
+    for k in range(2):
+        assert np.array_equal(res[True][k], res[False][k])
+    pick = np.linspace(0, 299, 24).astype(int)
+    so = np.zeros(pick.size + 1, dtype=np.uint32)
+    so[1:] = np.cumsum([po[p + 1] - po[p] for p in pick])
+    ss = np.concatenate([ps[po[p]:po[p + 1]] for p in pick])
+    assert np.array_equal(res[True][0][pick], oracle.evaluate_paths(so, ss, off, st, True, 8))
+    assert np.array_equal(res[True][1][pick], oracle.evaluate_paths(so, ss, off, st, False, 8))
+    # tiny alphabet
+    rng = np.random.default_rng(2)
+    off2, st2 = _rand_csr(rng, 30000, 4, [1, 2, 3, 4, 5, 7, 16, 17, 20])
+    P = 48
+    plen = rng.integers(1, 30, size=P)
+    po2 = np.zeros(P + 1, dtype=np.uint32)
+    po2[1:] = np.cumsum(plen)
+    ps2 = (rng.integers(0, 4, size=int(po2[-1])) * 2 + rng.integers(0, 2, size=int(po2[-1]))).astype(np.uint32)
+    engine.set_alignments(off2, st2, 4)
+    engine.set_universe(np.arange(4, dtype=np.uint32))
+    assert engine.dedup_stats()["in_use"]
+    for filt in (True, False):
+        assert np.array_equal(engine.score_paths(po2, ps2, filter=filt),
+                              oracle.evaluate_paths(po2, ps2, off2, st2, filt, 8)), filt
