@@ -113,38 +113,30 @@ struct Planes {
     }
 };
 
-// Group of a unit: the last group whose first unit is <= unit (s_gstart: shared copy of the groups'
-// unit_start, ascending).  Warp-uniform.
-__device__ __forceinline__ uint32_t unit_group(const uint32_t *s_gstart, uint32_t n_groups, uint32_t unit) {
-    uint32_t lo = 0, hi = n_groups;           // invariant: s_gstart[lo] <= unit < s_gstart[hi] (hi == n: +inf)
-    while (hi - lo > 1) {
-        const uint32_t mid = (lo + hi) >> 1;
-        if (s_gstart[mid] <= unit) lo = mid;
-        else hi = mid;
-    }
-    return lo;
+// Plain view (one group per row length): bucket of a unit by one vote — lane k compares with the
+// first unit of bucket k (s_ustart: shared copy of unit_start, 0xFFFFFFFF beyond kMaxBucket).
+__device__ __forceinline__ int unit_bucket(const uint32_t *s_ustart, uint32_t unit, int lane) {
+    return __popc(__ballot_sync(0xFFFFFFFFu, unit >= s_ustart[lane])) - 1;   // entries 0 and 1 are 0
 }
 
-// first row / row count / bytes of a unit; used to prefetch the next unit's rows into L1
-__device__ __forceinline__ void prefetch_unit(const BitsetArgs &a, uint32_t unit, const UnitGroup &g, int lane) {
-    const uint32_t row0 = g.row0 + (unit - g.unit_start) * a.unit_rows;
-    const uint32_t nrows = min(a.unit_rows, g.row0 + g.nrows - row0);
-    const uint32_t rs = row_stride(g.m);
-    const char *p = reinterpret_cast<const char *>(a.bk.bstep + a.bk.step_base[g.m] + (size_t)row0 * rs);
+// Class-sorted view: scheduling groups live in shared memory as uint4 {unit_start, row0, nrows, m | shift << 16}.  A warp
+// claims units in DEcreasing order, so the group of its next unit is found by walking down from the
+// group of the current one (usually zero or one step).  Warp-uniform.
+__device__ __forceinline__ uint32_t group_of(const uint4 *s_groups, uint32_t gi, uint32_t unit) {
+    while (gi > 0 && s_groups[gi].x > unit) --gi;
+    return gi;
+}
+
+// the rows of a unit into L1 ahead of time
+__device__ __forceinline__ void prefetch_unit(const BitsetArgs &a, uint32_t unit, const uint4 g, int lane) {
+    const uint32_t m = g.w & 0xFFFFu;
+    const uint32_t row0 = g.y + (unit - g.x) * a.unit_rows;
+    const uint32_t nrows = min(a.unit_rows, g.y + g.z - row0);
+    const uint32_t rs = row_stride((int)m);
+    const char *p = reinterpret_cast<const char *>(a.bk.bstep + a.bk.step_base[m] + (size_t)row0 * rs);
     const uint32_t bytes = nrows * rs * 2u;
     for (uint32_t o = (uint32_t)lane * 128u; o < bytes + 127u; o += 32u * 128u)
         asm volatile("prefetch.global.L1 [%0];" ::"l"(p + min(o, bytes - 1u)));
-}
-
-__device__ __forceinline__ UnitGroup load_group(const UnitGroup *g) {
-    const uint4 v = __ldg(reinterpret_cast<const uint4 *>(g));
-    UnitGroup r;
-    r.unit_start = v.x;
-    r.row0 = v.y;
-    r.nrows = v.z;
-    r.m = (uint16_t)(v.w & 0xFFFFu);
-    r.shift = (uint16_t)(v.w >> 16);
-    return r;
 }
 
 // Push the set bits of the eight masks of one warp step (paths word_base .. word_base+31, rows
@@ -438,7 +430,9 @@ __device__ __forceinline__ void score_unit(const UnitCtx &c, const uint16_t *__r
     }
 }
 
-template <int W>
+// kGroups = false: the plain view, units mapped to length buckets arithmetically (unit_start[]);
+// kGroups = true:  the multiplicity-compressed view, units mapped through the group table (m, class)
+template <int W, bool kGroups>
 __global__ void __launch_bounds__(kBitThreads, 1)
 score_bitset_kernel(const BitsetArgs a) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -450,9 +444,15 @@ score_bitset_kernel(const BitsetArgs a) {
     const uint32_t chunk = blockIdx.y;
     const uint32_t p_base = chunk * 32u * W;
     const int lane = threadIdx.x & 31;
-    __shared__ uint32_t s_gstart[kMaxGroups];
+    __shared__ uint4 s_groups[kGroups ? kMaxGroups : 1];
+    __shared__ uint32_t s_ustart[32];
     if (threadIdx.x == 0) mbar_init(s_bar, 1);
-    for (uint32_t i = threadIdx.x; i < a.n_groups; i += blockDim.x) s_gstart[i] = a.groups[i].unit_start;
+    if (kGroups) {
+        for (uint32_t i = threadIdx.x; i < a.n_groups; i += blockDim.x)
+            s_groups[i] = __ldg(reinterpret_cast<const uint4 *>(a.groups) + i);
+    } else if (threadIdx.x < 32) {
+        s_ustart[threadIdx.x] = threadIdx.x <= kMaxBucket ? a.unit_start[threadIdx.x] : 0xFFFFFFFFu;
+    }
     for (uint32_t i = threadIdx.x; i < 64u * W; i += blockDim.x) s_cnt[i] = 0;
     __syncthreads();
     pdl_wait();      // build_tables' mask tables (everything above only touched this CTA's shared memory)
@@ -525,25 +525,41 @@ score_bitset_kernel(const BitsetArgs a) {
         pending = atomicAdd(a.unit_ctr + chunk, 1u);
     }
     next = __shfl_sync(0xFFFFFFFFu, next, 0);
-    UnitGroup next_g = load_group(a.groups + unit_group(s_gstart, a.n_groups, n_units - 1u - min(next, n_units - 1u)));
+    uint32_t next_gi = 0;      // kGroups: group index of `next`; else: its bucket
+    if (kGroups) next_gi = a.n_groups ? group_of(s_groups, a.n_groups - 1u, n_units - 1u - min(next, n_units - 1u)) : 0u;
+    else next_gi = (uint32_t)unit_bucket(s_ustart, n_units - 1u - min(next, n_units - 1u), lane);
     for (;;) {
         if (next >= n_units) break;
         const uint32_t unit = n_units - 1u - next;
-        const UnitGroup gr = next_g;
-        const int b = gr.m;
+        uint32_t row0, unrows;
+        int b;
+        if (kGroups) {
+            const uint4 gr = s_groups[next_gi];          // {unit_start, row0, nrows, m | shift << 16}
+            b = (int)(gr.w & 0xFFFFu);
+            row0 = gr.y + (unit - gr.x) * a.unit_rows;
+            unrows = min(a.unit_rows, gr.y + gr.z - row0);
+            if ((gr.w >> 16) != cur_shift) {   // another multiplicity class: settle the counters first
+                flush();
+                cur_shift = gr.w >> 16;
+            }
+        } else {
+            b = (int)next_gi;
+            row0 = (unit - a.unit_start[b]) * a.unit_rows;
+            unrows = min(a.unit_rows, a.bk.count[b] - row0);
+        }
         next = __shfl_sync(0xFFFFFFFFu, pending, 0);
         if (lane == 0) pending = atomicAdd(a.unit_ctr + chunk, 1u);
         if (next < n_units) {
-            next_g = load_group(a.groups + unit_group(s_gstart, a.n_groups, n_units - 1u - next));
-            prefetch_unit(a, n_units - 1u - next, next_g, lane);
-        }
-        if (gr.shift != cur_shift) {       // another multiplicity class: settle the counters first
-            flush();
-            cur_shift = gr.shift;
+            if (kGroups) {
+                next_gi = group_of(s_groups, next_gi, n_units - 1u - next);
+                prefetch_unit(a, n_units - 1u - next, s_groups[next_gi], lane);
+            } else {
+                next_gi = (uint32_t)unit_bucket(s_ustart, n_units - 1u - next, lane);
+                prefetch_unit(a, n_units - 1u - next,
+                              make_uint4(a.unit_start[next_gi], 0u, a.bk.count[next_gi], next_gi), lane);
+            }
         }
         // rows [row0, row0 + unrows) of bucket b's dense matrix
-        const uint32_t row0 = gr.row0 + (unit - gr.unit_start) * a.unit_rows;
-        const uint32_t unrows = min(a.unit_rows, gr.row0 + gr.nrows - row0);
         const uint16_t *ubase = a.bk.bstep + a.bk.step_base[b] + (size_t)row0 * row_stride(b);
         const uint32_t usorted = a.bk.row_start[b] + row0;
         const uint32_t ulm = tab[(a.mg.lm_base + b) * W];
@@ -720,12 +736,16 @@ void launch_w(const BitsetArgs &a, int sm_count, cudaStream_t st) {
     const uint32_t n_units = a.n_units;
     const uint32_t max_gx = (n_units + (kBitThreads / 32) - 1) / (kBitThreads / 32);
     if (gx > max_gx) gx = max_gx ? max_gx : 1;
-    launch_pdl(1, score_bitset_kernel<W>, dim3(gx, chunks), dim3(kBitThreads), smem, st, a);
+    if (a.groups) launch_pdl(1, score_bitset_kernel<W, true>, dim3(gx, chunks), dim3(kBitThreads), smem, st, a);
+    else launch_pdl(1, score_bitset_kernel<W, false>, dim3(gx, chunks), dim3(kBitThreads), smem, st, a);
 }
 
 template <int W>
 cudaError_t configure_w() {
-    return cudaFuncSetAttribute(score_bitset_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    const cudaError_t e = cudaFuncSetAttribute(score_bitset_kernel<W, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               (int)(kBitsetSmemBudget + 1024));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(score_bitset_kernel<W, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)(kBitsetSmemBudget + 1024));
 }
 

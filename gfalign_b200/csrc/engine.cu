@@ -287,7 +287,9 @@ static int build_group_tables(gfe_engine *e, int view, const uint32_t *gcount, u
         const uint32_t W = 1u << wi;
         const uint32_t step = 4u * (32u / W);
         const uint64_t warps = (uint64_t)e->sm_count * (kBitThreads / 32);
-        const uint64_t want = rows_total / (8 * warps) / step * step;
+        // plain view: ~8 units per warp (dynamic balance); class-sorted view: ~2 larger units per warp, since
+        // every change of class costs a warp a counter flush
+        const uint64_t want = rows_total / ((view ? 2 : 8) * warps) / step * step;
         const uint32_t ur = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(want, step), 8 * step);
         uint32_t unit = 0, ng = 0;
         for (int m = 1; m <= kMaxBucket; ++m) {
@@ -682,9 +684,17 @@ static int enqueue_score(gfe_engine *e, const uint32_t *d_poff, const uint16_t *
             int wi = 0;
             while ((1u << wi) < W) ++wi;
             b.unit_rows = e->unit_rows[view][wi];
-            b.groups = e->d_groups[view].ptr + (size_t)wi * kMaxGroups;
+            b.groups = view ? e->d_groups[view].ptr + (size_t)wi * kMaxGroups : nullptr;
             b.n_groups = e->n_groups[view][wi];
             b.n_units = e->n_units[view][wi];
+            uint32_t unit = 0;       // plain view: the buckets' first units (the kernel maps units arithmetically)
+            b.unit_start[0] = 0;
+            for (int k = 1; k <= kMaxBucket; ++k) {
+                b.unit_start[k] = unit;
+                unit += (vbk.count[k] + b.unit_rows - 1) / b.unit_rows;
+            }
+            b.unit_start[kMaxBucket + 1] = unit;
+            if (!view) b.n_units = unit;
         }
         if (e->timing) {
             TRY(next_event_pair(e));

@@ -138,7 +138,8 @@ struct BitsetArgs {
     int filter;
     uint32_t *counts;         // P x {bad, good}
     uint32_t unit_rows;       // rows per scheduling unit (multiple of 8 * 32/W, set per launch)
-    const UnitGroup *groups;  // scheduling groups in ascending unit order (one per length, or per length and class)
+    uint32_t unit_start[kMaxBucket + 2];   // plain view: first unit of buckets 1..kMaxBucket; [kMaxBucket+1] = total
+    const UnitGroup *groups;  // class-sorted view: groups (length, class) in ascending unit order; else nullptr
     uint32_t n_groups, n_units;
     uint32_t *unit_ctr;       // per chunk: next unit (dynamic scheduling), zeroed per launch
     uint2 *slow;              // (path, sorted row) pairs the bitsets cannot settle
