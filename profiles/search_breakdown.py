@@ -5,7 +5,7 @@ w = synth.make_workload("cfg3", A=1_000_000)
 t = w.tangle
 nodes, counts, node_count = synth.node_table(t)
 args = (t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source, t.destination, nodes, counts, node_count)
-for width, roots in ((4096,256),(8192,512),(4096,512),(2048,256)):
+for width, roots in ((4096,256),):
     os.environ["GFE_SPEC_WIDTH"]=str(width); os.environ["GFE_SPEC_ROOTS"]=str(roots)
     eng = capi.Engine(0)
     eng.set_alignments(w.offsets, w.steps, t.n_nodes)
