@@ -352,7 +352,7 @@ struct Driver {
     std::priority_queue<std::pair<int32_t, uint32_t>, std::vector<std::pair<int32_t, uint32_t>>, FrontCmp> front;
     std::vector<std::pair<int32_t, uint32_t>> front_keep;
     // candidates per batch / speculation roots per batch / live front entries examined per batch: measured
-    // optimum on cfg3 (profiles/r02_search_sweep.txt): many roots with a small subtree each
+    // optimum on cfg3 (profiles/r02_search_sweep_effkey.txt): many roots with a small subtree each
     uint32_t spec_width = 4096, spec_roots = 256, spec_scan = 4096;
     std::vector<uint32_t> t_base_off, t_base_steps, t_item_base, t_suf_off, t_suf_steps, t_items, t_parents;
     std::vector<uint8_t> t_mode;
