@@ -684,12 +684,19 @@ score_incr_kernel(const IncrArgs a) {
         rows_acc = 0;
     };
 
-    // units are claimed in ascending order (one atomic each), so a warp sees pass 0 before pass 1
+    // units are claimed in ascending order, so a warp sees pass 0 before pass 1; one claim is always in
+    // flight (lane 0's atomic for the unit after next), so its round trip hides behind a unit of work
+    uint32_t next = 0, pending = 0;
+    if (lane == 0) {
+        next = atomicAdd(a.unit_ctr + chunk, 1u);
+        pending = atomicAdd(a.unit_ctr + chunk, 1u);
+    }
+    next = __shfl_sync(0xFFFFFFFFu, next, 0);
     for (;;) {
-        uint32_t unit = 0;
-        if (lane == 0) unit = atomicAdd(a.unit_ctr + chunk, 1u);
-        unit = __shfl_sync(0xFFFFFFFFu, unit, 0);
+        const uint32_t unit = next;
         if (unit >= n_units) break;
+        next = __shfl_sync(0xFFFFFFFFu, pending, 0);
+        if (lane == 0) pending = atomicAdd(a.unit_ctr + chunk, 1u);
         const int g = __popc(__ballot_sync(0xFFFFFFFFu, unit >= s_ustart[lane])) - 1;
         const uint32_t set = (uint32_t)g >> 4;
         const int m = (g & 15) + 1;

@@ -450,11 +450,7 @@ struct Driver {
     }
 
     int score_children_tree(uint32_t x) {
-        if (T[x].kids_scored && T[x].expanded) {
-            bool ok = true;
-            for (uint32_t c = 0; c < T[x].child_count; ++c) ok = ok && T[T[x].child_begin + c].scored;
-            if (ok) return GFE_OK;
-        }
+        if (T[x].kids_scored) return GFE_OK;     // set only once every child carries its counts
         t_base_off.assign(1, 0);
         t_base_steps.clear(); t_item_base.clear(); t_suf_off.assign(1, 0); t_suf_steps.clear();
         t_items.clear(); t_parents.clear(); t_mode.clear(); t_kids.clear();

@@ -81,3 +81,25 @@ def test_overlong_alignment_is_dropped_by_the_filter_and_flagged_when_it_passes(
     engine.set_alignments(w.offsets, w.steps, t.n_nodes)      # and the engine is usable afterwards
     engine.set_universe(nodes)
     assert np.array_equal(engine.score_paths(po, ps, filter=True), got)
+
+
+def test_search_without_pair_dictionary_falls_back_to_full_scans(engine):
+    """A universe too large for the bitset tables has no inverted-index path either: gfe_search must notice
+    (GFE_ERR_STATE from the incremental entry) and finish on full scans with the same rows."""
+    t = synth.make_tangle(20000, 8000, seed=41, minus_frac=0.05, count2_frac=0.05)
+    off, st = synth.random_walk_alignments(t.n_nodes, t.edge_from, t.edge_to, 60000, *synth.HIFI_LENGTHS, seed=42)
+    nodes, counts, node_count = synth.node_table(t)
+    engine.set_alignments(off, st, t.n_nodes)
+
+    def run():
+        rows, stats = engine.search(t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source, t.destination,
+                                    nodes, counts, node_count, max_steps=400, return_all_paths=True)
+        return [r.columns(t.names) for r in rows], stats["evaluations"]
+
+    got = run()
+    os.environ["GFE_SEARCH_FULLSCAN"] = "1"
+    try:
+        want = run()
+    finally:
+        del os.environ["GFE_SEARCH_FULLSCAN"]
+    assert got == want and got[1] > 400
