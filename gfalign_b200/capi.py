@@ -88,6 +88,7 @@ EXPORTS = [
     "gfe_exchange_create", "gfe_exchange_destroy", "gfe_score_paths_sharded", "gfe_search_sharded",
     "gfe_score_paths_incremental", "gfe_score_paths_incremental_sharded", "gfe_exchange_set_batch_sharding",
     "gfe_last_aux_kernel_ms", "gfe_set_dedup", "gfe_get_dedup_stats",
+    "gfe_filter_alignments_static",
 ]
 
 PEER_MAX = 16      # GFE_PEER_MAX
@@ -195,6 +196,9 @@ def load_library() -> C.CDLL:
     lib.gfe_trace_pairs.argtypes = [C.c_void_p, _u32p, C.c_uint32, C.c_uint64, C.c_uint32, _u8p, _u8p,
                                     C.c_uint64, C.POINTER(C.c_uint64), _u32p, _i32p]
     lib.gfe_filter_alignments.argtypes = [C.c_void_p, _u32p, C.c_uint32, C.c_int32, _u8p]
+    lib.gfe_filter_alignments_static.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32,
+                                                 C.c_void_p, C.c_uint32, C.c_int32, C.c_void_p, C.c_void_p,
+                                                 C.c_char_p, C.c_size_t]
     lib.gfe_text_open.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.POINTER(C.c_void_p), C.c_char_p,
                                   C.c_size_t]
     lib.gfe_text_close.argtypes = [C.c_void_p]

@@ -154,6 +154,32 @@ int gfe_trace_pairs(gfe_engine *e, const uint32_t *path_steps, uint32_t n, uint6
 int gfe_filter_alignments(gfe_engine *e, const uint32_t *nodes, uint32_t n, int32_t min_nodes,
                           uint8_t *keep /* A */);
 
+/* ---- filter mode without device allocation ------------------------------------------------------------
+ * No counterpart in the reference (it has no device memory to manage); same result as
+ * gfe_filter_alignments.  For hosts where this library must not call the CUDA allocator: processes in
+ * which a framework's caching allocator or a memory manager has already claimed nearly all of HBM (a
+ * cudaMalloc from here would fail or break their accounting), and services with other streams in
+ * flight on the GPU, which cudaMalloc / cudaFree would stall.  Such a caller holds the table in device
+ * memory of its own and passes everything as DEVICE pointers on the CURRENT CUDA device:
+ *   d_offsets[A + 1], d_steps[total_steps]  the alignment CSR (total_steps == d_offsets[A]);
+ *   d_nodes[n]   the node set (ids >= n_nodes are ignored; gfe_filter_alignments rejects them);
+ *   d_keep[A]    output, 1 = every step names a node of the set and the row has >= min_nodes steps.
+ * The work is enqueued on `cuda_stream` (a cudaStream_t; NULL = default stream) and NOT waited for.
+ * No cudaMalloc / cudaFree / allocating routine is called: the filter's two bitmaps live in a fixed
+ * 8.125 MiB array inside the library image, resident on every GPU that loads the library until the
+ * process ends.  Hence the limits below (GFE_ERR_LIMIT beyond them, text in err).
+ * One array per GPU, shared by all calls and never cleared between them except where a call needs
+ * zeros: calls that overlap on the same GPU (two streams) race and return garbage — order them.
+ * The first call on each device looks up the array's device address and the SM count (it may load the
+ * library's kernels onto that GPU); make it at start-up, before any stream capture.
+ * err (may be NULL) receives the message of a failed call. */
+#define GFE_STATIC_FILTER_MAX_STEPS (1u << 26)   /* 67 108 864 steps in the table */
+#define GFE_STATIC_FILTER_MAX_NODES (1u << 20)   /* size of the dense node-id space */
+int gfe_filter_alignments_static(const uint32_t *d_offsets, const uint32_t *d_steps, uint64_t A,
+                                 uint64_t total_steps, uint32_t n_nodes, const uint32_t *d_nodes,
+                                 uint32_t n, int32_t min_nodes, uint8_t *d_keep, void *cuda_stream,
+                                 char *err, size_t err_len);
+
 /* ---- evalGFA: per-edge read support -------------------------------------------------------------
  * Replaces InAlignments::buildEdgeGraph (reference src/alignments.cpp:353-403) + the per-edge
  * lookup of evalGFA (src/eval.cpp:42-60).  edges are the graph's L lines in file order as
