@@ -844,6 +844,17 @@ static int score_paths_impl(gfe_engine *e, gfe_exchange *x, const uint32_t *path
         set_error(e, "gfe_score_paths_sharded: a peer never reached epoch %u (GFE_PEER_TIMEOUT_MS)", x->epoch);
         return GFE_ERR_CUDA;
     }
+    if (x && (any_flags >> 8) && !e->h_counts.ptr[kWorkCounters]) {
+        // another rank's shard raised an error this rank's did not (flag_word_kernel: byte 2 = over-long
+        // alignment, byte 1 = bad step): return the same class on every rank, nobody retries alone
+        if ((any_flags >> 16) & 0xFFu) {
+            set_error(e, "gfe_score_paths_sharded: on another rank's shard an alignment of more than %u steps passes "
+                         "the id filter of a candidate path", GFE_MAX_STEPS);
+            return GFE_ERR_LIMIT;
+        }
+        set_error(e, "gfe_score_paths_sharded: another rank saw a step outside the universe");
+        return GFE_ERR_ARG;
+    }
     if (x && any_flags && !e->h_counts.ptr[kWorkCounters]) {
         // some rank overflowed a list (or all saw a bad step, handled below): every rank repeats the
         // batch; the ranks that overflowed grow their lists first
@@ -952,6 +963,43 @@ int gfe_score_paths_sharded(gfe_engine *e, gfe_exchange *x, const uint32_t *path
 
 }  // extern "C"
 
+// Internal to the library (C++ linkage, used by search.cpp): do ALL ranks of the exchange have the
+// incremental scoring path for their current universe?  Whether a rank has a pair dictionary depends on
+// its own shard (distinct pairs vs the dictionary capacity, GFE_FORCE_LEGACY), and the incremental and
+// the full-scan entries exchange records of different shapes under the same epoch counter — so the
+// choice between them must be the same on every rank.  One word per rank (1 = "I cannot") summed by the
+// peer kernel; collective: every rank calls it at the same point (start of gfe_search_sharded).
+int gfe_internal_incremental_consensus(gfe_engine *e, gfe_exchange *x, int *all_have) {
+    if (!e || !x || !all_have) return GFE_ERR_ARG;
+    if (!e->have_alignments || !e->have_universe) {
+        set_error(e, "gfe_search_sharded: alignments and universe must be set first");
+        return GFE_ERR_STATE;
+    }
+    if (x->n_cap < 1) return GFE_ERR_ARG;
+    TRY(ensure_pinned(e, e->h_counts, 2));
+    TRY(ensure_dev(e, e->d_counts, 2));
+    cudaStream_t st = e->stream;
+    uint32_t *d_mine = reinterpret_cast<uint32_t *>(x->bases[x->rank]) + (size_t)x->n_cap * ((x->epoch + 1) & 1u);
+    e->h_counts.ptr[0] = (e->have_dict && !e->force_legacy) ? 0u : 1u;
+    CUDA_TRY(e, cudaMemcpyAsync(d_mine, e->h_counts.ptr, sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    x->epoch += 1;
+    const int prc = gfe_peer_sum_u32(x->bases, x->world, x->rank, x->n_cap, 1, x->epoch, e->d_counts.ptr, st);
+    if (prc != GFE_OK) {
+        set_error(e, "gfe_search_sharded: peer sum launch failed");
+        return prc;
+    }
+    e->kernel_launches += 1;
+    CUDA_TRY(e, cudaMemcpyAsync(e->h_counts.ptr + 1, e->d_counts.ptr, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(e, cudaStreamSynchronize(st));
+    const uint32_t without = e->h_counts.ptr[1];
+    if (without == GFE_PEER_TIMEOUT) {
+        set_error(e, "gfe_search_sharded: a peer never reached epoch %u (GFE_PEER_TIMEOUT_MS)", x->epoch);
+        return GFE_ERR_CUDA;
+    }
+    *all_have = without == 0 ? 1 : 0;
+    return GFE_OK;
+}
+
 // ---- incremental search scoring (the ABI comment in include/gfalign_b200.h) ------------
 
 static int ensure_index(gfe_engine *e, uint32_t root_local, cudaStream_t st) {
@@ -1049,7 +1097,9 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
             set_error(e, "gfe_score_paths_incremental: item %u is malformed", i);
             return GFE_ERR_ARG;
         }
-        if (deal && (int)(kb % (uint32_t)x->world) != x->rank) continue;
+        // batch sharding: items of other ranks' subtrees are skipped only AFTER the argument checks, so that
+        // every rank returns the same GFE_ERR_* for a bad batch instead of one failing and its peers waiting
+        const bool mine = !(deal && (int)(kb % (uint32_t)x->world) != x->rank);
         const uint32_t s0 = b->suffix_offsets[i], ns = b->suffix_offsets[i + 1] - s0;
         const uint32_t nb = b->base_offsets[kb + 1] - b->base_offsets[kb];
         if ((uint64_t)nb + ns > GFE_MAX_STEPS) {
@@ -1058,8 +1108,10 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
             return GFE_ERR_LIMIT;
         }
         if (b->mode[i] == 0) {
-            slots.push_back(Slot{kNoNode, i, 0});
-            ++n_full;
+            if (mine) {
+                slots.push_back(Slot{kNoNode, i, 0});
+                ++n_full;
+            }
             continue;
         }
         if (nb + ns < (uint32_t)kMaxBucket + 1) {
@@ -1072,6 +1124,7 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
             set_error(e, "gfe_score_paths_incremental: item %u ends in a node outside the universe", i);
             return GFE_ERR_ARG;
         }
+        if (!mine) continue;
         // does the parent (the path without its last step) already visit v?
         bool revisit = false;
         if (ns) {
@@ -1384,9 +1437,22 @@ static int score_incremental_impl(gfe_engine *e, gfe_exchange *x, const gfe_path
         set_error(e, "gfe_score_paths_incremental: a step names a node outside the universe");
         return GFE_ERR_ARG;
     }
+    if (x && (any_flags >> 8)) {
+        // raised on another rank's shard only (flag_word_kernel: byte 2 = over-long alignment, byte 1 = bad
+        // step): every rank returns the same class of error, none retries alone and waits for the others
+        if ((any_flags >> 16) & 0xFFu) {
+            set_error(e, "gfe_score_paths_incremental_sharded: on another rank's shard an alignment of more than %u "
+                         "steps passes the id filter of a candidate path", GFE_MAX_STEPS);
+            return GFE_ERR_LIMIT;
+        }
+        set_error(e, "gfe_score_paths_incremental_sharded: another rank saw a step outside the universe");
+        return GFE_ERR_ARG;
+    }
     if (h[1] || h[3] || h[kWorkCounters + 1] || any_flags) {   // sharded: every rank repeats the batch together
-        // a list overflowed in one of the two chains: grow both lists and redo the batch
-        CUDA_TRY(e, cudaMemset(e->d_counts.ptr + kWorkCounters, 0, 2 * sizeof(uint32_t)));
+        // a list overflowed in one of the two chains: grow both lists and redo the batch.  The whole header
+        // is cleared: the failed attempt's overflow words (hdr[1], hdr[3]) would otherwise be promoted to the
+        // sticky flag by the retry's first prologue and a clean retry would be repeated once more
+        CUDA_TRY(e, cudaMemset(e->d_counts.ptr, 0, kHdrWords * sizeof(uint32_t)));
         if (++e->incr_retries > 6 || e->d_slow.cap >= ((size_t)1 << 28)) {
             e->incr_retries = 0;
             set_error(e, "gfe_score_paths_incremental: work lists still overflow; split the batch");

@@ -1265,8 +1265,8 @@ index_rows_kernel(const Buckets bk, const uint32_t L, const uint32_t root, uint3
 
 // exclusive scan of `groups` counters into off[0..groups] (one CTA; a one-off per universe) + cursor copy
 __global__ void __launch_bounds__(1024)
-index_scan_kernel(const uint32_t *__restrict__ cnt, uint32_t groups, uint32_t *__restrict__ off,
-                  uint32_t *__restrict__ cursor) {
+index_scan_kernel(const uint32_t *cnt, uint32_t groups, uint32_t *__restrict__ off,
+                  uint32_t *cursor) {   // cnt and cursor may be the same buffer (ensure_index): no __restrict__
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_carry;
     if (threadIdx.x == 0) s_carry = 0;
@@ -1435,12 +1435,17 @@ __global__ void status_flag_kernel(uint32_t *err, const uint32_t *wc, uint32_t *
     if (err) err[0] = err[1] = 0;   // reported: a later batch starts clean
 }
 
+// The word is SUMMED over up to GFE_PEER_MAX (16) ranks, so each condition counts ranks in a byte of its
+// own and the sum still tells them apart: byte 0 = ranks with a list overflow (all ranks repeat the batch),
+// byte 1 = ranks that saw a step outside the universe, byte 2 = ranks on whose shard an over-long alignment
+// passed the id filter (all ranks return the same error instead of retrying).
 __global__ void flag_word_kernel(const uint32_t *err, const uint32_t *wc, uint32_t *out) {
-    *out = (*err ? 1u : 0u) | ((wc[1] || wc[3]) ? 2u : 0u);
+    const uint32_t e = *err;
+    *out = ((wc[1] || wc[3]) ? 1u : 0u) | ((e & ~4u) ? 1u << 8 : 0u) | ((e & 4u) ? 1u << 16 : 0u);
 }
 
 __global__ void flag_or_kernel(const uint32_t *sticky, uint32_t *out) {
-    if (*sticky) *out |= 2u;
+    if (*sticky) *out |= 1u;
 }
 
 void launch_flag_or(const uint32_t *sticky, uint32_t *out, cudaStream_t st) {

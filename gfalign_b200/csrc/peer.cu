@@ -65,12 +65,20 @@ __global__ void __launch_bounds__(512) peer_sum_kernel(PeerArgs a) {
     __shared__ int s_timeout;
     if (threadIdx.x == 0) s_timeout = 0;
     __syncthreads();
+    // Callers test only the LAST slot (their flag word) for the poison.  Each CTA times its own wait, so a
+    // peer arriving right at the deadline could be seen by some CTAs and not by others.  The CTA that writes
+    // the last slot therefore gives up first; every other CTA waits 10 % + 1 ms longer.  If any CTA times
+    // out, the peer was still absent after the shorter deadline too, so the last slot is poisoned whenever
+    // any slot is.
+    const unsigned last_owner = a.n ? ((a.n - 1) / blockDim.x) % gridDim.x : 0u;
+    const unsigned long long limit_ns =
+        blockIdx.x == last_owner ? a.timeout_ns : a.timeout_ns + a.timeout_ns / 10 + 1000000ull;
     if (threadIdx.x < a.world) {
         const uint32_t *f = a.base[a.rank] + flag0 + threadIdx.x;
         const unsigned long long t0 = global_ns();
         while ((int32_t)(ld_acquire_sys(f) - a.epoch) < 0) {
             __nanosleep(20);
-            if (global_ns() - t0 > a.timeout_ns) {
+            if (global_ns() - t0 > limit_ns) {
                 s_timeout = 1;
                 break;
             }

@@ -591,8 +591,9 @@ static int run_search(gfe_score_fn score, void *score_user, const gfe_graph *g,
         d.T[x].extracted = true;
         if (d.T[x].depth < GFE_MAX_STEPS) {
             rc = eng ? d.score_children_tree(x) : d.score_children(x);
-            if (rc == GFE_ERR_STATE && eng) {
+            if (rc == GFE_ERR_STATE && eng && !xch) {
                 // no pair dictionary for this universe: the incremental path is off, use full scans
+                // (single engine only: over shards the choice is made for all ranks together, up front)
                 eng = nullptr;
                 d.eng = nullptr;
                 d.leave_path();
@@ -693,6 +694,9 @@ static int check_search_args(const gfe_graph *g, const gfe_search_params *p) {
     return GFE_OK;
 }
 
+// engine.cu (C++ linkage, not part of the C ABI): one-word vote over the exchange buffer
+int gfe_internal_incremental_consensus(gfe_engine *e, gfe_exchange *x, int *all_have);
+
 extern "C" int gfe_search(gfe_engine *e, const gfe_graph *g, const gfe_search_params *p,
                           gfe_row_fn emit, void *user, gfe_search_stats *stats) {
     if (!e) return GFE_ERR_ARG;
@@ -731,7 +735,15 @@ extern "C" int gfe_search_sharded(gfe_engine *e, gfe_exchange *x, const gfe_grap
     if (rc != GFE_OK) return rc;
     ShardedUser u{e, x};
     const char *fs = getenv("GFE_SEARCH_FULLSCAN");
-    const bool full = fs && fs[0] == '1';
+    bool full = fs && fs[0] == '1';
+    if (!full) {
+        // a rank whose shard has no pair dictionary can only run full scans, and the two scoring entries
+        // exchange records of different shapes: all ranks take the incremental path, or none does
+        int all_have = 0;
+        rc = gfe_internal_incremental_consensus(e, x, &all_have);
+        if (rc != GFE_OK) return rc;
+        full = !all_have;
+    }
     return run_search(sharded_scorer, &u, g, p, emit, user, stats, full ? nullptr : e, full ? nullptr : x);
 }
 

@@ -109,6 +109,10 @@ def main(argv=None):
     else:
         cuts = sharded.shard_bounds(tp.offsets, world)
         off, st = sharded.take_shard(tp.offsets, tp.steps, int(cuts[rank]), int(cuts[rank + 1]))
+    if os.environ.get("GFE_TEST_LEGACY_RANK") == str(rank):
+        # test hook: THIS rank alone runs without the pair dictionary / incremental path, as a rank whose
+        # shard overflows the dictionary would; gfe_search_sharded must then use full scans on every rank
+        os.environ["GFE_FORCE_LEGACY"] = "1"
     eng = capi.Engine(local)
     eng.set_alignments(off, st, tp.n_nodes)
 

@@ -104,3 +104,9 @@ int gfe_score_paths_incremental_sharded(gfe_engine *e, gfe_exchange *, const gfe
 }
 
 }  // extern "C"
+
+// library-internal vote of gfe_search_sharded (engine.cu): the stub is a single rank that has the path
+int gfe_internal_incremental_consensus(gfe_engine *, gfe_exchange *, int *all_have) {
+    *all_have = 1;
+    return GFE_OK;
+}

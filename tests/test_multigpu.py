@@ -12,8 +12,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 pytestmark = pytest.mark.gpu
 
 
-def _torchrun(n, args, cwd, port):
-    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
+def _torchrun(n, args, cwd, port, **extra_env):
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""), **extra_env)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), "-m", "gfalign_b200.multigpu"] + args
     return subprocess.run(cmd, cwd=cwd, env=env, capture_output=True, text=True, timeout=600)
@@ -45,6 +45,34 @@ def test_two_gpu_search_and_evalgfa_match_reference(tmp_path):
             assert out == c["out_text"], c["name"]
         seen += 1
     assert seen == 5
+
+
+def test_two_gpu_search_when_one_rank_has_no_incremental_path(tmp_path):
+    """One rank without a pair dictionary (here forced: GFE_FORCE_LEGACY on rank 1 only) can only answer
+    full scans; its peers must not keep sending incremental records under the same epochs.
+    gfe_search_sharded votes once over the exchange buffer and all ranks fall back together: the rows stay
+    the reference's."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    port = 29630
+    seen = 0
+    for c in _cases():
+        if c["name"] not in ("tangle1_search_all", "tangle2_search"):
+            continue
+        d = os.path.join(str(tmp_path), c["name"])
+        os.makedirs(d)
+        for fn, txt in c["files"].items():
+            with open(os.path.join(d, fn), "w") as f:
+                f.write(txt)
+        for legacy_rank in ("1", "0"):
+            p = _torchrun(2, list(c["args"]) + ["--shard", "alignments"], d, port, GFE_TEST_LEGACY_RANK=legacy_rank,
+                          GFE_PEER_TIMEOUT_MS="5000")
+            port += 1
+            assert p.returncode == 0, p.stderr[-2000:]
+            assert p.stdout == c["stdout"], (c["name"], legacy_rank)
+        seen += 1
+    assert seen == 2
 
 
 def test_peer_exchange_matches_nccl():
