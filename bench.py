@@ -338,6 +338,89 @@ def counters_child(args):
     eng.close()
 
 
+CFG5_PIECES = 8
+# rows of `search -m 20000` on the default cfg5 table (50 M alignments, 8 pieces), as emitted at N = 1 with every
+# candidate scored by full scans AND by the incremental path (they agreed); runs at N > 1 must reproduce it
+CFG5_SEARCH_SHA1 = {(50_000_000, 20000): "211e21f36920c6cd"}      # {(A_total, max_steps): sha1[:16]}
+
+
+def _row_key(r):
+    return (int(r.path_counter), int(r.bad), int(r.good), int(r.alt), int(r.uniques), int(r.hamiltonian),
+            tuple(int(v) for v in r.steps))
+
+
+def _rows_sha1(rows):
+    import hashlib
+    return hashlib.sha1(repr([_row_key(r) for r in rows]).encode()).hexdigest()[:16]
+
+
+def search_cfg5(args, rank, world, dist, dev, eng, t, nodes, counts, node_count, fixed_table):
+    """BASELINE configs[4] as the reference would run it: dijkstra() end to end (reference src/eval.cpp:110-193,
+    one evaluatePath per expansion :162) on the 400-node tangle with the 50 M alignments split over the ranks
+    — gfe_search at N = 1, gfe_search_sharded (incremental records summed by the peer kernel) at N > 1; -m is
+    the same at every N, so seconds_search_loop over N is strong scaling."""
+    import torch
+    from gfalign_b200.sharded import PeerExchange
+    m_steps = args.cfg5_search_steps
+    cx = px_s = None
+    if dist is not None:
+        px_s = PeerExchange(1 << 18, dev)     # must outlive the handle: it owns the peer-mapped buffer
+        cx = px_s.c_exchange()
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    kw = dict(max_steps=m_steps)
+    s0 = time.perf_counter()
+    if cx is not None:
+        rows, st = eng.search_sharded(cx, t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source, t.destination,
+                                      nodes, counts, node_count, **kw)
+    else:
+        rows, st = eng.search(t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source, t.destination,
+                              nodes, counts, node_count, **kw)
+    wall = time.perf_counter() - s0
+    sha = _rows_sha1(rows)
+    tm = torch.tensor([st["seconds_total"], st["seconds_scoring"], wall], dtype=torch.float64, device=dev)
+    agree = True
+    if dist is not None:
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        sig = torch.tensor([int(sha, 16) >> 2], dtype=torch.int64, device=dev)
+        lo, hi = sig.clone(), sig.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        agree = bool(torch.equal(lo, hi))
+    loop_s = float(tm[0].item())
+    out = {"workload": "gfalign search on the cfg5 table (sharded over the ranks), source/destination of the tangle",
+           "max_steps": m_steps, "n_gpus": world, "alignments_total": args.cfg5_alignments,
+           "evaluatePath_calls": st["evaluations"], "paths_per_s": st["evaluations"] / loop_s,
+           "seconds_search_loop": loop_s, "seconds_scoring": float(tm[1].item()),
+           "seconds_incl_universe_and_index": float(tm[2].item()),
+           "kernel_batches": st["kernel_batches"], "paths_scored": st["paths_scored"],
+           "speculation_hit_rate": st["evaluations"] / max(st["paths_scored"], 1), "rows": len(rows),
+           "rows_sha1": sha, "rows_identical_on_all_ranks": agree}
+    if not agree:
+        raise SystemExit("cfg5 search rows differ between ranks")
+    if world == 1 and not args.no_cfg5_fullscan:
+        # the checker of the incremental path at this size: every candidate through a full scan
+        os.environ["GFE_SEARCH_FULLSCAN"] = "1"
+        try:
+            f0 = time.perf_counter()
+            rows_fs, st_fs = eng.search(t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source, t.destination,
+                                        nodes, counts, node_count, **kw)
+            out["fullscan_driver_seconds"] = time.perf_counter() - f0
+        finally:
+            del os.environ["GFE_SEARCH_FULLSCAN"]
+        out["rows_equal_fullscan_driver"] = ([_row_key(r) for r in rows] == [_row_key(r) for r in rows_fs]
+                                             and st_fs["evaluations"] == st["evaluations"])
+        if not out["rows_equal_fullscan_driver"]:
+            raise SystemExit("cfg5: incremental search rows differ from the full-scan driver's")
+    del cx, px_s
+    want = CFG5_SEARCH_SHA1.get((args.cfg5_alignments, m_steps)) if fixed_table else None
+    out["rows_sha1_expected_from_n1"] = want
+    out["rows_equal_n1"] = None if want is None else (want == sha)
+    if want is not None and want != sha:
+        raise SystemExit(f"cfg5 search rows differ from the N = 1 rows: {sha} != {want}")
+    return out
+
+
 def strong_cfg5(args, rank, world, local, dist, dev, orc, flush):
     """BASELINE configs[4]: 400-node dense ONT tangle, 50 M alignments split over the N ranks (N = 1: the
     whole table on one GPU), P candidate paths per step, exchange inside the timed step."""
@@ -351,8 +434,16 @@ def strong_cfg5(args, rank, world, local, dist, dev, orc, flush):
     t = synth.make_tangle(400, 800, seed=3, minus_frac=0.05, count2_frac=0.10)
     nodes, counts, node_count = synth.node_table(t)
     t0 = time.perf_counter()
-    d_off, d_st = synth.random_walk_alignments_device(t.n_nodes, t.edge_from, t.edge_to, A, *synth.ONT_LENGTHS,
-                                                      seed=1300 + rank, device=dev)
+    # ONE table at every N: it is drawn as CFG5_PIECES pieces (seed 1300 + piece) and rank r of N holds the
+    # pieces [r * PIECES / N, (r + 1) * PIECES / N), so the union over the ranks — and with it every summed
+    # count and every search row — is the same for N = 1, 2, 4, 8
+    fixed_table = CFG5_PIECES % world == 0 and A_total % CFG5_PIECES == 0
+    if fixed_table:
+        d_off, d_st = synth.table_shard_device(t.n_nodes, t.edge_from, t.edge_to, A_total, *synth.ONT_LENGTHS,
+                                               seed=1300, device=dev, rank=rank, world=world, pieces=CFG5_PIECES)
+    else:
+        d_off, d_st = synth.random_walk_alignments_device(t.n_nodes, t.edge_from, t.edge_to, A, *synth.ONT_LENGTHS,
+                                                          seed=1300 + rank, device=dev)
     torch.cuda.synchronize(dev)
     gen_s = time.perf_counter() - t0
     S = int(d_off[-1].item())
@@ -437,7 +528,9 @@ def strong_cfg5(args, rank, world, local, dist, dev, orc, flush):
                        "peer-memory sum kernel" if px is not None else ("nccl all-reduce" if dist is not None else "none"))
     ms_step = total_ms / steps_k
     out = {"workload": "cfg5 synthetic dense ONT tangle: 400 nodes, 50M alignments split over the GPUs "
-                       "(table drawn on the device, seed 1300 + rank)",
+                       "(table drawn on the device in 8 pieces, seed 1300 + piece: the same union at N = 1/2/4/8)"
+                       if fixed_table else "cfg5 synthetic dense ONT tangle (table drawn on the device, seed 1300 + rank)",
+           "same_table_at_every_n": fixed_table,
            "A_total": A * world, "alignments_per_gpu": A, "mean_steps": S / A, "candidate_paths_per_step": P,
            "n_gpus": world, "steps": steps_k, "ms_per_step": ms_step,
            "checks_per_s": float(P) * A * world / (ms_step * 1e-3), "k1_ms": k1_mean,
@@ -468,6 +561,8 @@ def strong_cfg5(args, rank, world, local, dist, dev, orc, flush):
                     "in_use": ds["in_use"], "rows": ds["rows"], "view_rows": ds["view_rows"],
                     "row_reduction": ds["rows"] / max(ds["view_rows"], 1), "ms_per_step": float(dd.item()),
                     "counts_equal_brute_force": same}
+    if not args.no_search:
+        out["search"] = search_cfg5(args, rank, world, dist, dev, eng, t, nodes, counts, node_count, fixed_table)
     eng.close()
     del d_off, d_st
     if not par["ok"]:
@@ -495,6 +590,8 @@ def main():
     ap.add_argument("--no-cfg5", action="store_true", help="skip the cfg5 strong-scaling block")
     ap.add_argument("--cfg5-alignments", type=int, default=50_000_000)
     ap.add_argument("--cfg5-paths", type=int, default=1024)
+    ap.add_argument("--cfg5-search-steps", type=int, default=20000, help="-m of the cfg5 search block (same at every N)")
+    ap.add_argument("--no-cfg5-fullscan", action="store_true", help="skip the N = 1 full-scan check of the cfg5 search")
     ap.add_argument("--no-ncu", action="store_true")
     ap.add_argument("--counters-child", action="store_true", help=argparse.SUPPRESS)
     args = ap.parse_args()
@@ -851,6 +948,29 @@ def main():
                         "exact) / seconds of the search loop; reported separately from brute-force checks/s"}
         if not rows_agree:
             raise SystemExit("search rows differ between ranks")
+
+        row_key = _row_key
+        srch["rows_sha1"] = _rows_sha1(rows)
+        if world == 1:
+            # the same search with EVERY candidate scored by a full scan (gfe_score_paths, the kernel the oracle
+            # check above covers): the incremental path must emit the same rows in the same order
+            # (emission order is the contract: reference src/eval.cpp:176-183)
+            os.environ["GFE_SEARCH_FULLSCAN"] = "1"
+            try:
+                with gfalign_b200.Engine(local) as e4:
+                    e4.set_alignments(off, steps, t.n_nodes)
+                    f0 = time.perf_counter()
+                    rows_fs, st_fs = e4.search(t.adj_offsets, t.adj_target, t.adj_or0, t.adj_or1, t.source,
+                                               t.destination, nodes, counts, node_count, max_steps=m_steps)
+                    fs_sec = time.perf_counter() - f0
+            finally:
+                del os.environ["GFE_SEARCH_FULLSCAN"]
+            same_rows = [row_key(r) for r in rows] == [row_key(r) for r in rows_fs]
+            srch["rows_equal_fullscan_driver"] = same_rows
+            srch["fullscan_driver_seconds"] = fs_sec
+            srch["fullscan_evaluatePath_calls"] = st_fs["evaluations"]
+            if not same_rows or st_fs["evaluations"] != st["evaluations"]:
+                raise SystemExit("incremental search rows differ from the full-scan driver's")
         line["search"] = srch
         if cx is not None:
             # strong scaling of the N = 1 search (the cfg3 table of rank 0, replicated): candidate-batch sharding
@@ -900,6 +1020,29 @@ def main():
         if "search" in line and "search_paths_per_s" in cb:
             line["search"]["reference_paths_per_s"] = cb["search_paths_per_s"]
     if rank == 0:
+        # the numbers a reader of the last ~1 KB of the line needs (records that keep only a tail of it)
+        tail = {}
+        if "search" in line:
+            sr = line["search"]
+            tail["search"] = {k: sr[k] for k in ("max_steps", "alignments_total", "evaluatePath_calls", "paths_per_s",
+                                                 "seconds_search_loop", "seconds_scoring", "kernel_batches",
+                                                 "speculation_hit_rate", "rows", "rows_sha1",
+                                                 "rows_identical_on_all_ranks", "rows_equal_fullscan_driver")
+                              if k in sr}
+        if isinstance(line.get("strong_cfg5"), dict):
+            c5 = line["strong_cfg5"]
+            tail["strong_cfg5"] = {k: c5[k] for k in ("A_total", "n_gpus", "ms_per_step", "k1_ms", "exchange_ms",
+                                                      "worklist_and_launch_ms", "checks_per_s") if k in c5}
+            tail["strong_cfg5"]["parity_ok"] = (c5.get("parity_check") or {}).get("ok")
+            if isinstance(c5.get("search"), dict):
+                tail["search_cfg5"] = {k: c5["search"][k] for k in (
+                    "max_steps", "n_gpus", "alignments_total", "evaluatePath_calls", "paths_per_s", "seconds_search_loop",
+                    "seconds_scoring", "rows", "rows_sha1", "rows_equal_n1", "rows_equal_fullscan_driver",
+                    "rows_identical_on_all_ranks") if k in c5["search"]}
+        tail["headline"] = {"value": line.get("value"), "e2e": (line.get("e2e") or {}).get("value"),
+                            "ms_per_step": line.get("ms_per_step"), "n_gpus": line.get("n_gpus"),
+                            "parity_ok": (line.get("parity_check") or {}).get("ok")}
+        line["tail_summary"] = tail
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()

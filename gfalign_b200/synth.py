@@ -309,3 +309,25 @@ def random_walk_alignments_device(n_nodes: int, edge_from: np.ndarray, edge_to: 
     assert int(offsets[-1]) < 2 ** 31
     steps = torch.cat(step_chunks) if step_chunks else torch.zeros(0, dtype=torch.int32, device=device)
     return offsets.to(torch.int32), steps
+
+
+def table_shard_device(n_nodes: int, edge_from: np.ndarray, edge_to: np.ndarray, A_total: int,
+                       lengths: Sequence[int], probs: Sequence[float], seed: int, device, rank: int = 0,
+                       world: int = 1, pieces: int = 8):
+    """Rank `rank`'s shard of ONE table that is the same for every world size dividing `pieces`: the table is
+    drawn as `pieces` pieces of A_total / pieces rows (seed + piece) and the rank holds the pieces
+    [rank * pieces / world, (rank + 1) * pieces / world), concatenated.  Summed counts and search rows over
+    the ranks are therefore identical at N = 1, 2, 4, 8.  -> (offsets int32[A+1], steps int32[S]) on device."""
+    import torch
+    assert pieces % world == 0 and A_total % pieces == 0
+    per = pieces // world
+    offs, sts, base = [], [], 0
+    for pc in range(rank * per, (rank + 1) * per):
+        o, s_ = random_walk_alignments_device(n_nodes, edge_from, edge_to, A_total // pieces, lengths, probs,
+                                              seed=seed + pc, device=device)
+        offs.append(o[:-1] + base)
+        sts.append(s_)
+        base += int(o[-1].item())
+    assert base < 2 ** 31
+    offs.append(torch.tensor([base], dtype=torch.int32, device=device))
+    return torch.cat(offs), torch.cat(sts)
