@@ -1,6 +1,6 @@
 """Search driver on the cfg5 table of bench.py (400-node tangle, 50 M alignments drawn on the device in 8 pieces,
 one GPU): seconds of `gfe_search -m <max_steps>` vs the speculation parameters, the full-scan driver
-(GFE_SEARCH_FULLSCAN=1) as the row checker.  usage: python profiles/search_sweep_cfg5.py [max_steps] [A_total]"""
+(GFE_SEARCH_FULLSCAN=1) as the row checker.  usage: python profiles/search_sweep_cfg5.py [max_steps] [A_total] [one]"""
 import json
 import os
 import sys
@@ -41,6 +41,10 @@ def run(label, **env):
     return key
 
 
+if len(sys.argv) > 3 and sys.argv[3] == "one":      # ncu captures: the default policy only
+    run("incremental (default policy)")
+    eng.close()
+    sys.exit(0)
 ref = run("full-scan driver", GFE_SEARCH_FULLSCAN=1)
 for width, roots in ((4096, 256), (4096, 16), (1024, 256), (1024, 16), (1024, 1), (256, 16), (256, 1), (64, 8), (64, 1),
                      (16, 1)):

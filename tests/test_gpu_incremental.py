@@ -120,6 +120,21 @@ def test_incremental_cfg5_shape_and_wide_batch(engine, oracle):
     assert n_delta > 400
 
 
+def test_incremental_cfg5_real_shape_3m_rows(engine, oracle):
+    """cfg5 at a size where the per-node index lists are long (3 M rows of 4-16 steps over 400 nodes: ~75 k
+    rows per node, thousands of claim units per chunk) — parents by full scan, children by delta, both against
+    the oracle.  The bench runs the whole search on the 50 M-row table against the full-scan driver; this is
+    the oracle-side check of the same kernel regime."""
+    w = synth.make_workload("cfg5", A=3_000_000)
+    t = w.tangle
+    nodes, _, _ = synth.node_table(t)
+    po, ps = synth.candidate_paths(t, 64, seed=78)
+    paths = [ps[po[i]:po[i + 1]].tolist() for i in range(64)]
+    rng = np.random.default_rng(5)
+    n_delta = _check_batch(engine, oracle, w.offsets, w.steps, t.n_nodes, nodes, paths, rng, os.cpu_count() or 1)
+    assert n_delta > 30
+
+
 def test_search_rows_incremental_equal_full_scan(engine):
     """gfe_search with incremental scoring (default) emits the rows of the same search scored by full
     scans (GFE_SEARCH_FULLSCAN=1), for several speculation widths; paths here reach ~100 steps."""
